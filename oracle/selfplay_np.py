@@ -1,0 +1,83 @@
+"""Oracle self-play loop and record format: restatement of Blackbird.GenerateTrainingSamples
+(Blackbird.py:219-268) and ExampleState.SerializeState (Blackbird.py:68-81, proto/state.proto:3-9).
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).
+"""
+import struct
+
+import numpy as np
+
+
+def _varint(n):
+    out = bytearray()
+    while True:
+        b = n & 0x7F
+        n >>= 7
+        if n:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _bytes_field(number, payload):
+    if not payload:
+        return b''                                   # proto3: default values are not emitted
+    return bytes([(number << 3) | 2]) + _varint(len(payload)) + payload
+
+
+def dims_int8(shape):
+    """np.array(shape, dtype=np.int8).tobytes() with legacy wrap-around.
+
+    numpy 2 raises OverflowError for DragonChess' policyDims=[4032]; legacy
+    numpy wrapped to 0xC0.  The engine emits the wrapped byte and so does the oracle.
+    """
+    return bytes((int(d) & 0xFF) for d in shape)
+
+
+def serialize_record(evaluation, policy, planes):
+    """State{float mctsEval=1; bytes mctsPolicy=2; bytes boardEncoding=3; bytes boardDims=4;
+    bytes policyDims=5} in field order (state.proto:3-9)."""
+    out = b''
+    ev = float(evaluation)
+    if struct.pack('<f', ev) != b'\x00\x00\x00\x00':
+        out += b'\x0d' + struct.pack('<f', ev)
+    out += _bytes_field(2, np.ascontiguousarray(policy, dtype=np.float64).tobytes())
+    out += _bytes_field(3, np.ascontiguousarray(planes, dtype=np.int8).tobytes())
+    out += _bytes_field(4, dims_int8(planes.shape))
+    out += _bytes_field(5, dims_int8(policy.shape))
+    return out
+
+
+def play_game(search, game_cls, temp, max_plies=None):
+    """One iteration of the loop at Blackbird.py:238-267.
+
+    Returns (records: list[bytes], winner, trace) where trace holds, per move,
+    (child plays f64[A], chosen action, Root.WinRate(), Root.Plays) for KAT tests.
+    winner is None only when ``max_plies`` truncated the game (engine-side cap, A.20).
+    """
+    history = []
+    trace = []
+    state = game_cls()
+    winner = None
+    search.DropRoot()
+    probs = None
+    while winner is None:
+        nxt, v, probs = search.FindMove(state, temp)
+        root = search.Root
+        trace.append((root.ChildPlays().copy(), search.LastAction, v, root.Plays))
+        history.append([1 - v, probs, state.AsInputArray(), state.Player])
+        state = nxt
+        search.MoveRoot(state)
+        winner = state.Winner(None)                  # lastAction is always None (Blackbird.py:242,253)
+        if max_plies is not None and len(history) >= max_plies and winner is None:
+            break
+    history.append([None, np.zeros([len(probs)]), state.AsInputArray(), state.Player])
+    for ex in history:                               # Blackbird.py:260-264 (A.27)
+        if winner is None:
+            ex[0] = 0                                # truncated: engine convention, not in the reference
+        elif winner == 0:
+            ex[0] = 0
+        else:
+            ex[0] = 1 if ex[3] == winner else -1
+    return [serialize_record(e[0], e[1], e[2]) for e in history], winner, trace
