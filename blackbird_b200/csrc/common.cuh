@@ -1,0 +1,57 @@
+// Shared helpers for libbbengine.so translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/bbengine.h"
+#include "games.cuh"
+
+namespace bb {
+
+void set_error(const char* fmt, ...);
+
+#define BB_CUDA(call)                                                                     \
+  do {                                                                                    \
+    cudaError_t _e = (call);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      bb::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return BB_ECUDA;                                                                    \
+    }                                                                                     \
+  } while (0)
+
+#define BB_DISPATCH_GAME(game, ...)                                                       \
+  switch (game) {                                                                         \
+    case BB_TICTACTOE: { using G = bb::TicTacToe; __VA_ARGS__; } break;                   \
+    case BB_CONNECT4: { using G = bb::Connect4; __VA_ARGS__; } break;                     \
+    case BB_DRAGONCHESS: { using G = bb::DragonChess; __VA_ARGS__; } break;               \
+    default: bb::set_error("unknown game id %d", (int)(game)); return BB_EINVAL;          \
+  }
+
+// Appendix B.2 evaluator over n (or min(n, *count_dev)) packed states (rules.cu)
+int launch_kat(int game, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream);
+
+// Built-in network (net.cu)
+struct NetDev;
+int net_create(int game, const bb_net_desc* d, const float* w_host, size_t n_floats, NetDev** out);
+void net_destroy(NetDev* net);
+int net_forward(NetDev* net, const void* states_dev, int n, const int* count_dev, float* policy, float* value,
+                cudaStream_t stream);
+
+static inline unsigned grid_for(long long n, int block) { return (unsigned)((n + block - 1) / block); }
+
+// Appendix B.2 integer evaluator hash over the flattened [1,H,W,C] planes.
+template <class G>
+__device__ __forceinline__ uint32_t kat_hash(const typename G::State& s) {
+  long long acc = 0;
+  for (int cell = 0; cell < G::H * G::W; ++cell) {
+#pragma unroll
+    for (int ch = 0; ch < G::C; ++ch) acc += (long long)(cell * G::C + ch + 1) * G::plane(s, cell, ch);
+  }
+  long long m = acc % 1000003ll;
+  if (m < 0) m += 1000003ll;
+  return (uint32_t)m;
+}
+
+}  // namespace bb

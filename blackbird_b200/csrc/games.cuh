@@ -58,6 +58,7 @@ struct TicTacToe {
   BB_HD static void set_meta(State& s, int player, int prev) {
     s.v = (s.v & 0x3FFFFu) | ((uint32_t)(player - 1) << 18) | ((uint32_t)prev << 19);
   }
+  BB_HD static int next_player(const State& s) { return 3 - player(s); }
   BB_HD static uint32_t xs(const State& s) { return s.v & 0x1FF; }
   BB_HD static uint32_t os(const State& s) { return (s.v >> 9) & 0x1FF; }
 
@@ -122,6 +123,7 @@ struct Connect4 {
   BB_HD static void set_meta(State& s, int player, int prev) {
     s.o = (s.o & BOARD) | ((uint64_t)(player - 1) << 56) | ((uint64_t)prev << 57);
   }
+  BB_HD static int next_player(const State& s) { return 3 - player(s); }
   BB_HD static uint64_t xs(const State& s) { return s.x & BOARD; }
   BB_HD static uint64_t os(const State& s) { return s.o & BOARD; }
 
@@ -223,6 +225,7 @@ struct DragonChess {
   }
   BB_HD static int player(const State& s) { return 1 + ((s.meta >> 4) & 1); }
   BB_HD static int prev(const State& s) { return (s.meta >> 5) & 3; }
+  BB_HD static int next_player(const State& s) { return (prev(s) == 1 && player(s) == 1) ? 2 : 1; }
   BB_HD static int at(const State& s, int r, int c) { return (s.row[r] >> (4 * c)) & 0xF; }
   BB_HD static void put(State& s, int r, int c, int v) {
     s.row[r] = (s.row[r] & ~(0xFu << (4 * c))) | ((uint32_t)v << (4 * c));

@@ -1,0 +1,463 @@
+// Engine host side: owns the tree pool in HBM, runs the tick loop (advance kernel + evaluator),
+// and implements the search / self-play / record entry points of include/bbengine.h.
+#include <vector>
+
+#include "search_kernels.cuh"
+
+namespace bb {
+
+static void plan_rec(PairwisePlan& P, int lo, int n) {        // numpy pairwise_sum recursion (A.11)
+  if (n <= 128) {
+    int id = P.n_leaves++;
+    P.leaf_lo[id] = (int16_t)lo;
+    P.leaf_n[id] = (int16_t)n;
+    P.ops[P.n_ops++] = (int8_t)id;
+    return;
+  }
+  int n2 = n / 2;
+  n2 -= n2 % 8;
+  plan_rec(P, lo, n2);
+  plan_rec(P, lo + n2, n - n2);
+  P.ops[P.n_ops++] = -1;
+}
+
+template <class G>
+__global__ void k_root_stats(EngineDev<G> E, int kmax, int32_t* n_children, int32_t* actions, uint32_t* plays,
+                             float* child_value, double* child_prior, uint32_t* root_plays, double* root_value,
+                             int32_t* root_has_parent) {
+  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (g >= E.n_games) return;
+  const Slot<G> s = E.slots[g];
+  const int lane = lane_id();
+  if (s.root == NONE) { if (lane == 0) { n_children[g] = -1; root_plays[g] = 0; root_value[g] = 0; root_has_parent[g] = 0; } return; }
+  const NodeHdr* hdr = E.hdr + (size_t)g * E.node_cap;
+  const NodeStat* stat = E.stat + (size_t)g * E.node_cap;
+  const NodeHdr rh = hdr[s.root];
+  const int k = rh.child_base == NONE ? -1 : meta_nchild(rh.meta);
+  if (lane == 0) {
+    n_children[g] = k;
+    root_plays[g] = stat[s.root].plays;
+    root_value[g] = (double)stat[s.root].value;
+    root_has_parent[g] = s.root_parent_player != 0;
+  }
+  for (int j = lane; j < k && j < kmax; j += 32) {
+    const size_t o = (size_t)g * kmax + j;
+    const NodeStat st = stat[rh.child_base + j];
+    actions[o] = meta_action(hdr[rh.child_base + j].meta);
+    plays[o] = st.plays;
+    child_value[o] = st.value;
+    child_prior[o] = st.prior;
+  }
+}
+
+template <class G>
+__global__ void k_gather_slots(EngineDev<G> E, typename G::State* states, int32_t* phases, int32_t* status) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= E.n_games) return;
+  if (states) states[g] = E.slots[g].root_state;
+  if (phases) phases[g] = E.slots[g].phase;
+  if (status) status[g] = E.slots[g].status;
+}
+
+}  // namespace bb
+
+using namespace bb;
+
+struct bb_engine {
+  bb_config cfg;
+  virtual ~bb_engine() {}
+  virtual int net_load(const bb_net_desc*, const float*, size_t) = 0;
+  virtual int net_fwd(const void*, int, float*, float*, cudaStream_t) = 0;
+  virtual int reset(const void* states_dev) = 0;
+  virtual int drop_root() = 0;
+  virtual int begin_move(int play_limit) = 0;
+  virtual int run(int* pending) = 0;
+  virtual int root_stats(int, int32_t*, int32_t*, uint32_t*, float*, double*, uint32_t*, double*, int32_t*) = 0;
+  virtual int choose(double, const double*, int32_t*) = 0;
+  virtual int move_root(const int32_t*) = 0;
+  virtual int states(void*) = 0;
+  virtual int phases(int32_t*, int32_t*) = 0;
+  virtual int eval_pending(int32_t*, const int32_t**, const void**) = 0;
+  virtual int eval_fetch(void*, int32_t*) = 0;
+  virtual int eval_submit(const float*, const float*) = 0;
+  virtual int selfplay(int, double, const double*) = 0;
+  virtual int pool_cap() = 0;
+  virtual int records_export(int32_t*, int32_t*, void*, uint32_t*, uint16_t*, uint32_t*, uint16_t*) = 0;
+  virtual int records_device(void**, void**, void**, void**, void**, void**, void**) = 0;
+  virtual int counters(bb_counters*, int) = 0;
+};
+
+template <class G>
+struct EngineT : bb_engine {
+  using State = typename G::State;
+  EngineDev<G> d{};
+  NetDev* net = nullptr;
+  cudaStream_t stream = nullptr;
+  std::vector<void*> allocs;
+  double* uniforms_dev = nullptr;
+  int* host_flags = nullptr;       // pinned: [0] active, [1] req_count
+  void* scratch = nullptr;         // device scratch for exports
+  size_t scratch_bytes = 0;
+  unsigned long long host_ticks = 0, host_launches = 0;
+
+  template <class T>
+  int alloc(T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, count * sizeof(T));
+    if (e != cudaSuccess) { set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e)); return BB_ENOMEM; }
+    allocs.push_back(q);
+    *p = (T*)q;
+    return BB_OK;
+  }
+  int ensure_scratch(size_t bytes) {
+    if (bytes <= scratch_bytes) return BB_OK;
+    if (scratch) cudaFree(scratch);
+    scratch = nullptr;
+    scratch_bytes = 0;
+    BB_CUDA(cudaMalloc(&scratch, bytes));
+    scratch_bytes = bytes;
+    return BB_OK;
+  }
+
+  int init(const bb_config& c) {
+    cfg = c;
+    BB_CUDA(cudaSetDevice(c.device));
+    BB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    PairwisePlan P{};
+    plan_rec(P, 0, G::A);
+    BB_CUDA(cudaMemcpyToSymbol(c_plan, &P, sizeof P, sizeof(PairwisePlan) * G::ID));
+    const size_t n = c.n_games, cap = c.node_cap;
+    d.n_games = c.n_games;
+    d.node_cap = c.node_cap;
+    d.search = c.search;
+    d.max_depth = c.max_depth;
+    d.max_plies = c.max_plies;
+    d.c = c.exploration_rate;
+    d.pool_cap = (uint32_t)c.max_plies * (uint32_t)(G::A < 64 ? G::A : 64);
+    int rc;
+#define A_(p, cnt) if ((rc = alloc(&p, cnt)) != BB_OK) return rc
+    A_(d.slots, n);
+    A_(d.hdr, n * cap);
+    A_(d.stat, n * cap);
+    A_(d.req_count, 1);
+    A_(d.active, 1);
+    A_(d.req_slot, n);
+    A_(d.req_state, n);
+    A_(d.resp_policy, n * G::A);
+    A_(d.resp_value, n);
+    A_(d.rec_states, n * (c.max_plies + 1));
+    A_(d.rec_off, n * (c.max_plies + 2));
+    A_(d.pool_actions, n * d.pool_cap);
+    A_(d.pool_plays, n * d.pool_cap);
+    A_(d.chosen, n * c.max_plies);
+    A_(d.n_moves, n);
+    A_(d.winners, n);
+    A_(d.counters, 1);
+    A_(uniforms_dev, n * c.max_plies);
+#undef A_
+    BB_CUDA(cudaMemset(d.counters, 0, sizeof(Counters)));
+    BB_CUDA(cudaMemset(d.rec_off, 0, n * (c.max_plies + 2) * sizeof(uint32_t)));
+    BB_CUDA(cudaMallocHost(&host_flags, 4 * sizeof(int)));
+    d.uniforms = uniforms_dev;
+    return reset(nullptr);
+  }
+  ~EngineT() override {
+    cudaSetDevice(cfg.device);
+    if (stream) cudaStreamSynchronize(stream);
+    for (void* p : allocs) cudaFree(p);
+    if (scratch) cudaFree(scratch);
+    if (host_flags) cudaFreeHost(host_flags);
+    if (net) net_destroy(net);
+    if (stream) cudaStreamDestroy(stream);
+  }
+
+  unsigned warp_grid() const { return grid_for((long long)d.n_games * 32, 128); }
+
+  int net_load(const bb_net_desc* nd, const float* w, size_t nfl) override {
+    BB_CUDA(cudaSetDevice(cfg.device));
+    if (net) { net_destroy(net); net = nullptr; }
+    return net_create(G::ID, nd, w, nfl, &net);
+  }
+  int net_fwd(const void* st, int n, float* pol, float* val, cudaStream_t s) override {
+    if (!net) { set_error("bb_net_forward: no network loaded (bb_net_load)"); return BB_ESTATE; }
+    return net_forward(net, st, n, nullptr, pol, val, s);
+  }
+  int reset(const void* states_dev) override {
+    BB_CUDA(cudaSetDevice(cfg.device));
+    k_reset<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d, (const State*)states_dev);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int drop_root() override {
+    k_drop_root<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d);
+    BB_CUDA(cudaGetLastError());
+    return BB_OK;
+  }
+  int begin_move(int play_limit) override {
+    if (play_limit <= 0) { set_error("play_limit must be > 0"); return BB_EINVAL; }
+    k_begin_move<G><<<warp_grid(), 128, 0, stream>>>(d, play_limit);
+    BB_CUDA(cudaGetLastError());
+    return BB_OK;
+  }
+
+  // one tick = advance kernel (+ evaluator kernel)
+  int tick() {
+    BB_CUDA(cudaMemsetAsync(d.req_count, 0, sizeof(int), stream));
+    BB_CUDA(cudaMemsetAsync(d.active, 0, sizeof(int), stream));
+    k_advance<G><<<warp_grid(), 128, 0, stream>>>(d);
+    BB_CUDA(cudaGetLastError());
+    host_ticks++;
+    host_launches++;
+    if (cfg.evaluator == BB_EVAL_KAT) {
+      int rc = launch_kat(G::ID, d.req_state, d.n_games, d.req_count, d.resp_policy, d.resp_value, stream);
+      if (rc) return rc;
+      host_launches++;
+    } else if (cfg.evaluator == BB_EVAL_NET) {
+      if (!net) { set_error("evaluator is BB_EVAL_NET but no network is loaded"); return BB_ESTATE; }
+      int rc = net_forward(net, d.req_state, d.n_games, d.req_count, d.resp_policy, d.resp_value, stream);
+      if (rc) return rc;
+      host_launches++;
+    }
+    return BB_OK;
+  }
+  int read_flags() {
+    BB_CUDA(cudaMemcpyAsync(&host_flags[0], d.active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaMemcpyAsync(&host_flags[1], d.req_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int run(int* pending) override {
+    BB_CUDA(cudaSetDevice(cfg.device));
+    int rc;
+    if (cfg.evaluator == BB_EVAL_EXTERNAL) {
+      if ((rc = tick())) return rc;
+      if ((rc = read_flags())) return rc;
+      if (pending) *pending = host_flags[1];
+      return BB_OK;
+    }
+    const int burst = 8;
+    for (;;) {
+      for (int i = 0; i < burst; ++i)
+        if ((rc = tick())) return rc;
+      if ((rc = read_flags())) return rc;
+      if (host_flags[0] == 0) break;
+    }
+    if (pending) *pending = 0;
+    return BB_OK;
+  }
+
+  int root_stats(int kmax, int32_t* nch, int32_t* act, uint32_t* pl, float* cv, double* cp, uint32_t* rp, double* rv,
+                 int32_t* hp) override {
+    const size_t n = d.n_games, nk = n * kmax;
+    const size_t bytes = n * (4 + 4 + 8 + 4) + nk * (4 + 4 + 4 + 8) + 64;
+    int rc = ensure_scratch(bytes);
+    if (rc) return rc;
+    char* p = (char*)scratch;
+    double* d_cp = (double*)p; p += nk * 8;
+    double* d_rv = (double*)p; p += n * 8;
+    int32_t* d_act = (int32_t*)p; p += nk * 4;
+    uint32_t* d_pl = (uint32_t*)p; p += nk * 4;
+    float* d_cv = (float*)p; p += nk * 4;
+    int32_t* d_nch = (int32_t*)p; p += n * 4;
+    uint32_t* d_rp = (uint32_t*)p; p += n * 4;
+    int32_t* d_hp = (int32_t*)p; p += n * 4;
+    BB_CUDA(cudaMemsetAsync(scratch, 0, bytes, stream));
+    k_root_stats<G><<<warp_grid(), 128, 0, stream>>>(d, kmax, d_nch, d_act, d_pl, d_cv, d_cp, d_rp, d_rv, d_hp);
+    BB_CUDA(cudaGetLastError());
+#define D2H(dst, src, b) if (dst) BB_CUDA(cudaMemcpyAsync(dst, src, b, cudaMemcpyDeviceToHost, stream))
+    D2H(nch, d_nch, n * 4); D2H(act, d_act, nk * 4); D2H(pl, d_pl, nk * 4); D2H(cv, d_cv, nk * 4);
+    D2H(cp, d_cp, nk * 8); D2H(rp, d_rp, n * 4); D2H(rv, d_rv, n * 8); D2H(hp, d_hp, n * 4);
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int choose(double temp, const double* u_host, int32_t* actions_host) override {
+    if (temp != 1.0 && temp != 0.0) { set_error("device move choice supports temp 1 (sampled) and 0 (PUCT argmax); got %g", temp); return BB_EINVAL; }
+    const size_t n = d.n_games;
+    int rc = ensure_scratch(n * 16);
+    if (rc) return rc;
+    double* d_u = (double*)scratch;
+    int32_t* d_a = (int32_t*)((char*)scratch + n * 8);
+    if (temp == 1.0) {
+      if (!u_host) { set_error("temp 1 needs one uniform per slot"); return BB_EINVAL; }
+      BB_CUDA(cudaMemcpyAsync(d_u, u_host, n * 8, cudaMemcpyHostToDevice, stream));
+    }
+    k_choose<G><<<warp_grid(), 128, 0, stream>>>(d, temp == 1.0 ? 1 : 0, d_u, d_a);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaMemcpyAsync(actions_host, d_a, n * 4, cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int move_root(const int32_t* actions_host) override {
+    const size_t n = d.n_games;
+    int rc = ensure_scratch(n * 4);
+    if (rc) return rc;
+    BB_CUDA(cudaMemcpyAsync(scratch, actions_host, n * 4, cudaMemcpyHostToDevice, stream));
+    EngineDev<G> e = d;
+    e.autoplay = 0;
+    k_move_root<G><<<warp_grid(), 128, 0, stream>>>(e, (const int32_t*)scratch);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int states(void* out) override {
+    const size_t n = d.n_games;
+    int rc = ensure_scratch(n * sizeof(State));
+    if (rc) return rc;
+    k_gather_slots<G><<<grid_for(n, 128), 128, 0, stream>>>(d, (State*)scratch, nullptr, nullptr);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaMemcpyAsync(out, scratch, n * sizeof(State), cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int phases(int32_t* ph, int32_t* st) override {
+    const size_t n = d.n_games;
+    int rc = ensure_scratch(n * 8);
+    if (rc) return rc;
+    int32_t* a = (int32_t*)scratch;
+    int32_t* b = a + n;
+    k_gather_slots<G><<<grid_for(n, 128), 128, 0, stream>>>(d, nullptr, a, b);
+    BB_CUDA(cudaGetLastError());
+    if (ph) BB_CUDA(cudaMemcpyAsync(ph, a, n * 4, cudaMemcpyDeviceToHost, stream));
+    if (st) BB_CUDA(cudaMemcpyAsync(st, b, n * 4, cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int eval_pending(int32_t* n_host, const int32_t** slots, const void** sts) override {
+    int rc = read_flags();
+    if (rc) return rc;
+    *n_host = host_flags[1];
+    if (slots) *slots = d.req_slot;
+    if (sts) *sts = d.req_state;
+    return BB_OK;
+  }
+  int eval_fetch(void* sts, int32_t* slots) override {
+    int n = host_flags[1];
+    if (n <= 0) return BB_OK;
+    if (sts) BB_CUDA(cudaMemcpyAsync(sts, d.req_state, (size_t)n * sizeof(State), cudaMemcpyDeviceToDevice, stream));
+    if (slots) BB_CUDA(cudaMemcpyAsync(slots, d.req_slot, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int eval_submit(const float* pol, const float* val) override {
+    int n = host_flags[1];
+    if (n <= 0) return BB_OK;
+    BB_CUDA(cudaStreamSynchronize(stream));
+    BB_CUDA(cudaMemcpyAsync(d.resp_policy, pol, (size_t)n * G::A * 4, cudaMemcpyDeviceToDevice, stream));
+    BB_CUDA(cudaMemcpyAsync(d.resp_value, val, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    return BB_OK;
+  }
+
+  int selfplay(int play_limit, double temp, const double* u_host) override {
+    if (temp != 1.0 && temp != 0.0) { set_error("bb_selfplay_run supports temp 1 and 0 on the device; got %g", temp); return BB_EINVAL; }
+    if (cfg.evaluator == BB_EVAL_EXTERNAL) { set_error("bb_selfplay_run needs a device evaluator"); return BB_EINVAL; }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    if (temp == 1.0) {
+      if (!u_host) { set_error("temp 1 needs uniforms[n_games][max_plies]"); return BB_EINVAL; }
+      BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
+    }
+    int rc = reset(nullptr);
+    if (rc) return rc;
+    d.autoplay = 1;
+    d.play_limit = play_limit;
+    d.temp_mode = temp == 1.0 ? 1 : 0;
+    rc = begin_move(play_limit);
+    if (!rc) rc = run(nullptr);
+    d.autoplay = 0;
+    return rc;
+  }
+  int pool_cap() override { return (int)d.pool_cap; }
+  int records_export(int32_t* nm, int32_t* win, void* st, uint32_t* off, uint16_t* pa, uint32_t* pp, uint16_t* ch) override {
+    const size_t n = d.n_games, mp = d.max_plies;
+    D2H(nm, d.n_moves, n * 4); D2H(win, d.winners, n * 4); D2H(st, d.rec_states, n * (mp + 1) * sizeof(State));
+    D2H(off, d.rec_off, n * (mp + 2) * 4); D2H(pa, d.pool_actions, n * d.pool_cap * 2);
+    D2H(pp, d.pool_plays, n * d.pool_cap * 4); D2H(ch, d.chosen, n * mp * 2);
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+#undef D2H
+  int records_device(void** nm, void** win, void** st, void** off, void** pa, void** pp, void** ch) override {
+    if (nm) *nm = d.n_moves;
+    if (win) *win = d.winners;
+    if (st) *st = d.rec_states;
+    if (off) *off = d.rec_off;
+    if (pa) *pa = d.pool_actions;
+    if (pp) *pp = d.pool_plays;
+    if (ch) *ch = d.chosen;
+    return BB_OK;
+  }
+  int counters(bb_counters* out, int do_reset) override {
+    Counters c;
+    BB_CUDA(cudaStreamSynchronize(stream));
+    BB_CUDA(cudaMemcpy(&c, d.counters, sizeof c, cudaMemcpyDeviceToHost));
+    out->sims = c.sims; out->evals = c.evals; out->nodes = c.nodes; out->expansions = c.expansions;
+    out->select_steps = c.select_steps; out->moves = c.moves; out->games_done = c.games_done;
+    out->ticks = host_ticks; out->kernel_launches = host_launches;
+    if (do_reset) { BB_CUDA(cudaMemset(d.counters, 0, sizeof c)); host_ticks = host_launches = 0; }
+    return BB_OK;
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// C-ABI (include/bbengine.h)
+// ------------------------------------------------------------------------------------------
+#define BB_NEED(e) if (!(e)) { bb::set_error("null engine handle"); return BB_EINVAL; }
+
+extern "C" {
+
+int bb_engine_create(const bb_config* cfg, bb_engine** out) {
+  if (!cfg || !out) { set_error("bb_engine_create: null argument"); return BB_EINVAL; }
+  *out = nullptr;
+  if (cfg->n_games <= 0 || cfg->node_cap < 2 || cfg->max_plies <= 0) { set_error("n_games, node_cap, max_plies must be positive"); return BB_EINVAL; }
+  if (cfg->search != BB_FIXED && cfg->search != BB_DYNAMIC) { set_error("unknown search kind %d", cfg->search); return BB_EINVAL; }
+  if (cfg->search == BB_FIXED && cfg->max_depth <= 0) { set_error("MaxDepth for MCTS must be > 0."); return BB_EINVAL; }   // FixedMCTS.py:15-16
+  if (cfg->evaluator < BB_EVAL_KAT || cfg->evaluator > BB_EVAL_EXTERNAL) { set_error("unknown evaluator %d", cfg->evaluator); return BB_EINVAL; }
+  if (cfg->value_f64) { set_error("value_f64 accumulation (rollout evaluators, SURVEY.md 8f-2) is not built yet"); return BB_EINVAL; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { set_error("no CUDA device: the engine has no CPU fallback"); return BB_ECUDA; }
+  if (cfg->device < 0 || cfg->device >= ndev) { set_error("device %d out of range (%d devices)", cfg->device, ndev); return BB_EINVAL; }
+  int rc = BB_EINVAL;
+  BB_DISPATCH_GAME(cfg->game, {
+    auto* e = new EngineT<G>();
+    rc = e->init(*cfg);
+    if (rc != BB_OK) { delete e; return rc; }
+    *out = e;
+  });
+  return rc;
+}
+int bb_engine_destroy(bb_engine* e) { delete e; return BB_OK; }
+
+int bb_net_load(bb_engine* e, const bb_net_desc* d, const float* w, size_t n) { BB_NEED(e); return e->net_load(d, w, n); }
+int bb_net_forward(bb_engine* e, const void* st, int n, float* pol, float* val, void* stream) {
+  BB_NEED(e);
+  return e->net_fwd(st, n, pol, val, (cudaStream_t)stream);
+}
+int bb_search_reset(bb_engine* e, const void* states_dev) { BB_NEED(e); return e->reset(states_dev); }
+int bb_search_drop_root(bb_engine* e) { BB_NEED(e); return e->drop_root(); }
+int bb_search_begin_move(bb_engine* e, int play_limit) { BB_NEED(e); return e->begin_move(play_limit); }
+int bb_search_run(bb_engine* e, int* pending) { BB_NEED(e); return e->run(pending); }
+int bb_search_root_stats(bb_engine* e, int kmax, int32_t* nch, int32_t* act, uint32_t* pl, float* cv, double* cp,
+                         uint32_t* rp, double* rv, int32_t* hp) {
+  BB_NEED(e);
+  return e->root_stats(kmax, nch, act, pl, cv, cp, rp, rv, hp);
+}
+int bb_search_choose(bb_engine* e, double temp, const double* u, int32_t* a) { BB_NEED(e); return e->choose(temp, u, a); }
+int bb_search_move_root(bb_engine* e, const int32_t* a) { BB_NEED(e); return e->move_root(a); }
+int bb_search_states(bb_engine* e, void* out) { BB_NEED(e); return e->states(out); }
+int bb_search_phases(bb_engine* e, int32_t* ph, int32_t* st) { BB_NEED(e); return e->phases(ph, st); }
+int bb_eval_pending(bb_engine* e, int32_t* n, const int32_t** slots, const void** st) { BB_NEED(e); return e->eval_pending(n, slots, st); }
+int bb_eval_fetch(bb_engine* e, void* st, int32_t* slots) { BB_NEED(e); return e->eval_fetch(st, slots); }
+int bb_eval_submit(bb_engine* e, const float* pol, const float* val) { BB_NEED(e); return e->eval_submit(pol, val); }
+int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* u) { BB_NEED(e); return e->selfplay(play_limit, temp, u); }
+int bb_records_pool_cap(bb_engine* e) { BB_NEED(e); return e->pool_cap(); }
+int bb_records_export(bb_engine* e, int32_t* nm, int32_t* win, void* st, uint32_t* off, uint16_t* pa, uint32_t* pp, uint16_t* ch) {
+  BB_NEED(e);
+  return e->records_export(nm, win, st, off, pa, pp, ch);
+}
+int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off, void** pa, void** pp, void** ch) {
+  BB_NEED(e);
+  return e->records_device(nm, win, st, off, pa, pp, ch);
+}
+int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
+
+}  // extern "C"

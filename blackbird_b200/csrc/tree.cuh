@@ -1,0 +1,99 @@
+// Tree pool layout and the per-slot search state (SoA arenas in HBM; DESIGN.md "data layout").
+//
+// Per game slot g the arena holds node_cap nodes; node ids are arena-local u32.  Children of one
+// expansion are allocated contiguously (ascending action id), so PUCT select reads one coalesced
+// run of 16-byte NodeStat records and expansion writes one.  Child STATES are never stored: the
+// descent re-derives them by applying actions to the root state held in registers.
+//
+// Reference objects restated: MCTS.Node (MCTS.py:7-98) -> NodeHdr + NodeStat; MCTS.Root and the
+// _findLeaf locals (MCTS.py:120, DynamicMCTS.py:22-32) -> Slot.
+#pragma once
+#include "common.cuh"
+
+namespace bb {
+
+constexpr uint32_t NONE = 0xFFFFFFFFu;
+
+struct __align__(16) NodeStat {   // one per node, read by the PARENT's select
+  uint32_t plays;                 // Node.Plays
+  float value;                    // Node.Value, f32 accumulation
+  double prior;                   // Parent.Priors[action] (f64, A.9)
+};
+
+struct __align__(16) NodeHdr {
+  uint32_t parent;                // Node.Parent (NONE for the game's first root)
+  uint32_t child_base;            // first child id; NONE = Children is None
+  uint32_t meta;                  // action:12 | nchild:10 | player-1:1 | has_value:1
+  float eval;                     // raw network value of this state (cached getEvaluation)
+};
+constexpr uint32_t META_HAS_VALUE = 1u << 23;
+__host__ __device__ __forceinline__ uint32_t meta_pack(int action, int nchild, int player, bool has_value) {
+  return (uint32_t)action | ((uint32_t)nchild << 12) | ((uint32_t)(player - 1) << 22) | (has_value ? META_HAS_VALUE : 0u);
+}
+__host__ __device__ __forceinline__ int meta_action(uint32_t m) { return m & 0xFFF; }
+__host__ __device__ __forceinline__ int meta_nchild(uint32_t m) { return (m >> 12) & 0x3FF; }
+__host__ __device__ __forceinline__ int meta_player(uint32_t m) { return 1 + ((m >> 22) & 1); }
+
+template <class G>
+struct Slot {
+  typename G::State root_state;   // Root.State
+  typename G::State cur_state;    // state of `cur` during a descent
+  uint32_t root, cur;             // NONE root = "Root is None"
+  int32_t depth, last_action;     // _findLeaf locals
+  uint32_t n_nodes;               // arena bump pointer
+  uint32_t end_plays;             // endPlays (MCTS.py:297)
+  int32_t phase, status;          // BB_PH_*, BB_* error code
+  int32_t ply;                    // moves played
+  int32_t root_parent_player;     // Player of Root.Parent.State (0: Root has no parent), A.13
+  int32_t winner;                 // BB_WIN_* after GAME_OVER
+  uint32_t req_idx;               // index of the open evaluator request
+  uint32_t pool_used;             // record pool bump pointer
+  int32_t pad;
+};
+
+// numpy pairwise-sum plan for a dense vector of length A, built on the host.
+constexpr int PW_MAX_LEAVES = 64;
+constexpr int PW_MAX_OPS = 2 * PW_MAX_LEAVES;
+struct PairwisePlan {
+  int n_leaves, n_ops;
+  int16_t leaf_lo[PW_MAX_LEAVES], leaf_n[PW_MAX_LEAVES];
+  int8_t ops[PW_MAX_OPS];         // >=0: push leaf sum; -1: add the two top entries
+};
+
+struct Counters {                 // mirrors bb_counters
+  unsigned long long sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
+};
+
+template <class G>
+struct EngineDev {                // passed to kernels by value
+  Slot<G>* slots;
+  NodeHdr* hdr;
+  NodeStat* stat;
+  int n_games;
+  uint32_t node_cap;
+  int search, max_depth, max_plies;
+  double c;                       // ExplorationRate
+  // evaluator mailbox
+  int* req_count;
+  int* req_slot;
+  typename G::State* req_state;
+  float* resp_policy;             // [n_games][A], indexed by request
+  float* resp_value;
+  // self-play
+  int autoplay;                   // 1: choose / move root / end games on the device
+  int play_limit;
+  int temp_mode;                  // 1: temp == 1 (sample), 0: temp == 0 (PUCT argmax)
+  const double* uniforms;         // [n_games][max_plies]
+  typename G::State* rec_states;  // [n_games][max_plies+1]
+  uint32_t* rec_off;              // [n_games][max_plies+2]
+  uint16_t* pool_actions;         // [n_games][pool_cap]
+  uint32_t* pool_plays;
+  uint16_t* chosen;               // [n_games][max_plies]
+  int32_t* n_moves;
+  int32_t* winners;
+  uint32_t pool_cap;
+  int* active;                    // slots still searching after this tick
+  Counters* counters;
+};
+
+}  // namespace bb

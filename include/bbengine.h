@@ -1,0 +1,164 @@
+/* bbengine.h -- C-ABI of the B200-native BlackBird self-play engine (libbbengine.so).
+ *
+ * The reference (ZackAttack614/BlackBird) is pure Python with no FFI layer; its "operator API"
+ * for the self-play path is the duck-typed Python surface of GameState / MCTS / Model
+ * (SURVEY.md 8b).  Each entry point below names the reference interface it replaces
+ * (file:line under /root/reference/src).  The Python mirror in blackbird_b200/ binds these
+ * with ctypes (INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions: plain C, opaque handle, int status (0 = OK, <0 = error, bb_last_error() gives
+ * text).  Pointers named *_dev are CUDA device pointers (e.g. torch.Tensor.data_ptr()),
+ * *_host are host pointers.  `stream` is a cudaStream_t passed as void* (NULL = default
+ * stream).  One engine = one GPU; an engine is not thread-safe, distinct engines are.
+ */
+#ifndef BBENGINE_H
+#define BBENGINE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { BB_OK = 0, BB_EINVAL = -1, BB_EILLEGAL = -2, BB_EASSERT = -3, BB_ENOMEM = -4,
+       BB_ECUDA = -5, BB_ESTATE = -6 };
+enum { BB_TICTACTOE = 0, BB_CONNECT4 = 1, BB_DRAGONCHESS = 2 };   /* TicTacToe.py / Connect4.py / DragonChess.py */
+enum { BB_FIXED = 0, BB_DYNAMIC = 1 };                            /* FixedMCTS.py:21-34 / DynamicMCTS.py:14-34 */
+enum { BB_EVAL_KAT = 0,        /* integer evaluator of SURVEY.md Appendix B.2 (parity vehicle) */
+       BB_EVAL_NET = 1,        /* built-in policy-value network (NetworkFactory.py:22-183)     */
+       BB_EVAL_EXTERNAL = 2 }; /* caller serves requests (bb_eval_pending / bb_eval_submit)    */
+/* winner codes: None, python int 0 (draw), 1.0, 2.0, np.float64(0.0) */
+enum { BB_WIN_NONE = -1, BB_WIN_DRAW = 0, BB_WIN_P1 = 1, BB_WIN_P2 = 2, BB_WIN_FLOAT0 = 3 };
+/* per-game phases reported by bb_search_phases */
+enum { BB_PH_IDLE = 0, BB_PH_RUN = 1, BB_PH_WAIT_EXPAND = 2, BB_PH_WAIT_LEAF = 3,
+       BB_PH_MOVE_READY = 4, BB_PH_GAME_OVER = 5, BB_PH_ERROR = 6 };
+
+const char* bb_last_error(void);
+int bb_abi_version(void);
+
+/* ---- game description -------------------------------------------------------------------- */
+int bb_game_state_bytes(int game);     /* packed state size: 4 / 16 / 40                      */
+int bb_game_actions(int game);         /* BoardState.LegalMoves: 9 / 7 / 4032                 */
+int bb_game_plane_shape(int game, int* h, int* w, int* c);   /* AsInputArray() is [1,h,w,c]   */
+
+/* ---- batched rule kernels over n packed states (all pointers device) ---------------------- */
+/* BoardState.__init__ (TicTacToe.py:18-21, Connect4.py:19-22, DragonChess.py:38-60) */
+int bb_game_init(int game, void* states_dev, int n, void* stream);
+/* BoardState.LegalActions -> float64[n][A] of 0/1 (TicTacToe.py:29-36, Connect4.py:30-36, DragonChess.py:78-106) */
+int bb_game_legal(int game, const void* states_dev, int n, double* out_dev, void* stream);
+/* BoardState.ApplyAction; ok_dev[i]=0 where the reference raises ValueError('Tried to make an
+ * illegal move.') and the state is left untouched (TicTacToe.py:41-48, Connect4.py:41-53, DragonChess.py:127-214) */
+int bb_game_apply(int game, void* states_dev, const int32_t* actions_dev, int n, uint8_t* ok_dev, void* stream);
+/* BoardState.Winner(prevAction): prev_actions_dev NULL or entry <0 means None
+ * (TicTacToe.py:57-105, Connect4.py:62-108, DragonChess.py:161-167) */
+int bb_game_winner(int game, const void* states_dev, const int32_t* prev_actions_dev, int n, int32_t* out_dev, void* stream);
+/* BoardState.AsInputArray -> int8[n][h*w*c] (TicTacToe.py:50-55, Connect4.py:55-60, DragonChess.py:111-125) */
+int bb_game_planes(int game, const void* states_dev, int n, int8_t* out_dev, void* stream);
+/* BoardState.__eq__ (TicTacToe.py:132-135, Connect4.py:129-132, DragonChess.py:226-237) */
+int bb_game_equal(int game, const void* a_dev, const void* b_dev, int n, uint8_t* out_dev, void* stream);
+/* Build packed states from the reference's array form: cells int8[n][h*w] (0/1/2 for the line
+ * games; signed piece codes for DragonChess), player[n], prev[n] (0=None), castle[n] bit0..3 */
+int bb_game_pack(int game, const int8_t* cells_dev, const uint8_t* player_dev, const uint8_t* prev_dev,
+                 const uint8_t* castle_dev, int n, void* states_dev, void* stream);
+/* Inverse of bb_game_pack (any output pointer may be NULL). */
+int bb_game_unpack(int game, const void* states_dev, int n, int8_t* cells_dev, uint8_t* player_dev,
+                   uint8_t* prev_dev, uint8_t* castle_dev, void* stream);
+
+/* ---- engine ------------------------------------------------------------------------------ */
+typedef struct bb_engine bb_engine;
+
+typedef struct bb_config {
+  int32_t game;              /* BB_TICTACTOE | BB_CONNECT4 | BB_DRAGONCHESS                      */
+  int32_t search;            /* BB_FIXED | BB_DYNAMIC                                            */
+  int32_t max_depth;         /* FixedMCTS maxDepth (FixedMCTS.py:9,15-16); ignored for dynamic   */
+  int32_t evaluator;         /* BB_EVAL_*                                                        */
+  int32_t n_games;           /* concurrent game slots on this GPU                                */
+  int32_t node_cap;          /* tree nodes per game arena (overflow -> BB_ENOMEM, never silent)  */
+  int32_t max_plies;         /* record slots per game; engine-side ply cap      */
+  int32_t device;            /* CUDA device ordinal                                              */
+  double exploration_rate;   /* MCTS.ExplorationRate (MCTS.py:119)                               */
+  int32_t value_f64;         /* 0: Node.Value accumulates in f32 (Model path, A.9); 1: f64       */
+  int32_t reserved[7];
+} bb_config;
+
+int bb_engine_create(const bb_config* cfg, bb_engine** out);
+int bb_engine_destroy(bb_engine* e);
+
+/* ---- built-in network (NetworkFactory.py:22-183 forward, Network.py:48-64) ---------------- */
+typedef struct bb_net_desc {
+  int32_t blocks, filters, dense;   /* parameters_template.yaml:12-16 */
+  int32_t cin;                      /* input planes (3 / 3 / 17)      */
+  float epsilon;                    /* policy noise weight (A.17); 0 = deterministic */
+  float alpha;
+  uint64_t noise_seed;
+  int32_t reserved[4];
+} bb_net_desc;
+/* weights_host: flat fp32 in the order documented in DESIGN.md ("weight layout"). */
+int bb_net_load(bb_engine* e, const bb_net_desc* d, const float* weights_host, size_t n_floats);
+/* Network.getPolicy + getEvaluation for n packed states: policy f32[n][A] (softmax, noise,
+ * renormalised), value f32[n] (tanh). */
+int bb_net_forward(bb_engine* e, const void* states_dev, int n, float* policy_dev, float* value_dev, void* stream);
+/* Appendix B.2 integer evaluator, same signature (parity vehicle). */
+int bb_kat_forward(int game, const void* states_dev, int n, float* policy_dev, float* value_dev, void* stream);
+
+/* ---- search (MCTS.py:101-399) ------------------------------------------------------------ */
+/* Start games: every slot gets the initial position and no Root (Model.Game() + DropRoot,
+ * Blackbird.py:241-244).  states_dev != NULL starts from those packed states instead. */
+int bb_search_reset(bb_engine* e, const void* states_dev);
+/* MCTS.DropRoot (MCTS.py:141-144) for all slots. */
+int bb_search_drop_root(bb_engine* e);
+/* FindMove's search half (MCTS.py:184-195): create Root if None, then run play_limit
+ * simulations per slot (Root.Plays grows by exactly play_limit, MCTS.py:297-299).
+ * Runs ticks (advance kernel + evaluator) until every slot is MOVE_READY.  With
+ * BB_EVAL_EXTERNAL it returns after one advance with *pending = number of open requests. */
+int bb_search_begin_move(bb_engine* e, int play_limit);
+int bb_search_run(bb_engine* e, int* pending);
+/* Root statistics after the search: Root.ChildPlays() as sparse (action,plays) lists padded to
+ * kmax per slot, Root.Plays, Root.Value (as double), and child count.
+ * (MCTS.py:43-98; used by FindMove's return value MCTS.py:198-199) */
+int bb_search_root_stats(bb_engine* e, int kmax, int32_t* n_children_host, int32_t* actions_host,
+                         uint32_t* plays_host, float* child_value_host, double* child_prior_host,
+                         uint32_t* root_plays_host, double* root_value_host, int32_t* root_has_parent_host);
+/* _selectAction(exploring=False) (MCTS.py:335-338) on the device for temp==1 (uniforms: one
+ * double per slot = RandomState.random_sample()) or temp==0 (PUCT argmax, A.15).  actions out. */
+int bb_search_choose(bb_engine* e, double temp, const double* uniforms_host, int32_t* actions_host);
+/* state = nextState; MoveRoot(state) (Blackbird.py:249-251, MCTS.py:260-282), by action. */
+int bb_search_move_root(bb_engine* e, const int32_t* actions_host);
+/* current root states / phases / status codes per slot */
+int bb_search_states(bb_engine* e, void* states_host);
+int bb_search_phases(bb_engine* e, int32_t* phases_host, int32_t* status_host);
+/* External evaluator (Model.GetPriors / SampleValue overrides, MCTS.py:346-383): list open
+ * requests (slot ids + packed states, device pointers valid until submit), then answer them. */
+int bb_eval_pending(bb_engine* e, int32_t* n_host, const int32_t** slots_dev, const void** states_dev);
+/* Copy the open requests (packed states, slot ids) into caller-owned device buffers. */
+int bb_eval_fetch(bb_engine* e, void* states_out_dev, int32_t* slots_out_dev);
+int bb_eval_submit(bb_engine* e, const float* policy_dev, const float* value_dev);
+
+/* ---- whole self-play (Blackbird.GenerateTrainingSamples, Blackbird.py:219-268) ----------- */
+/* Plays every slot's game to the end on the device: play_limit simulations per move, move
+ * choice at temp 1 from uniforms_host[n_games][max_plies] (one double per move, A.15), root
+ * motion, Winner(None) after every move, records kept on the device. */
+int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* uniforms_host);
+/* Fixed-stride record export (host buffers).  Per slot: n_moves, winner code (BB_WIN_*; NONE =
+ * truncated by max_plies), and per record r in [0, n_moves] (the last one is the terminal
+ * record): packed state, player to move, and sparse child plays (offsets into a per-slot pool).
+ * Sizes: states [n_games][max_plies+1][state_bytes]; rec_off [n_games][max_plies+2];
+ * pool_actions/pool_plays [n_games][pool_cap].  Use bb_records_pool_cap() to size. */
+int bb_records_pool_cap(bb_engine* e);
+int bb_records_export(bb_engine* e, int32_t* n_moves_host, int32_t* winner_host, void* states_host,
+                      uint32_t* rec_off_host, uint16_t* pool_actions_host, uint32_t* pool_plays_host,
+                      uint16_t* chosen_host);
+/* Same buffers as device pointers (for the NCCL all-gather of records). */
+int bb_records_device(bb_engine* e, void** n_moves_dev, void** winner_dev, void** states_dev,
+                      void** rec_off_dev, void** pool_actions_dev, void** pool_plays_dev, void** chosen_dev);
+
+/* ---- counters (sims, evals, nodes, depth, expansions, launches) ------------- */
+typedef struct bb_counters {
+  uint64_t sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
+} bb_counters;
+int bb_counters_read(bb_engine* e, bb_counters* out, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

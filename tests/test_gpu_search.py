@@ -1,0 +1,150 @@
+"""GPU: tree search and self-play (through the C-ABI) vs the reference's golden vectors and vs
+the numpy oracle -- visit counts, chosen moves, win-rate bits and record bytes, bit-exact."""
+import hashlib
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+from oracle import search_np, selfplay_np  # noqa: E402
+from oracle.rules_np import GAMES  # noqa: E402
+
+
+@pytest.fixture(scope='module')
+def mods():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    from blackbird_b200 import engine, records
+    return engine, records
+
+
+def step_move(eng, play_limit, u):
+    """FindMove + MoveRoot on every slot; returns per-slot dicts like the golden rows."""
+    eng.begin_move(play_limit)
+    eng.run()
+    eng.check_status()
+    st = eng.root_stats()
+    acts = eng.choose(1.0, u)
+    eng.move_root(acts)
+    rows = []
+    for g in range(eng.n_games):
+        k = int(st['n_children'][g])
+        plays = np.zeros(eng.A)
+        plays[st['actions'][g, :k]] = st['plays'][g, :k]
+        if st['root_has_parent'][g]:
+            wr = (np.float32(st['root_value'][g]) / np.float32(st['root_plays'][g])).tobytes().hex()
+        else:
+            wr = 0
+        total = sum(plays)
+        probs = plays / total if total > 0 else np.zeros(eng.A)
+        nz = np.flatnonzero(plays)
+        rows.append({'plays_idx': nz.tolist(), 'plays': plays[nz].astype(int).tolist(), 'action': int(acts[g]),
+                     'winrate': wr, 'root_plays': int(st['root_plays'][g]),
+                     'probs_sha': hashlib.sha256(probs.tobytes()).hexdigest()[:16]})
+    return rows
+
+
+def test_mcts_goldens(mods, golden):
+    """Appendix B.2: reference Blackbird.Model + integer evaluator, np.random.seed(0), temp 1."""
+    engine, _ = mods
+    for case in golden('mcts_kat.json'):
+        eng = engine.Engine(case['game'], case['kind'], n_games=1, evaluator='kat', play_limit_hint=case['playLimit'])
+        u = np.random.RandomState(case['seed']).random_sample(len(case['moves']))
+        for i, want in enumerate(case['moves']):
+            got = step_move(eng, case['playLimit'], u[i:i + 1])[0]
+            assert got == want, (case['game'], case['kind'], i, got, want)
+        eng.close()
+
+
+def test_tie_break_kat(mods):
+    """Uniform priors + constant value 0.5 (SURVEY.md B.2 footnote): child plays
+    [29,29,29,28,28,28,28] for Connect4 dynamic, 200 sims -- served by the external evaluator."""
+    engine, _ = mods
+    eng = engine.Engine('Connect4', 'dynamic', n_games=1, evaluator='external', play_limit_hint=200)
+    eng.begin_move(200)
+    while True:
+        n = eng.run()
+        if n == 0:
+            break
+        k, states, _ = eng.eval_pending()
+        pol = torch.full((k, 7), 1.0 / 7, dtype=torch.float32, device='cuda')
+        val = torch.zeros((k,), dtype=torch.float32, device='cuda')      # (0+1)*0.5 = 0.5
+        eng.eval_submit(pol, val)
+    st = eng.root_stats()
+    assert st['plays'][0, :7].tolist() == [29, 29, 29, 28, 28, 28, 28]
+
+
+@pytest.mark.parametrize('game,kind,P,n_games', [
+    ('Connect4', 'dynamic', 120, 24), ('Connect4', 'fixed', 40, 24),
+    ('TicTacToe', 'dynamic', 60, 32), ('TicTacToe', 'fixed', 25, 32),
+    ('DragonChess', 'dynamic', 16, 2), ('DragonChess', 'fixed', 4, 2),
+])
+def test_selfplay_vs_oracle(mods, game, kind, P, n_games):
+    """Whole games on the device (bb_selfplay_run) vs the oracle's GenerateTrainingSamples
+    restatement, per-game RandomState(1000+g) move sampling: record bytes, winners, moves."""
+    engine, records = mods
+    cap = 12 if game == 'DragonChess' else None
+    eng = engine.Engine(game, kind, n_games=n_games, evaluator='kat', play_limit_hint=P, max_plies=cap)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(n_games)])
+    eng.selfplay(P, 1.0, u)
+    got = records.build_records(eng)
+    raw = eng.records_raw()
+    tot_sims = 0
+    for g in range(n_games):
+        s = search_np.NetSearch(search_np.KatEvaluator(eng.A), kind, maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        want, winner, trace = selfplay_np.play_game(s, GAMES[game], 1, max_plies=cap)
+        recs, wcode, n_moves = got[g]
+        assert n_moves == len(trace)
+        assert raw['chosen'][g, :n_moves].tolist() == [t[1] for t in trace], g
+        assert wcode == (-1 if winner is None else int(winner))
+        assert recs == want, (game, kind, g)
+        tot_sims += s.Stats['sims']
+    c = eng.counters()
+    assert c['sims'] == tot_sims and c['games_done'] == n_games
+    eng.close()
+
+
+def test_selfplay_record_goldens(mods, golden):
+    """Records of whole games produced by the UNMODIFIED reference (GenerateTrainingSamples)."""
+    engine, records = mods
+    for case in golden('records.json'):
+        eng = engine.Engine(case['game'], case['kind'], n_games=1, evaluator='kat', play_limit_hint=case['playLimit'])
+        u = np.random.RandomState(case['seed']).random_sample(eng.max_plies)[None]
+        eng.selfplay(case['playLimit'], 1.0, u)
+        recs = records.build_records(eng)[0][0]
+        assert [r.hex() for r in recs] == case['records'], (case['game'], case['kind'], case['seed'])
+        eng.close()
+
+
+def test_full_size_properties(mods):
+    """BASELINE config 2 shape at reduced sims (Connect4 fixed, 4096 games): size-independent
+    properties -- every game ends, visit counts per record sum to the simulations spent on that
+    move, records replay legally to the recorded terminal state, slot 0 matches the oracle."""
+    engine, records = mods
+    G, P = 4096, 16
+    eng = engine.Engine('Connect4', 'fixed', n_games=G, evaluator='kat', play_limit_hint=P)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
+    eng.selfplay(P, 1.0, u)
+    raw = eng.records_raw()
+    assert (raw['winner'] >= 0).all() and (raw['n_moves'] >= 7).all() and (raw['n_moves'] <= 42).all()
+    c = eng.counters()
+    assert c['sims'] == int(raw['n_moves'].sum()) * P and c['games_done'] == G
+    for g in range(0, G, 97):
+        st = engine.init_states('Connect4', 1)
+        for r in range(int(raw['n_moves'][g])):
+            lo, hi = raw['rec_off'][g, r], raw['rec_off'][g, r + 1]
+            visits = int(raw['pool_plays'][g, lo:hi].sum())
+            assert visits >= P
+            a = int(raw['chosen'][g, r])
+            assert raw['pool_plays'][g, lo:hi][raw['pool_actions'][g, lo:hi] == a][0] > 0
+            assert np.array_equal(st.cpu().numpy()[0], raw['states'][g, r])
+            assert int(engine.apply('Connect4', st, torch.tensor([a])).item()) == 1
+        assert int(engine.winner('Connect4', st).item()) == int(raw['winner'][g])
+    s = search_np.NetSearch(search_np.KatEvaluator(7), 'fixed', maxDepth=10, explorationRate=0.85, playLimit=P,
+                            rng=np.random.RandomState(1000))
+    want, _, _ = selfplay_np.play_game(s, GAMES['Connect4'], 1)
+    assert records.build_records(eng, raw)[0][0] == want
+    eng.close()
