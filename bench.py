@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py -- Connect4 MCTS simulations/s (BASELINE.json metric) on N B200s of one node.
+
+Workload (N=1): BASELINE.json configs[1] -- Connect4, FixedMCTS maxDepth 10, 800 simulations per
+move, 4096 concurrent games per GPU, template network (blocks 4, filters 16, dense 16), random-init
+weights, synthetic data (games start from the empty board; move sampling from per-game uniforms).
+
+A "step" is one move round: every game slot runs one FindMove (800 simulations, every simulation a
+PUCT descent + lazy network evaluation + backup) and plays the move; finished games restart in
+place so all slots stay busy (steady state).  `value` = simulations of all ranks / device time
+(max over ranks), inputs resident in HBM.  `e2e` = the same metric through the C-ABI self-play
+call with HOST buffers: uniforms H2D, G whole games to completion, raw records D2H, all inside
+the timed region.  `--impl reference` times the CPU port of the reference (oracle/) on the host
+cores instead.  See DESIGN.md "measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GAME, SEARCH, MAX_DEPTH, C_PUCT = 'Connect4', 'fixed', 10, 0.85
+NET = dict(blocks=4, filters=16, dense=16)
+METRIC, UNIT = 'connect4_mcts_simulations_per_sec', 'sims/s'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=6)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--games', type=int, default=4096, help='concurrent games per GPU')
+    ap.add_argument('--sims', type=int, default=800, help='simulations per move (playLimit)')
+    ap.add_argument('--epsilon', type=float, default=0.0, help='policy noise weight (template: 0.3)')
+    ap.add_argument('--cpu-seconds', type=float, default=12.0, help='CPU baseline sample length')
+    ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-cpu', action='store_true')
+    return ap.parse_args()
+
+
+def config_dict(args, n_gpus):
+    return {'workload': 'Connect4 FixedMCTS(maxDepth 10, c 0.85) self-play, %d sims/move, %d concurrent games/GPU, '
+                        'network blocks4/filters16/dense16 (BASELINE configs[1])' % (args.sims, args.games),
+            'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS', 'max_depth': MAX_DEPTH,
+            'step': 'one move round (FindMove+MoveRoot) of every game slot, finished games restart in place',
+            'epsilon': args.epsilon, 'parallelism': 'games sharded over %d GPU(s), no data-path collective' % n_gpus,
+            'l2_policy': 'working set (tree pool, GBs) larger than L2; no flush needed'}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference (Blackbird.GenerateTrainingSamples -> FindMove ...)
+# ---------------------------------------------------------------------------------------------
+def _cpu_worker(task):
+    seed, seconds, sims, epsilon = task
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(1)
+    except Exception:
+        pass
+    import numpy as np
+    from oracle import network_np, search_np
+    from oracle.rules_np import GAMES
+    w = network_np.init_weights(3, 7, seed=0, **NET)
+    ev = network_np.NetEvaluator(w, eps=epsilon)
+    s = search_np.NetSearch(ev, SEARCH, maxDepth=MAX_DEPTH, explorationRate=C_PUCT, playLimit=sims,
+                            rng=np.random.RandomState(seed))
+    t0 = time.time()
+    end = t0 + seconds
+    games = 0
+    while time.time() < end:
+        state = GAMES[GAME]()
+        s.DropRoot()
+        winner = None
+        while winner is None and time.time() < end:
+            state, _, _ = s.FindMove(state, 1, moveTime=max(end - time.time(), 1e-3), playLimit=sims)
+            s.MoveRoot(state)
+            winner = state.Winner(None)
+        games += winner is not None
+    return s.Stats['sims'], games, time.time() - t0
+
+
+def cpu_sample(seconds, sims, epsilon, cores=None):
+    import multiprocessing as mp
+    cores = cores or os.cpu_count() or 1
+    ctx = mp.get_context('fork')
+    with ctx.Pool(cores) as pool:
+        res = pool.map(_cpu_worker, [(1000 + i, seconds, sims, epsilon) for i in range(cores)])
+    total = sum(r[0] for r in res)
+    wall = max(r[2] for r in res)
+    return total / wall, sum(r[1] for r in res), cores, wall
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    seconds = max(2.0, min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_sample(min(seconds, 2.0), args.sims, args.epsilon)
+    vals, tot_t = [], 0.0
+    for _ in range(args.steps):
+        v, _, cores, wall = cpu_sample(seconds, args.sims, args.epsilon)
+        vals.append(v)
+        tot_t += wall
+    value = sum(vals) / len(vals)
+    sample = '%d worker processes x %.0f s of Connect4 FixedMCTS self-play per step (oracle port, numpy fp32 network at batch 1)' % (cores, seconds)
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': 1e3 * tot_t / max(1, args.steps), 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(args, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0}))
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    Q = 'index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,' \
+        'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits'],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        sm = sorted(float(r[1]) for r in self.rows if r[1].replace('.', '').isdigit())
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[5:9]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        mx = max([float(r[2]) for r in self.rows if r[2].replace('.', '').isdigit()] or [0.0])
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx or None, 'reasons': sorted(reasons),
+                'samples': len(self.rows)}
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    rank, world = int(os.environ.get('RANK', '0')), int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if local == 0:
+        ge.build()
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        torch.cuda.set_device(local)
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+        dist.barrier()
+    else:
+        torch.cuda.set_device(local)
+    from blackbird_b200 import netinit
+    from blackbird_b200.engine import Engine, plane_shape
+
+    G, P = args.games, args.sims
+    h, w, cin = plane_shape(GAME)
+    eng = Engine(GAME, SEARCH, n_games=G, max_depth=MAX_DEPTH, exploration_rate=C_PUCT, evaluator='net',
+                 play_limit_hint=P, device=local)
+    weights = netinit.random_weights(cin, 7, seed=0, **NET)
+    eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=args.epsilon, alpha=0.2, seed=rank)
+    # per-game move-sampling uniforms, game id = rank*G + slot (records identical for any GPU count)
+    uniforms = np.stack([np.random.RandomState(1000 + rank * G + g).random_sample(eng.max_plies) for g in range(G)])
+    stream = eng.stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    eng.reset()
+    eng.step(1, P, 1.0, uniforms)                    # uploads the uniform table; first warm-up step
+    for _ in range(max(0, args.warmup - 1)):
+        eng.step(1, P)
+    eng.check_status()
+    c0 = eng.counters(reset=True)
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        eng.step(1, P)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.summary()
+    eng.check_status()
+    c = eng.counters(reset=True)
+    t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+    cnt = torch.tensor([c['sims'], c['evals'], c['nodes'], c['expansions'], c['select_steps'], c['games_done'],
+                        c['kernel_launches'], c['moves'], c['ticks']], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms = float(t.item())
+    sims, evals, nodes, exps, sel, games_done, launches, moves, ticks = [float(x) for x in cnt.tolist()]
+    value = sims / (ms * 1e-3)
+
+    # kernel shares: one profiled step (CUDA events around every advance / network launch)
+    eng.profile(True, 16384)
+    eng.step(1, P)
+    prof = eng.profile_read()
+    eng.profile(False)
+    cp = eng.counters(reset=True)
+    flops = netinit.flops_per_eval(h, w, cin, 7, **NET)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        pass
+    tensor_peak = float(peaks.get('bf16_tflops_sustained', 1400.0))
+    hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
+    peak_src = 'measured (MEASURED_PEAKS.json, sustained bf16)' if peaks else 'fallback'
+    net_tflops = cp['evals'] * flops / (prof['eval_ms'] * 1e-3) / 1e12 if prof['eval_ms'] > 0 else 0.0
+    # tree traffic model of SURVEY.md 8d with measured d, k, n_exp (Connect4: S folded out -- child states are not stored)
+    d_bar = cp['select_steps'] / max(1, cp['sims'])
+    nexp = cp['expansions'] / max(1, cp['sims'])
+    k_bar = cp['nodes'] / max(1, cp['expansions'])
+    b_sim = d_bar * (16 * k_bar + 16) + nexp * k_bar * 32 + (cp['evals'] / max(1, cp['sims'])) * (16 + 4 * 8) + 16 * (d_bar + 1)
+    tree_gbs = cp['sims'] * b_sim / (prof['advance_ms'] * 1e-3) / 1e9 if prof['advance_ms'] > 0 else 0.0
+    roofline = {'bound': 'tensor', 'kernel': 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks'])),
+                'achieved': net_tflops, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / tensor_peak,
+                'traffic': None, 'peak_source': peak_src, 'flops_per_eval': flops,
+                'launch_ms_avg': prof['eval_ms'] / max(1, prof['ticks']),
+                'step_share': prof['eval_ms'] / max(1e-9, prof['eval_ms'] + prof['advance_ms'])}
+    roofline_tree = {'bound': 'hbm', 'kernel': 'k_advance<Connect4> (select/expand/backup)', 'achieved': tree_gbs, 'peak': hbm_peak,
+                     'unit': 'GB/s', 'frac': tree_gbs / hbm_peak, 'bytes_per_sim_model': b_sim, 'mean_depth': d_bar,
+                     'expansions_per_sim': nexp, 'children_per_expansion': k_bar, 'evals_per_sim': cp['evals'] / max(1, cp['sims']),
+                     'launch_ms_avg': prof['advance_ms'] / max(1, prof['ticks'])}
+
+    # e2e: whole games through the C-ABI call with host buffers (H2D uniforms, D2H records inside)
+    e2e = None
+    if not args.no_e2e:
+        barrier()
+        pinned = torch.from_numpy(uniforms).pin_memory()
+        t0 = time.perf_counter()
+        eng.selfplay(P, 1.0, pinned.numpy())
+        raw = eng.records_raw()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        ce = eng.counters(reset=True)
+        tt = torch.tensor([dt], dtype=torch.float64, device='cuda')
+        ss = torch.tensor([ce['sims'], ce['games_done']], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+        d2h = sum(v.nbytes for v in raw.values())
+        e2e = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'h2d_bytes_per_step': int(uniforms.nbytes),
+               'd2h_bytes_per_step': int(d2h), 'games_per_sec': float(ss[1].item()) / float(tt.item()),
+               'seconds': float(tt.item()), 'what': 'bb_selfplay_run + bb_records_export: %d whole games/GPU to completion' % G,
+               'mean_moves_per_game': float(raw['n_moves'].mean())}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, games, cores, wall = cpu_sample(args.cpu_seconds, P, args.epsilon)
+        cpu = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+               'sample': '%d worker processes x %.0f s of the same workload (oracle port of the reference, numpy fp32 network at batch 1)' % (cores, wall)}
+
+    if rank == 0:
+        print(json.dumps({
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+            'ms_per_step': ms / max(1, args.steps), 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(args, world),
+            'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
+            'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
+            'roofline': roofline, 'roofline_tree': roofline_tree, 'cpu_baseline': cpu, 'e2e': e2e,
+            'gpu_launches': int(launches), 'clocks': clocks}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -67,6 +67,10 @@ SIGNATURES = {
     'bb_eval_fetch': (I, [VP, VP, VP]),
     'bb_eval_submit': (I, [VP, VP, VP]),
     'bb_selfplay_run': (I, [VP, I, C.c_double, VP]),
+    'bb_selfplay_step': (I, [VP, I, I, C.c_double, VP]),
+    'bb_engine_stream': (VP, [VP]),
+    'bb_profile_enable': (I, [VP, I, I]),
+    'bb_profile_read': (I, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(I)]),
     'bb_records_pool_cap': (I, [VP]),
     'bb_records_export': (I, [VP, VP, VP, VP, VP, VP, VP, VP]),
     'bb_records_device': (I, [VP] + [C.POINTER(VP)] * 7),

@@ -1,8 +1,451 @@
-// placeholder until the network kernel lands (next commit): keeps the library linkable.
+// Policy-value network forward (NetworkFactory.py:22-183 as run by Network.getPolicy /
+// getEvaluation, Network.py:48-64), fp32 SIMT version: the whole tower for a tile of positions
+// stays in shared memory (weights resident, activations ping-pong), input planes are decoded
+// from the packed game state in the kernel, BN is folded into the convolutions on the host, the
+// heads (1x1 conv -> BN -> ReLU -> per-cell dense -> sum over H,W) are reduced in a fixed order
+// so results are run-to-run deterministic.
+//
+// Persistent grid (one CTA per SM), 256 threads, 2 output cells x 16 filters per thread.
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
 #include "common.cuh"
+
 namespace bb {
-struct NetDev { int game; };
-int net_create(int, const bb_net_desc*, const float*, size_t, NetDev**) { set_error("network kernel not built yet"); return BB_ESTATE; }
-void net_destroy(NetDev* n) { delete n; }
-int net_forward(NetDev*, const void*, int, const int*, float*, float*, cudaStream_t) { set_error("network kernel not built yet"); return BB_ESTATE; }
+
+constexpr int NET_F = 16;          // tower width this kernel is specialised for (template shape)
+constexpr int NET_THREADS = 256;
+constexpr int NET_MAX_DENSE = 64;
+
+template <class G> struct NetTile;
+template <> struct NetTile<TicTacToe> { static constexpr int P = 40; };
+template <> struct NetTile<Connect4> { static constexpr int P = 12; };
+template <> struct NetTile<DragonChess> { static constexpr int P = 8; };
+
+struct NetParams {
+  const float* tower_w;    // [layer][tap][ci][16] (stem: ci padded to CIN_PAD), BN folded
+  const float* tower_b;    // [layer][16]
+  const float* head;       // value conv w[16], b | policy conv w[16][2], b[2] | d1 w[D], b[D] | d2 w[D], b
+  const float* pol_w;      // [2][A]
+  const float* pol_b;      // [A]
+  int layers;              // 1 + 2*blocks
+  int dense;
+  float eps, alpha;
+  unsigned long long seed;
+  unsigned long long* call_counter;
+};
+
+struct NetDev {
+  int game;
+  bb_net_desc desc;
+  NetParams p;
+  std::vector<void*> allocs;
+  int sm_count;
+};
+
+template <class G>
+struct NetGeom {
+  static constexpr int P = NetTile<G>::P;
+  static constexpr int HW = G::H * G::W;
+  static constexpr int PW = G::W + 2, PH = G::H + 2, CELLS = PW * PH;
+  static constexpr int CIN_PAD = (G::C + 3) / 4 * 4;
+  static constexpr int NG0 = CIN_PAD / 4 > 4 ? CIN_PAD / 4 : 4;       // channel groups in buffer 0
+  static constexpr int ITEMS = P * HW;
+  static constexpr int IPT = (ITEMS + NET_THREADS - 1) / NET_THREADS; // items per thread
+  static_assert(IPT <= 2, "tile too large");
+  static constexpr int X0_FLOATS = NG0 * P * CELLS * 4;
+  static constexpr int X1_FLOATS = 4 * P * CELLS * 4;
+  static constexpr int STEM_W = 9 * CIN_PAD * NET_F;
+  static constexpr int LAYER_W = 9 * NET_F * NET_F;
+};
+
+// 3x3 'same' convolution over the tile: in[cg][cell][4] -> out[cg][cell][4], 2 items per thread.
+template <class G, int CIG, bool SKIP>
+__device__ __forceinline__ void conv3x3(const float* __restrict__ in, float* __restrict__ out, const float* __restrict__ w,
+                                        const float* __restrict__ bias, const int* cell, const bool* live) {
+  using Ge = NetGeom<G>;
+  constexpr int PLANE = Ge::P * Ge::CELLS;     // cells per channel group
+  float acc[2][NET_F];
+#pragma unroll
+  for (int t = 0; t < 2; ++t)
+#pragma unroll
+    for (int co = 0; co < NET_F; ++co) acc[t][co] = bias[co];
+#pragma unroll 1
+  for (int tap = 0; tap < 9; ++tap) {
+    const int off = (tap / 3 - 1) * Ge::PW + (tap % 3 - 1);
+#pragma unroll
+    for (int cg = 0; cg < CIG; ++cg) {
+      const float4 a0 = *reinterpret_cast<const float4*>(in + ((size_t)cg * PLANE + cell[0] + off) * 4);
+      const float4 a1 = *reinterpret_cast<const float4*>(in + ((size_t)cg * PLANE + cell[1] + off) * 4);
+      const float av0[4] = {a0.x, a0.y, a0.z, a0.w}, av1[4] = {a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4* wp = reinterpret_cast<const float4*>(w + ((tap * CIG * 4) + cg * 4 + q) * NET_F);
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const float4 ww = wp[v];
+          acc[0][v * 4 + 0] = fmaf(av0[q], ww.x, acc[0][v * 4 + 0]);
+          acc[0][v * 4 + 1] = fmaf(av0[q], ww.y, acc[0][v * 4 + 1]);
+          acc[0][v * 4 + 2] = fmaf(av0[q], ww.z, acc[0][v * 4 + 2]);
+          acc[0][v * 4 + 3] = fmaf(av0[q], ww.w, acc[0][v * 4 + 3]);
+          acc[1][v * 4 + 0] = fmaf(av1[q], ww.x, acc[1][v * 4 + 0]);
+          acc[1][v * 4 + 1] = fmaf(av1[q], ww.y, acc[1][v * 4 + 1]);
+          acc[1][v * 4 + 2] = fmaf(av1[q], ww.z, acc[1][v * 4 + 2]);
+          acc[1][v * 4 + 3] = fmaf(av1[q], ww.w, acc[1][v * 4 + 3]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    if (!live[t]) continue;
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      float4* o = reinterpret_cast<float4*>(out + ((size_t)v * PLANE + cell[t]) * 4);
+      float4 r = make_float4(acc[t][v * 4], acc[t][v * 4 + 1], acc[t][v * 4 + 2], acc[t][v * 4 + 3]);
+      if (SKIP) { const float4 s = *o; r.x += s.x; r.y += s.y; r.z += s.z; r.w += s.w; }
+      r.x = fmaxf(r.x, 0.f); r.y = fmaxf(r.y, 0.f); r.z = fmaxf(r.z, 0.f); r.w = fmaxf(r.w, 0.f);
+      *o = r;
+    }
+  }
+}
+
+__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
+  // fixed-order tree: deterministic
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    float t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    v = is_max ? fmaxf(v, t) : v + t;
+  }
+  __syncthreads();
+  if (lane == 0) red[wid] = v;
+  __syncthreads();
+  float r = red[0];
+  for (int i = 1; i < NET_THREADS / 32; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  return r;
+}
+
+// counter-based uniform in (0,1): splitmix64 of (seed, call, element, draw)
+__device__ __forceinline__ float u01(unsigned long long key, unsigned long long ctr) {
+  unsigned long long z = key + 0x9E3779B97F4A7C15ull * (ctr + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return ((float)(z >> 40) + 0.5f) * (1.0f / 16777216.0f);
+}
+// Gamma(a, 1) for 0 < a < 1: Marsaglia-Tsang on a+1, boosted by U^(1/a)
+__device__ float gamma_small(float a, unsigned long long key, unsigned long long& ctr) {
+  const float d = a + 1.0f - 1.0f / 3.0f, c = rsqrtf(9.0f * d);
+  for (int it = 0; it < 16; ++it) {
+    float u1 = u01(key, ctr++), u2 = u01(key, ctr++);
+    float x = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+    float v = 1.0f + c * x;
+    if (v <= 0.f) continue;
+    v = v * v * v;
+    float u = u01(key, ctr++);
+    if (logf(u) < 0.5f * x * x + d - d * v + d * logf(v)) return d * v * powf(u01(key, ctr++), 1.0f / a);
+  }
+  return a;
+}
+// dist.sample(...)[..., 0] of Dirichlet([alpha, 1-alpha]) == Beta(alpha, 1-alpha)  (A.17)
+__device__ float beta_noise(float alpha, unsigned long long key, unsigned long long elem) {
+  unsigned long long ctr = elem << 8;
+  float x = gamma_small(alpha, key, ctr), y = gamma_small(1.0f - alpha, key, ctr);
+  return x / (x + y);
+}
+
+template <class G>
+__global__ void __launch_bounds__(NET_THREADS, 1)
+k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_max, const int* __restrict__ count_dev,
+              float* __restrict__ policy, float* __restrict__ value) {
+  using Ge = NetGeom<G>;
+  extern __shared__ __align__(16) float smem[];
+  float* sw = smem;                                         // tower weights
+  float* sb = sw + Ge::STEM_W + (np.layers - 1) * Ge::LAYER_W;
+  float* x0 = sb + np.layers * NET_F;
+  float* x1 = x0 + Ge::X0_FLOATS;
+  float* red = x1 + Ge::X1_FLOATS;                          // 8 floats block-reduce scratch
+  float* hsum = red + 8;                                    // [P][3] head sums
+  float* hcell = hsum + Ge::P * 4;                          // [3][ITEMS] per-cell head activations
+  typename G::State* sst = reinterpret_cast<typename G::State*>(hcell + 3 * Ge::ITEMS + (Ge::ITEMS & 1));
+  const int tid = threadIdx.x;
+  const int n = count_dev ? min(n_max, *count_dev) : n_max;
+  const int n_tiles = (n + Ge::P - 1) / Ge::P;
+  if ((int)blockIdx.x >= n_tiles) return;
+
+  const int wtot = Ge::STEM_W + (np.layers - 1) * Ge::LAYER_W;
+  for (int i = tid * 4; i < wtot; i += NET_THREADS * 4)
+    *reinterpret_cast<float4*>(sw + i) = *reinterpret_cast<const float4*>(np.tower_w + i);
+  for (int i = tid; i < np.layers * NET_F; i += NET_THREADS) sb[i] = np.tower_b[i];
+  for (int i = tid; i < Ge::X0_FLOATS + Ge::X1_FLOATS; i += NET_THREADS) x0[i] = 0.f;   // zero halos once
+
+  int cell[2], pos[2], hw[2];
+  bool live[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int item = tid + t * NET_THREADS;
+    live[t] = item < Ge::ITEMS;
+    const int it = live[t] ? item : 0;
+    pos[t] = it / Ge::HW;
+    hw[t] = it % Ge::HW;
+    cell[t] = pos[t] * Ge::CELLS + (hw[t] / G::W + 1) * Ge::PW + (hw[t] % G::W + 1);
+  }
+  constexpr int PLANE = Ge::P * Ge::CELLS;
+  const float* hd = np.head;
+  const int D = np.dense;
+  unsigned long long call = 0;
+  if (np.eps > 0.f) call = *np.call_counter;
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int base = tile * Ge::P;
+    __syncthreads();
+    if (tid < Ge::P) sst[tid] = states[min(base + tid, n - 1)];
+    __syncthreads();
+    // decode input planes (AsInputArray) straight from the packed state
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (!live[t]) continue;
+      const typename G::State s = sst[pos[t]];
+#pragma unroll
+      for (int cg = 0; cg < Ge::CIN_PAD / 4; ++cg) {
+        float v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) v[q] = (cg * 4 + q < G::C) ? (float)G::plane(s, hw[t], cg * 4 + q) : 0.f;
+        *reinterpret_cast<float4*>(x0 + ((size_t)cg * PLANE + cell[t]) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+      }
+    }
+    __syncthreads();
+    conv3x3<G, Ge::CIN_PAD / 4, false>(x0, x1, sw, sb, cell, live);                         // stem
+    const float* lw = sw + Ge::STEM_W;
+    for (int l = 1; l < np.layers; l += 2) {
+      __syncthreads();
+      conv3x3<G, 4, false>(x1, x0, lw, sb + l * NET_F, cell, live);                          // conv_1 + BN + ReLU
+      __syncthreads();
+      conv3x3<G, 4, true>(x0, x1, lw + Ge::LAYER_W, sb + (l + 1) * NET_F, cell, live);       // conv_2 + BN + skip + ReLU
+      lw += 2 * Ge::LAYER_W;
+    }
+    __syncthreads();
+    // heads: 1x1 convs (1 value filter, 2 policy filters) + BN + ReLU per cell
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (!live[t]) continue;
+      float v = hd[16], p0 = hd[17 + 32], p1 = hd[17 + 33];
+#pragma unroll
+      for (int cg = 0; cg < 4; ++cg) {
+        const float4 a = *reinterpret_cast<const float4*>(x1 + ((size_t)cg * PLANE + cell[t]) * 4);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int ci = cg * 4 + q;
+          v = fmaf(av[q], hd[ci], v);
+          p0 = fmaf(av[q], hd[17 + ci * 2], p0);
+          p1 = fmaf(av[q], hd[17 + ci * 2 + 1], p1);
+        }
+      }
+      const int item = tid + t * NET_THREADS;
+      hcell[item] = fmaxf(v, 0.f);
+      hcell[Ge::ITEMS + item] = fmaxf(p0, 0.f);
+      hcell[2 * Ge::ITEMS + item] = fmaxf(p1, 0.f);
+    }
+    __syncthreads();
+    if (tid < Ge::P * 3) {                                   // sum over H,W in a fixed order
+      const int p = tid / 3, k = tid % 3;
+      float s = 0.f;
+      for (int c = 0; c < Ge::HW; ++c) s += hcell[k * Ge::ITEMS + p * Ge::HW + c];
+      hsum[p * 4 + k] = s;
+    }
+    __syncthreads();
+    const float* d1w = hd + 17 + 34;
+    const float* d1b = d1w + D;
+    const float* d2w = d1b + D;
+    const float d2b = d2w[D];
+    if (tid < Ge::P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
+      const float s = hsum[tid * 4];
+      float o = d2b;
+      for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)Ge::HW * d1b[d]), 0.f), d2w[d], o);
+      value[base + tid] = tanhf(o);
+    }
+    // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
+    if (G::A <= 32) {
+      if (tid < Ge::P && base + tid < n) {
+        const float s0 = hsum[tid * 4 + 1], s1 = hsum[tid * 4 + 2];
+        float z[G::A <= 32 ? G::A : 1];
+        float m = -INFINITY;
+#pragma unroll
+        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
+          z[a] = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)Ge::HW * np.pol_b[a]));
+          m = fmaxf(m, z[a]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) { z[a] = expf(z[a] - m); sum += z[a]; }
+        float tot = 0.f;
+#pragma unroll
+        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
+          float pa = z[a] / sum;
+          if (np.eps > 0.f)
+            pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + tid) * G::A + a);
+          z[a] = pa;
+          tot += pa;
+        }
+#pragma unroll
+        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[(size_t)(base + tid) * G::A + a] = z[a] / tot;
+      }
+    } else {
+      for (int p = 0; p < Ge::P && base + p < n; ++p) {      // block-wide over the 4032 actions
+        const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
+        float* out = policy + (size_t)(base + p) * G::A;
+        float m = -INFINITY;
+        for (int a = tid; a < G::A; a += NET_THREADS) {
+          float z = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)Ge::HW * np.pol_b[a]));
+          out[a] = z;
+          m = fmaxf(m, z);
+        }
+        m = block_reduce(m, red, true);
+        float sum = 0.f;
+        for (int a = tid; a < G::A; a += NET_THREADS) { float e = expf(out[a] - m); out[a] = e; sum += e; }
+        sum = block_reduce(sum, red, false);
+        float tot = 0.f;
+        for (int a = tid; a < G::A; a += NET_THREADS) {
+          float pa = out[a] / sum;
+          if (np.eps > 0.f)
+            pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + p) * G::A + a);
+          out[a] = pa;
+          tot += pa;
+        }
+        tot = block_reduce(tot, red, false);
+        for (int a = tid; a < G::A; a += NET_THREADS) out[a] = out[a] / tot;
+      }
+    }
+  }
+}
+
+__global__ void k_bump(unsigned long long* c) { *c += 1; }
+
+template <class G>
+static size_t net_smem_bytes(int layers) {
+  using Ge = NetGeom<G>;
+  size_t fl = Ge::STEM_W + (size_t)(layers - 1) * Ge::LAYER_W + (size_t)layers * NET_F + Ge::X0_FLOATS + Ge::X1_FLOATS + 8 + Ge::P * 4 + 3 * Ge::ITEMS + 2;
+  return fl * 4 + Ge::P * sizeof(typename G::State) + 16;
+}
+
+template <class G>
+static int net_launch(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
+  using Ge = NetGeom<G>;
+  const size_t smem = net_smem_bytes<G>(net->p.layers);
+  static bool configured[3] = {false, false, false};
+  if (!configured[G::ID]) {
+    BB_CUDA(cudaFuncSetAttribute(k_net_forward<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[G::ID] = true;
+  }
+  const int tiles = (n + Ge::P - 1) / Ge::P;
+  const int grid = tiles < net->sm_count ? tiles : net->sm_count;
+  k_net_forward<G><<<grid, NET_THREADS, smem, stream>>>(net->p, (const typename G::State*)states, n, count_dev, policy, value);
+  BB_CUDA(cudaGetLastError());
+  if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
+  return BB_OK;
+}
+
+int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
+  if (n <= 0) return BB_OK;
+  BB_DISPATCH_GAME(net->game, return net_launch<G>(net, states, n, count_dev, policy, value, stream));
+  return BB_EINVAL;
+}
+
+// Host side of bb_net_load: fold BN (training=False, eps 1e-3) into each convolution and lay the
+// tower out as [layer][tap][ci][16].  Flat input order (oracle/network_np.py init_weights):
+//   conv_bn := w[k,k,ci,co] b[co] gamma[co] beta[co] mean[co] var[co]
+//   stem, block{i}.c1, block{i}.c2 ..., value.conv, value.d1.w[1,D] .b[D], value.d2.w[D,1] .b[1],
+//   policy.conv, policy.d.w[2,A] .b[A]
+template <class G>
+static int net_build(NetDev* net, const bb_net_desc* d, const float* w, size_t n_floats) {
+  using Ge = NetGeom<G>;
+  const int F = d->filters, D = d->dense, blocks = d->blocks, cin = d->cin, A = G::A;
+  if (F != NET_F) { set_error("this build of the network kernel is specialised for filters=%d (got %d)", NET_F, F); return BB_EINVAL; }
+  if (cin != G::C) { set_error("cin %d does not match the game's %d input planes", cin, G::C); return BB_EINVAL; }
+  if (D < 1 || D > NET_MAX_DENSE || blocks < 0) { set_error("dense must be in [1,%d], blocks >= 0", NET_MAX_DENSE); return BB_EINVAL; }
+  auto conv_sz = [](int k, int ci, int co) { return (size_t)k * k * ci * co + 5 * (size_t)co; };
+  const size_t need = conv_sz(3, cin, F) + 2 * (size_t)blocks * conv_sz(3, F, F) + conv_sz(1, F, 1) + D + D + D + 1 +
+                      conv_sz(1, F, 2) + 2 * (size_t)A + A;
+  if (n_floats != need) { set_error("bb_net_load: expected %zu floats for this shape, got %zu", need, n_floats); return BB_EINVAL; }
+  const int layers = 1 + 2 * blocks;
+  std::vector<float> tw(Ge::STEM_W + (size_t)(layers - 1) * Ge::LAYER_W, 0.f), tb((size_t)layers * NET_F);
+  const float* p = w;
+  auto fold = [&](int k, int ci, int co, int ci_pad, float* wout, float* bout) {
+    const float* cw = p; p += (size_t)k * k * ci * co;
+    const float *b = p, *g = p + co, *be = p + 2 * co, *mu = p + 3 * co, *var = p + 4 * co;
+    p += 5 * (size_t)co;
+    for (int o = 0; o < co; ++o) {
+      const double s = (double)g[o] / sqrt((double)var[o] + 1e-3);
+      bout[o] = (float)(((double)b[o] - (double)mu[o]) * s + (double)be[o]);
+      for (int t = 0; t < k * k; ++t)
+        for (int i = 0; i < ci; ++i) wout[((size_t)t * ci_pad + i) * co + o] = (float)((double)cw[((size_t)t * ci + i) * co + o] * s);
+    }
+  };
+  fold(3, cin, F, Ge::CIN_PAD, tw.data(), tb.data());
+  for (int l = 1; l < layers; ++l) fold(3, F, F, F, tw.data() + Ge::STEM_W + (size_t)(l - 1) * Ge::LAYER_W, tb.data() + (size_t)l * NET_F);
+  std::vector<float> head(17 + 34 + 3 * (size_t)D + 1);
+  fold(1, F, 1, F, head.data(), head.data() + 16);                       // value conv: w[16], b
+  memcpy(head.data() + 17 + 34, p, sizeof(float) * (3 * (size_t)D + 1)); // d1.w, d1.b, d2.w, d2.b
+  p += 3 * (size_t)D + 1;
+  fold(1, F, 2, F, head.data() + 17, head.data() + 17 + 32);             // policy conv: w[16][2], b[2]
+  const float* pw = p;
+  const float* pb = p + 2 * (size_t)A;
+  auto upload = [&](const float* src, size_t cnt, const float** dst) -> int {
+    void* q = nullptr;
+    BB_CUDA(cudaMalloc(&q, cnt * sizeof(float)));
+    net->allocs.push_back(q);
+    BB_CUDA(cudaMemcpy(q, src, cnt * sizeof(float), cudaMemcpyHostToDevice));
+    *dst = (const float*)q;
+    return BB_OK;
+  };
+  int rc;
+  if ((rc = upload(tw.data(), tw.size(), &net->p.tower_w))) return rc;
+  if ((rc = upload(tb.data(), tb.size(), &net->p.tower_b))) return rc;
+  if ((rc = upload(head.data(), head.size(), &net->p.head))) return rc;
+  if ((rc = upload(pw, 2 * (size_t)A, &net->p.pol_w))) return rc;
+  if ((rc = upload(pb, (size_t)A, &net->p.pol_b))) return rc;
+  void* ctr = nullptr;
+  BB_CUDA(cudaMalloc(&ctr, 8));
+  BB_CUDA(cudaMemset(ctr, 0, 8));
+  net->allocs.push_back(ctr);
+  net->p.call_counter = (unsigned long long*)ctr;
+  net->p.layers = layers;
+  net->p.dense = D;
+  net->p.eps = d->epsilon;
+  net->p.alpha = d->alpha;
+  net->p.seed = d->noise_seed;
+  if (net_smem_bytes<G>(layers) > 227 * 1024) { set_error("network too deep for the smem-resident kernel (%d blocks)", blocks); return BB_EINVAL; }
+  return BB_OK;
+}
+
+int net_create(int game, const bb_net_desc* d, const float* w, size_t n_floats, NetDev** out) {
+  if (!d || !w || !out) { set_error("bb_net_load: null argument"); return BB_EINVAL; }
+  NetDev* net = new NetDev();
+  net->game = game;
+  net->desc = *d;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&net->sm_count, cudaDevAttrMultiProcessorCount, dev);
+  int rc = BB_EINVAL;
+  switch (game) {
+    case BB_TICTACTOE: rc = net_build<TicTacToe>(net, d, w, n_floats); break;
+    case BB_CONNECT4: rc = net_build<Connect4>(net, d, w, n_floats); break;
+    case BB_DRAGONCHESS: rc = net_build<DragonChess>(net, d, w, n_floats); break;
+    default: set_error("unknown game id %d", game);
+  }
+  if (rc != BB_OK) { net_destroy(net); return rc; }
+  *out = net;
+  return BB_OK;
+}
+
+void net_destroy(NetDev* net) {
+  if (!net) return;
+  for (void* p : net->allocs) cudaFree(p);
+  delete net;
+}
+
 }  // namespace bb

@@ -81,6 +81,10 @@ struct bb_engine {
   virtual int eval_fetch(void*, int32_t*) = 0;
   virtual int eval_submit(const float*, const float*) = 0;
   virtual int selfplay(int, double, const double*) = 0;
+  virtual int step(int, int, double, const double*) = 0;
+  virtual void* stream_handle() = 0;
+  virtual int profile(int, int) = 0;
+  virtual int profile_read(double*, double*, int*) = 0;
   virtual int pool_cap() = 0;
   virtual int records_export(int32_t*, int32_t*, void*, uint32_t*, uint16_t*, uint32_t*, uint16_t*) = 0;
   virtual int records_device(void**, void**, void**, void**, void**, void**, void**) = 0;
@@ -99,6 +103,9 @@ struct EngineT : bb_engine {
   void* scratch = nullptr;         // device scratch for exports
   size_t scratch_bytes = 0;
   unsigned long long host_ticks = 0, host_launches = 0;
+  bool prof = false;               // per-tick CUDA-event timing of the two kernels (bench only)
+  std::vector<cudaEvent_t> prof_ev;
+  size_t prof_used = 0;
 
   template <class T>
   int alloc(T** p, size_t count) {
@@ -165,6 +172,7 @@ struct EngineT : bb_engine {
     cudaSetDevice(cfg.device);
     if (stream) cudaStreamSynchronize(stream);
     for (void* p : allocs) cudaFree(p);
+    for (cudaEvent_t e : prof_ev) cudaEventDestroy(e);
     if (scratch) cudaFree(scratch);
     if (host_flags) cudaFreeHost(host_flags);
     if (net) net_destroy(net);
@@ -194,9 +202,10 @@ struct EngineT : bb_engine {
     BB_CUDA(cudaGetLastError());
     return BB_OK;
   }
-  int begin_move(int play_limit) override {
+  int begin_move(int play_limit) override { return begin_move_budget(play_limit, -1); }
+  int begin_move_budget(int play_limit, int moves_budget) {
     if (play_limit <= 0) { set_error("play_limit must be > 0"); return BB_EINVAL; }
-    k_begin_move<G><<<warp_grid(), 128, 0, stream>>>(d, play_limit);
+    k_begin_move<G><<<warp_grid(), 128, 0, stream>>>(d, play_limit, moves_budget);
     BB_CUDA(cudaGetLastError());
     return BB_OK;
   }
@@ -205,8 +214,11 @@ struct EngineT : bb_engine {
   int tick() {
     BB_CUDA(cudaMemsetAsync(d.req_count, 0, sizeof(int), stream));
     BB_CUDA(cudaMemsetAsync(d.active, 0, sizeof(int), stream));
+    const bool timed = prof && prof_used + 3 <= prof_ev.size();
+    if (timed) cudaEventRecord(prof_ev[prof_used], stream);
     k_advance<G><<<warp_grid(), 128, 0, stream>>>(d);
     BB_CUDA(cudaGetLastError());
+    if (timed) cudaEventRecord(prof_ev[prof_used + 1], stream);
     host_ticks++;
     host_launches++;
     if (cfg.evaluator == BB_EVAL_KAT) {
@@ -219,6 +231,32 @@ struct EngineT : bb_engine {
       if (rc) return rc;
       host_launches++;
     }
+    if (timed) { cudaEventRecord(prof_ev[prof_used + 2], stream); prof_used += 3; }
+    return BB_OK;
+  }
+  int profile(int enable, int max_ticks) override {
+    prof = enable != 0;
+    prof_used = 0;
+    while (prof && prof_ev.size() < (size_t)max_ticks * 3) {
+      cudaEvent_t e;
+      BB_CUDA(cudaEventCreate(&e));
+      prof_ev.push_back(e);
+    }
+    return BB_OK;
+  }
+  int profile_read(double* adv_ms, double* eval_ms, int* ticks) override {
+    BB_CUDA(cudaStreamSynchronize(stream));
+    double a = 0, b = 0;
+    for (size_t i = 0; i + 2 < prof_used + 0 && i < prof_used; i += 3) {
+      float t0 = 0, t1 = 0;
+      cudaEventElapsedTime(&t0, prof_ev[i], prof_ev[i + 1]);
+      cudaEventElapsedTime(&t1, prof_ev[i + 1], prof_ev[i + 2]);
+      a += t0;
+      b += t1;
+    }
+    if (adv_ms) *adv_ms = a;
+    if (eval_ms) *eval_ms = b;
+    if (ticks) *ticks = (int)(prof_used / 3);
     return BB_OK;
   }
   int read_flags() {
@@ -366,6 +404,24 @@ struct EngineT : bb_engine {
     d.autoplay = 0;
     return rc;
   }
+  // steady-state stepping: every slot plays n_moves moves (finished games restart in place)
+  int step(int n_moves, int play_limit, double temp, const double* u_host) override {
+    if (temp != 1.0 && temp != 0.0) { set_error("bb_selfplay_step supports temp 1 and 0; got %g", temp); return BB_EINVAL; }
+    if (cfg.evaluator == BB_EVAL_EXTERNAL) { set_error("bb_selfplay_step needs a device evaluator"); return BB_EINVAL; }
+    if (n_moves <= 0) { set_error("n_moves must be > 0"); return BB_EINVAL; }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    if (u_host) BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
+    d.autoplay = 1;
+    d.refill = 1;
+    d.play_limit = play_limit;
+    d.temp_mode = temp == 1.0 ? 1 : 0;
+    int rc = begin_move_budget(play_limit, n_moves);
+    if (!rc) rc = run(nullptr);
+    d.autoplay = 0;
+    d.refill = 0;
+    return rc;
+  }
+  void* stream_handle() override { return (void*)stream; }
   int pool_cap() override { return (int)d.pool_cap; }
   int records_export(int32_t* nm, int32_t* win, void* st, uint32_t* off, uint16_t* pa, uint32_t* pp, uint16_t* ch) override {
     const size_t n = d.n_games, mp = d.max_plies;
@@ -449,6 +505,13 @@ int bb_eval_pending(bb_engine* e, int32_t* n, const int32_t** slots, const void*
 int bb_eval_fetch(bb_engine* e, void* st, int32_t* slots) { BB_NEED(e); return e->eval_fetch(st, slots); }
 int bb_eval_submit(bb_engine* e, const float* pol, const float* val) { BB_NEED(e); return e->eval_submit(pol, val); }
 int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* u) { BB_NEED(e); return e->selfplay(play_limit, temp, u); }
+int bb_selfplay_step(bb_engine* e, int n_moves, int play_limit, double temp, const double* u) {
+  BB_NEED(e);
+  return e->step(n_moves, play_limit, temp, u);
+}
+int bb_profile_enable(bb_engine* e, int enable, int max_ticks) { BB_NEED(e); return e->profile(enable, max_ticks); }
+int bb_profile_read(bb_engine* e, double* adv_ms, double* eval_ms, int* ticks) { BB_NEED(e); return e->profile_read(adv_ms, eval_ms, ticks); }
+void* bb_engine_stream(bb_engine* e) { return e ? e->stream_handle() : nullptr; }
 int bb_records_pool_cap(bb_engine* e) { BB_NEED(e); return e->pool_cap(); }
 int bb_records_export(bb_engine* e, int32_t* nm, int32_t* win, void* st, uint32_t* off, uint16_t* pa, uint32_t* pp, uint16_t* ch) {
   BB_NEED(e);

@@ -171,14 +171,25 @@ __global__ void __launch_bounds__(128) k_advance(EngineDev<G> E) {
           const int k = meta_nchild(rh.meta);
           int j;
           if (E.temp_mode == 1) {
-            j = sample_child(stat + rh.child_base, k, E.uniforms[(size_t)g * E.max_plies + s.ply]);
+            const int row = (int)(((unsigned)g + s.game_no) % (unsigned)E.n_games);   // refill: next game, next row
+            j = sample_child(stat + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
           } else {
             double u;
             j = puct_select(stat + rh.child_base, k, E.c, &u);
           }
           play_move(E, s, g, hdr, stat, j, &n_done);
           n_moves += 1;
-          if (s.phase == BB_PH_MOVE_READY) begin_move(E, s, hdr, stat, E.play_limit);
+          if (s.moves_budget > 0) s.moves_budget -= 1;
+          if (s.phase == BB_PH_GAME_OVER && E.refill) {         // Model.Game(); DropRoot() for the next game
+            s.game_no += 1;
+            s.root_state = G::initial();
+            s.root = NONE;
+            s.ply = 0;
+            s.pool_used = 0;
+            s.winner = WIN_NONE;
+            s.phase = BB_PH_MOVE_READY;
+          }
+          if (s.phase == BB_PH_MOVE_READY && s.moves_budget != 0) begin_move(E, s, hdr, stat, E.play_limit);
         }
       } else {
         start_descent(s);
@@ -220,7 +231,8 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.winner = WIN_NONE;
   s.req_idx = 0;
   s.pool_used = 0;
-  s.pad = 0;
+  s.moves_budget = -1;
+  s.game_no = 0;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;
   if (E.winners) E.winners[g] = WIN_NONE;
@@ -237,11 +249,12 @@ __global__ void k_drop_root(EngineDev<G> E) {
 }
 
 template <class G>
-__global__ void k_begin_move(EngineDev<G> E, int play_limit) {
+__global__ void k_begin_move(EngineDev<G> E, int play_limit, int moves_budget) {
   const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (g >= E.n_games) return;
   Slot<G> s = E.slots[g];
   if (s.phase == BB_PH_GAME_OVER || s.phase == BB_PH_ERROR) return;
+  s.moves_budget = moves_budget;
   begin_move(E, s, E.hdr + (size_t)g * E.node_cap, E.stat + (size_t)g * E.node_cap, play_limit);
   if (lane_id() == 0) E.slots[g] = s;
 }

@@ -48,7 +48,8 @@ struct Slot {
   int32_t winner;                 // BB_WIN_* after GAME_OVER
   uint32_t req_idx;               // index of the open evaluator request
   uint32_t pool_used;             // record pool bump pointer
-  int32_t pad;
+  int32_t moves_budget;           // steady-state stepping: moves this slot may still play (<0: unlimited)
+  uint32_t game_no;               // games this slot has finished (refill mode)
 };
 
 // numpy pairwise-sum plan for a dense vector of length A, built on the host.
@@ -81,6 +82,7 @@ struct EngineDev {                // passed to kernels by value
   float* resp_value;
   // self-play
   int autoplay;                   // 1: choose / move root / end games on the device
+  int refill;                     // 1: a finished game's slot starts the next game (steady-state stepping)
   int play_limit;
   int temp_mode;                  // 1: temp == 1 (sample), 0: temp == 0 (PUCT argmax)
   const double* uniforms;         // [n_games][max_plies]

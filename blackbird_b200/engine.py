@@ -257,6 +257,27 @@ class Engine(object):
         check(lib.bb_selfplay_run(self._h, int(play_limit), float(temp), None if u is None else u.ctypes.data_as(C.c_void_p)))
         self.check_status()
 
+    def step(self, n_moves, play_limit, temp=1.0, uniforms=None):
+        """Steady-state stepping: every slot plays n_moves moves; finished games restart in place."""
+        u = None
+        if uniforms is not None:
+            u = np.ascontiguousarray(uniforms, dtype=np.float64)
+            assert u.shape == (self.n_games, self.max_plies), u.shape
+        check(lib.bb_selfplay_step(self._h, int(n_moves), int(play_limit), float(temp),
+                                   None if u is None else u.ctypes.data_as(C.c_void_p)))
+
+    def stream(self):
+        """torch view of the engine's CUDA stream (for CUDA-event timing)."""
+        return torch.cuda.ExternalStream(lib.bb_engine_stream(self._h), device=_dev(self.device))
+
+    def profile(self, enable, max_ticks=4096):
+        check(lib.bb_profile_enable(self._h, int(enable), int(max_ticks)))
+
+    def profile_read(self):
+        a, b, n = C.c_double(), C.c_double(), C.c_int()
+        check(lib.bb_profile_read(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return dict(advance_ms=a.value, eval_ms=b.value, ticks=n.value)
+
     def records_raw(self):
         n, mp, cap = self.n_games, self.max_plies, lib.bb_records_pool_cap(self._h)
         out = dict(n_moves=np.empty(n, np.int32), winner=np.empty(n, np.int32),

@@ -139,6 +139,16 @@ int bb_eval_submit(bb_engine* e, const float* policy_dev, const float* value_dev
  * choice at temp 1 from uniforms_host[n_games][max_plies] (one double per move, A.15), root
  * motion, Winner(None) after every move, records kept on the device. */
 int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* uniforms_host);
+/* Steady-state stepping for throughput measurement and streaming generation: every slot plays
+ * n_moves further moves (play_limit simulations each); a slot whose game ends starts the next
+ * game in place (Blackbird.py:238-244 loop).  uniforms_host may be NULL to keep the table. */
+int bb_selfplay_step(bb_engine* e, int n_moves, int play_limit, double temp, const double* uniforms_host);
+/* The cudaStream_t all engine kernels are launched on (for CUDA-event timing by the caller). */
+void* bb_engine_stream(bb_engine* e);
+/* Per-tick CUDA-event timing of the advance kernel and the evaluator kernel on the engine's
+ * stream (measurement only; up to max_ticks ticks are recorded after enabling). */
+int bb_profile_enable(bb_engine* e, int enable, int max_ticks);
+int bb_profile_read(bb_engine* e, double* advance_ms, double* eval_ms, int* ticks);
 /* Fixed-stride record export (host buffers).  Per slot: n_moves, winner code (BB_WIN_*; NONE =
  * truncated by max_plies), and per record r in [0, n_moves] (the last one is the terminal
  * record): packed state, player to move, and sparse child plays (offsets into a per-slot pool).

@@ -1,0 +1,142 @@
+"""GPU: built-in policy-value network forward vs the float64 restatement of NetworkFactory.py
+(oracle/network_np.py; parity unpinned by the reference, TensorFlow is unavailable), and
+search-with-network vs the oracle search fed the SAME (replayed) network outputs, bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+from oracle import network_np, search_np, selfplay_np  # noqa: E402
+from oracle.rules_np import GAMES  # noqa: E402
+
+REL_TOL = 1e-5      # north_star: "1e-5 rel in fp32"
+
+
+@pytest.fixture(scope='module')
+def mods():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    from blackbird_b200 import engine, records
+    return engine, records
+
+
+def playout_states(game, n, seed):
+    rs = np.random.RandomState(seed)
+    out = []
+    while len(out) < n:
+        s = GAMES[game]()
+        while s.Winner() is None and len(out) < n:
+            out.append(s.Copy())
+            idx = np.flatnonzero(s.LegalActions() == 1)
+            if idx.size == 0:
+                break
+            s.ApplyAction(int(idx[rs.randint(idx.size)]))
+            if game == 'DragonChess' and rs.rand() < 0.1:
+                break
+    return out
+
+
+def pack(engine, game, states):
+    if game == 'DragonChess':
+        cells = np.stack([s.board.astype(np.int8).ravel() for s in states])
+        castle = [sum(int(b) << i for i, b in enumerate(s.castle)) for s in states]
+    else:
+        cells = np.stack([(s.Board[:, :, 0] + 2 * s.Board[:, :, 1]).astype(np.int8).ravel() for s in states])
+        castle = None
+    return engine.pack(game, cells, [s.Player for s in states], [s.PreviousPlayer or 0 for s in states], castle)
+
+
+@pytest.mark.parametrize('game,n', [('TicTacToe', 333), ('Connect4', 1001), ('DragonChess', 150)])
+@pytest.mark.parametrize('jitter', [0.0, 0.2])
+def test_forward_vs_fp64(mods, game, n, jitter):
+    engine, _ = mods
+    C = engine.plane_shape(game)[2]
+    A = engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=4, filters=16, dense=16, seed=5, jitter=jitter)
+    eng = engine.Engine(game, 'dynamic', n_games=1, evaluator='net')
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16)
+    states = playout_states(game, n, seed=1)
+    dev = pack(engine, game, states)
+    pol, val = eng.net_forward(dev)
+    planes = np.concatenate([s.AsInputArray() for s in states])
+    want_p, want_v = network_np.forward(w, planes, dtype=np.float64)
+    got_p, got_v = pol.cpu().numpy().astype(np.float64), val.cpu().numpy().astype(np.float64)
+    assert np.abs(got_p.sum(axis=1) - 1).max() < 1e-6
+    # 1e-5 relative; the 1e-8 absolute floor only matters for softmax tails below 1e-3 (random-init
+    # heads give logits of magnitude ~20, where one fp32 ulp of the logit is already 2e-6 relative)
+    assert (np.abs(got_p - want_p) <= REL_TOL * np.abs(want_p) + 1e-8).all(), \
+        (np.abs(got_p - want_p) / np.maximum(np.abs(want_p), 1e-30)).max()
+    # value = tanh(x): compare with tolerance relative to the [0,1] win-rate scale used downstream
+    assert np.abs(got_v - want_v).max() < REL_TOL
+    # run-to-run determinism (fixed reduction order)
+    pol2, val2 = eng.net_forward(dev)
+    assert torch.equal(pol, pol2) and torch.equal(val, val2)
+    eng.close()
+
+
+class Replay(object):
+    """Evaluator for the oracle search that replays the GPU network's own outputs (looked up by
+    input planes): isolates tree-search parity from network rounding."""
+
+    def __init__(self, engine, eng, game):
+        self.engine, self.eng, self.game, self.cache = engine, eng, game, {}
+
+    def _eval(self, planes):
+        key = planes.tobytes()
+        if key not in self.cache:
+            H, W, C = planes.shape[1:]
+            cells = (planes[0, :, :, 0] + 2 * planes[0, :, :, 1]).astype(np.int8).reshape(1, -1)
+            player = 1 if planes[0, 0, 0, 2] == 1 else 2
+            dev = self.engine.pack(self.game, cells, [player], [0])
+            pol, val = self.eng.net_forward(dev)
+            self.cache[key] = (pol[0].cpu().numpy(), np.float32(val[0].item()))
+        return self.cache[key]
+
+    def getPolicy(self, planes):
+        return self._eval(planes)[0]
+
+    def getEvaluation(self, planes):
+        return self._eval(planes)[1]
+
+
+@pytest.mark.parametrize('kind,P', [('dynamic', 64), ('fixed', 24)])
+def test_selfplay_with_network_replay(mods, kind, P):
+    engine, records = mods
+    game, G = 'Connect4', 6
+    w = network_np.init_weights(3, 7, seed=2, jitter=0.1)
+    eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P)
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
+    eng.selfplay(P, 1.0, u)
+    got = records.build_records(eng)
+    replay = Replay(engine, eng, game)
+    for g in range(G):
+        s = search_np.NetSearch(replay, kind, maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        want, winner, _ = selfplay_np.play_game(s, GAMES[game], 1)
+        assert got[g][0] == want, (kind, g)
+    eng.close()
+
+
+def test_noise_statistics(mods):
+    """epsilon > 0: policy = (1-eps)*softmax + eps*Beta(alpha, 1-alpha) draws, renormalised (A.17).
+    TF's RNG cannot be matched; check moments: E[Beta(a,1-a)] = a, Var = a(1-a)/2."""
+    engine, _ = mods
+    w = network_np.init_weights(3, 7, seed=2)
+    eng = engine.Engine('Connect4', 'dynamic', n_games=1, evaluator='net')
+    eps, alpha = 0.3, 0.2
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, epsilon=eps, alpha=alpha, seed=7)
+    n = 20000
+    dev = engine.init_states('Connect4', n)
+    pol, _ = eng.net_forward(dev)
+    soft = network_np.forward(w, GAMES['Connect4']().AsInputArray(), dtype=np.float64)[0][0]
+    p = pol.cpu().numpy().astype(np.float64)
+    assert np.abs(p.sum(axis=1) - 1).max() < 1e-5
+    # un-normalise: p_i = m_i / sum(m), m_i = (1-eps) soft_i + eps n_i  => ratios against E[m]
+    mean_m = (1 - eps) * soft + eps * alpha
+    est = p.mean(axis=0)
+    assert np.abs(est - mean_m / mean_m.sum()).max() < 0.01
+    pol2, _ = eng.net_forward(dev)
+    assert not torch.equal(pol, pol2)          # fresh draw on every evaluation
+    eng.close()

@@ -33,10 +33,7 @@ def step_move(eng, play_limit, u):
         k = int(st['n_children'][g])
         plays = np.zeros(eng.A)
         plays[st['actions'][g, :k]] = st['plays'][g, :k]
-        if st['root_has_parent'][g]:
-            wr = (np.float32(st['root_value'][g]) / np.float32(st['root_plays'][g])).tobytes().hex()
-        else:
-            wr = 0
+        wr = (np.float32(st['root_value'][g]) / np.float32(st['root_plays'][g])).tobytes().hex()
         total = sum(plays)
         probs = plays / total if total > 0 else np.zeros(eng.A)
         nz = np.flatnonzero(plays)
