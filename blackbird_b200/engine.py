@@ -118,7 +118,8 @@ def kat_forward(game, states):
 
 def default_node_cap(game, search, play_limit, max_plies):
     a = min(_ACTIONS[game], 48)
-    per_sim = a * (1.4 if search == 'fixed' else 1.0)
+    # fixed-depth search expands several fresh nodes per simulation while the tree is young
+    per_sim = a * ((3.5 if play_limit < 200 else 1.4) if search == 'fixed' else 1.0)
     return int(min(1 << 22, max(4096, play_limit * per_sim * max_plies + 64)))
 
 
