@@ -5,9 +5,10 @@ Workload (N=1): BASELINE.json configs[1] -- Connect4, FixedMCTS maxDepth 10, 800
 move, 4096 concurrent games per GPU, template network (blocks 4, filters 16, dense 16), random-init
 weights, synthetic data (games start from the empty board; move sampling from per-game uniforms).
 
-A "step" is one move round: every game slot runs one FindMove (800 simulations, every simulation a
-PUCT descent + lazy network evaluation + backup) and plays the move; finished games restart in
-place so all slots stay busy (steady state).  `value` = simulations of all ranks / device time
+A "step" is one move round: the game slots together play as many moves as there are slots (each
+move = one FindMove of 800 simulations, every simulation a PUCT descent + lazy network evaluation
++ backup, then MoveRoot); there is no barrier between moves and finished games restart in place,
+so all slots stay busy (steady state).  `value` = simulations of all ranks / device time
 (max over ranks), inputs resident in HBM.  `e2e` = the same metric through the C-ABI self-play
 call with HOST buffers: uniforms H2D, G whole games to completion, raw records D2H, all inside
 the timed region.  `--impl reference` times the CPU port of the reference (oracle/) on the host
@@ -48,7 +49,7 @@ def config_dict(args, n_gpus):
     return {'workload': 'Connect4 FixedMCTS(maxDepth 10, c 0.85) self-play, %d sims/move, %d concurrent games/GPU, '
                         'network blocks4/filters16/dense16 (BASELINE configs[1])' % (args.sims, args.games),
             'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS', 'max_depth': MAX_DEPTH,
-            'step': 'one move round (FindMove+MoveRoot) of every game slot, finished games restart in place',
+            'step': 'one move round: the %d slots together play %d moves (FindMove+MoveRoot each), no barrier between moves, finished games restart in place' % (args.games, args.games),
             'epsilon': args.epsilon, 'parallelism': 'games sharded over %d GPU(s), no data-path collective' % n_gpus,
             'l2_policy': 'working set (tree pool, GBs) larger than L2; no flush needed'}
 
@@ -189,9 +190,9 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     eng.reset()
-    eng.step(1, P, 1.0, uniforms)                    # uploads the uniform table; first warm-up step
+    eng.stream_moves(G, P, 1.0, uniforms)            # uploads the uniform table; first warm-up step
     for _ in range(max(0, args.warmup - 1)):
-        eng.step(1, P)
+        eng.stream_moves(G, P)
     eng.check_status()
     c0 = eng.counters(reset=True)
     sampler = ClockSampler(local)
@@ -200,7 +201,7 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
-        eng.step(1, P)
+        eng.stream_moves(G, P)
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -219,7 +220,7 @@ def run_ours(args):
 
     # kernel shares: one profiled step (CUDA events around every advance / network launch)
     eng.profile(True, 16384)
-    eng.step(1, P)
+    eng.stream_moves(G, P)
     prof = eng.profile_read()
     eng.profile(False)
     cp = eng.counters(reset=True)
@@ -237,7 +238,9 @@ def run_ours(args):
     d_bar = cp['select_steps'] / max(1, cp['sims'])
     nexp = cp['expansions'] / max(1, cp['sims'])
     k_bar = cp['nodes'] / max(1, cp['expansions'])
-    b_sim = d_bar * (16 * k_bar + 16) + nexp * k_bar * 32 + (cp['evals'] / max(1, cp['sims'])) * (16 + 4 * 8) + 16 * (d_bar + 1)
+    # select: one 32-byte node per child per level; expand: k 32-byte nodes + the parent's header; evaluator
+    # mailbox: state out/in + policy/value out/in; backup: 8-byte read-modify-write per path node
+    b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * 16 + 2 * 4 * 8) + 16 * (d_bar + 1)
     tree_gbs = cp['sims'] * b_sim / (prof['advance_ms'] * 1e-3) / 1e9 if prof['advance_ms'] > 0 else 0.0
     roofline = {'bound': 'tensor', 'kernel': 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks'])),
                 'achieved': net_tflops, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / tensor_peak,

@@ -8,13 +8,13 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libbbengine.so')
+LIB_PATH = os.environ.get('BB_ENGINE_LIB') or os.path.join(HERE, 'libbbengine.so')   # override: debug builds (-DBB_DEBUG)
 
 BB_OK, BB_EINVAL, BB_EILLEGAL, BB_EASSERT, BB_ENOMEM, BB_ECUDA, BB_ESTATE = 0, -1, -2, -3, -4, -5, -6
 TICTACTOE, CONNECT4, DRAGONCHESS = 0, 1, 2
 FIXED, DYNAMIC = 0, 1
 EVAL_KAT, EVAL_NET, EVAL_EXTERNAL = 0, 1, 2
-PH_IDLE, PH_RUN, PH_WAIT_EXPAND, PH_WAIT_LEAF, PH_MOVE_READY, PH_GAME_OVER, PH_ERROR = range(7)
+PH_IDLE, PH_RUN, PH_WAIT_EXPAND, PH_WAIT_LEAF, PH_MOVE_READY, PH_GAME_OVER, PH_ERROR, PH_COMPACT = range(8)
 GAME_IDS = {'TicTacToe': TICTACTOE, 'Connect4': CONNECT4, 'DragonChess': DRAGONCHESS}
 
 
@@ -68,6 +68,7 @@ SIGNATURES = {
     'bb_eval_submit': (I, [VP, VP, VP]),
     'bb_selfplay_run': (I, [VP, I, C.c_double, VP]),
     'bb_selfplay_step': (I, [VP, I, I, C.c_double, VP]),
+    'bb_selfplay_stream': (I, [VP, C.c_longlong, I, C.c_double, VP]),
     'bb_engine_stream': (VP, [VP]),
     'bb_profile_enable': (I, [VP, I, I]),
     'bb_profile_read': (I, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(I)]),

@@ -30,23 +30,22 @@ __global__ void k_root_stats(EngineDev<G> E, int kmax, int32_t* n_children, int3
   const Slot<G> s = E.slots[g];
   const int lane = lane_id();
   if (s.root == NONE) { if (lane == 0) { n_children[g] = -1; root_plays[g] = 0; root_value[g] = 0; root_has_parent[g] = 0; } return; }
-  const NodeHdr* hdr = E.hdr + (size_t)g * E.node_cap;
-  const NodeStat* stat = E.stat + (size_t)g * E.node_cap;
-  const NodeHdr rh = hdr[s.root];
-  const int k = rh.child_base == NONE ? -1 : meta_nchild(rh.meta);
+  const Node* nodes = E.half(g, s.half);
+  const Node rn = nodes[s.root];
+  const int k = rn.h.child_base == NONE ? -1 : meta_nchild(rn.h.meta);
   if (lane == 0) {
     n_children[g] = k;
-    root_plays[g] = stat[s.root].plays;
-    root_value[g] = (double)stat[s.root].value;
+    root_plays[g] = rn.s.plays;
+    root_value[g] = (double)rn.s.value;
     root_has_parent[g] = s.root_parent_player != 0;
   }
   for (int j = lane; j < k && j < kmax; j += 32) {
     const size_t o = (size_t)g * kmax + j;
-    const NodeStat st = stat[rh.child_base + j];
-    actions[o] = meta_action(hdr[rh.child_base + j].meta);
-    plays[o] = st.plays;
-    child_value[o] = st.value;
-    child_prior[o] = st.prior;
+    const Node kid = nodes[rn.h.child_base + j];
+    actions[o] = meta_action(kid.h.meta);
+    plays[o] = kid.s.plays;
+    child_value[o] = kid.s.value;
+    child_prior[o] = kid.s.prior;
   }
 }
 
@@ -82,6 +81,7 @@ struct bb_engine {
   virtual int eval_submit(const float*, const float*) = 0;
   virtual int selfplay(int, double, const double*) = 0;
   virtual int step(int, int, double, const double*) = 0;
+  virtual int stream_moves(long long, int, double, const double*) = 0;
   virtual void* stream_handle() = 0;
   virtual int profile(int, int) = 0;
   virtual int profile_read(double*, double*, int*) = 0;
@@ -99,7 +99,11 @@ struct EngineT : bb_engine {
   cudaStream_t stream = nullptr;
   std::vector<void*> allocs;
   double* uniforms_dev = nullptr;
-  int* host_flags = nullptr;       // pinned: [0] active, [1] req_count
+  struct Snap { TickCtl ctl; unsigned long long moves; unsigned par; };
+  Snap* snap = nullptr;            // pinned: two snapshots of the tick control block + move counter
+  cudaEvent_t snap_ev[2] = {nullptr, nullptr};
+  unsigned par = 0;                // parity of the next tick
+  int last_active = 0, last_req = 0;
   void* scratch = nullptr;         // device scratch for exports
   size_t scratch_bytes = 0;
   unsigned long long host_ticks = 0, host_launches = 0;
@@ -144,10 +148,9 @@ struct EngineT : bb_engine {
     int rc;
 #define A_(p, cnt) if ((rc = alloc(&p, cnt)) != BB_OK) return rc
     A_(d.slots, n);
-    A_(d.hdr, n * cap);
-    A_(d.stat, n * cap);
-    A_(d.req_count, 1);
-    A_(d.active, 1);
+    A_(d.nodes, n * 2 * cap);
+    A_(d.path, n * PATH_LEN);
+    A_(d.ctl, 1);
     A_(d.req_slot, n);
     A_(d.req_state, n);
     A_(d.resp_policy, n * G::A);
@@ -164,7 +167,9 @@ struct EngineT : bb_engine {
 #undef A_
     BB_CUDA(cudaMemset(d.counters, 0, sizeof(Counters)));
     BB_CUDA(cudaMemset(d.rec_off, 0, n * (c.max_plies + 2) * sizeof(uint32_t)));
-    BB_CUDA(cudaMallocHost(&host_flags, 4 * sizeof(int)));
+    BB_CUDA(cudaMemset(d.ctl, 0, sizeof(TickCtl)));
+    BB_CUDA(cudaMallocHost(&snap, 2 * sizeof(Snap)));
+    for (int i = 0; i < 2; ++i) BB_CUDA(cudaEventCreateWithFlags(&snap_ev[i], cudaEventDisableTiming));
     d.uniforms = uniforms_dev;
     return reset(nullptr);
   }
@@ -174,12 +179,13 @@ struct EngineT : bb_engine {
     for (void* p : allocs) cudaFree(p);
     for (cudaEvent_t e : prof_ev) cudaEventDestroy(e);
     if (scratch) cudaFree(scratch);
-    if (host_flags) cudaFreeHost(host_flags);
+    if (snap) cudaFreeHost(snap);
+    for (int i = 0; i < 2; ++i) if (snap_ev[i]) cudaEventDestroy(snap_ev[i]);
     if (net) net_destroy(net);
     if (stream) cudaStreamDestroy(stream);
   }
 
-  unsigned warp_grid() const { return grid_for((long long)d.n_games * 32, 128); }
+  unsigned warp_grid() const { return grid_for((long long)d.n_games * 32, 32 * WARPS_PER_CTA); }
 
   int net_load(const bb_net_desc* nd, const float* w, size_t nfl) override {
     BB_CUDA(cudaSetDevice(cfg.device));
@@ -205,33 +211,33 @@ struct EngineT : bb_engine {
   int begin_move(int play_limit) override { return begin_move_budget(play_limit, -1); }
   int begin_move_budget(int play_limit, int moves_budget) {
     if (play_limit <= 0) { set_error("play_limit must be > 0"); return BB_EINVAL; }
-    k_begin_move<G><<<warp_grid(), 128, 0, stream>>>(d, play_limit, moves_budget);
+    k_begin_move<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(d, play_limit, moves_budget);
     BB_CUDA(cudaGetLastError());
     return BB_OK;
   }
 
-  // one tick = advance kernel (+ evaluator kernel)
+  // one tick = advance kernel + evaluator kernel; request counters alternate by tick parity
   int tick() {
-    BB_CUDA(cudaMemsetAsync(d.req_count, 0, sizeof(int), stream));
-    BB_CUDA(cudaMemsetAsync(d.active, 0, sizeof(int), stream));
     const bool timed = prof && prof_used + 3 <= prof_ev.size();
     if (timed) cudaEventRecord(prof_ev[prof_used], stream);
-    k_advance<G><<<warp_grid(), 128, 0, stream>>>(d);
+    k_advance<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(d, par);
     BB_CUDA(cudaGetLastError());
     if (timed) cudaEventRecord(prof_ev[prof_used + 1], stream);
     host_ticks++;
     host_launches++;
+    const int* count = &d.ctl->req[par];
     if (cfg.evaluator == BB_EVAL_KAT) {
-      int rc = launch_kat(G::ID, d.req_state, d.n_games, d.req_count, d.resp_policy, d.resp_value, stream);
+      int rc = launch_kat(G::ID, d.req_state, d.n_games, count, d.resp_policy, d.resp_value, stream);
       if (rc) return rc;
       host_launches++;
     } else if (cfg.evaluator == BB_EVAL_NET) {
       if (!net) { set_error("evaluator is BB_EVAL_NET but no network is loaded"); return BB_ESTATE; }
-      int rc = net_forward(net, d.req_state, d.n_games, d.req_count, d.resp_policy, d.resp_value, stream);
+      int rc = net_forward(net, d.req_state, d.n_games, count, d.resp_policy, d.resp_value, stream);
       if (rc) return rc;
       host_launches++;
     }
     if (timed) { cudaEventRecord(prof_ev[prof_used + 2], stream); prof_used += 3; }
+    par ^= 1u;
     return BB_OK;
   }
   int profile(int enable, int max_ticks) override {
@@ -259,10 +265,37 @@ struct EngineT : bb_engine {
     if (ticks) *ticks = (int)(prof_used / 3);
     return BB_OK;
   }
-  int read_flags() {
-    BB_CUDA(cudaMemcpyAsync(&host_flags[0], d.active, sizeof(int), cudaMemcpyDeviceToHost, stream));
-    BB_CUDA(cudaMemcpyAsync(&host_flags[1], d.req_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
-    BB_CUDA(cudaStreamSynchronize(stream));
+  // snapshot of the control block after the ticks enqueued so far (async; wait on snap_ev[i])
+  int post_snapshot(int i) {
+    snap[i].par = par ^ 1u;                                    // parity of the last enqueued tick
+    BB_CUDA(cudaMemcpyAsync(&snap[i].ctl, d.ctl, sizeof(TickCtl), cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaMemcpyAsync(&snap[i].moves, &d.counters->moves, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaEventRecord(snap_ev[i], stream));
+    return BB_OK;
+  }
+  int wait_snapshot(int i) {
+    BB_CUDA(cudaEventSynchronize(snap_ev[i]));
+    last_active = snap[i].ctl.active[snap[i].par];
+    last_req = snap[i].ctl.req[snap[i].par];
+    return BB_OK;
+  }
+  // Tick until `done(snapshot index)` holds.  Bursts are double-buffered: the next burst is
+  // already queued while the host waits for the previous snapshot, so the GPU never idles on the
+  // host round trip (the price is one surplus burst of near-empty ticks at the end).
+  template <class Done>
+  int tick_until(Done done) {
+    const int burst = 16;
+    int rc, i = 0;
+    for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
+    if ((rc = post_snapshot(0))) return rc;
+    for (;;) {
+      for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
+      if ((rc = post_snapshot(i ^ 1))) return rc;
+      if ((rc = wait_snapshot(i))) return rc;
+      if (done(i)) break;
+      i ^= 1;
+    }
+    if ((rc = wait_snapshot(i ^ 1))) return rc;
     return BB_OK;
   }
   int run(int* pending) override {
@@ -270,19 +303,14 @@ struct EngineT : bb_engine {
     int rc;
     if (cfg.evaluator == BB_EVAL_EXTERNAL) {
       if ((rc = tick())) return rc;
-      if ((rc = read_flags())) return rc;
-      if (pending) *pending = host_flags[1];
+      if ((rc = post_snapshot(0))) return rc;
+      if ((rc = wait_snapshot(0))) return rc;
+      if (pending) *pending = last_req;
       return BB_OK;
     }
-    const int burst = 8;
-    for (;;) {
-      for (int i = 0; i < burst; ++i)
-        if ((rc = tick())) return rc;
-      if ((rc = read_flags())) return rc;
-      if (host_flags[0] == 0) break;
-    }
+    rc = tick_until([&](int i) { return snap[i].ctl.active[snap[i].par] == 0; });
     if (pending) *pending = 0;
-    return BB_OK;
+    return rc;
   }
 
   int root_stats(int kmax, int32_t* nch, int32_t* act, uint32_t* pl, float* cv, double* cp, uint32_t* rp, double* rv,
@@ -301,7 +329,7 @@ struct EngineT : bb_engine {
     uint32_t* d_rp = (uint32_t*)p; p += n * 4;
     int32_t* d_hp = (int32_t*)p; p += n * 4;
     BB_CUDA(cudaMemsetAsync(scratch, 0, bytes, stream));
-    k_root_stats<G><<<warp_grid(), 128, 0, stream>>>(d, kmax, d_nch, d_act, d_pl, d_cv, d_cp, d_rp, d_rv, d_hp);
+    k_root_stats<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(d, kmax, d_nch, d_act, d_pl, d_cv, d_cp, d_rp, d_rv, d_hp);
     BB_CUDA(cudaGetLastError());
 #define D2H(dst, src, b) if (dst) BB_CUDA(cudaMemcpyAsync(dst, src, b, cudaMemcpyDeviceToHost, stream))
     D2H(nch, d_nch, n * 4); D2H(act, d_act, nk * 4); D2H(pl, d_pl, nk * 4); D2H(cv, d_cv, nk * 4);
@@ -320,7 +348,7 @@ struct EngineT : bb_engine {
       if (!u_host) { set_error("temp 1 needs one uniform per slot"); return BB_EINVAL; }
       BB_CUDA(cudaMemcpyAsync(d_u, u_host, n * 8, cudaMemcpyHostToDevice, stream));
     }
-    k_choose<G><<<warp_grid(), 128, 0, stream>>>(d, temp == 1.0 ? 1 : 0, d_u, d_a);
+    k_choose<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(d, temp == 1.0 ? 1 : 0, d_u, d_a);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaMemcpyAsync(actions_host, d_a, n * 4, cudaMemcpyDeviceToHost, stream));
     BB_CUDA(cudaStreamSynchronize(stream));
@@ -333,7 +361,7 @@ struct EngineT : bb_engine {
     BB_CUDA(cudaMemcpyAsync(scratch, actions_host, n * 4, cudaMemcpyHostToDevice, stream));
     EngineDev<G> e = d;
     e.autoplay = 0;
-    k_move_root<G><<<warp_grid(), 128, 0, stream>>>(e, (const int32_t*)scratch);
+    k_move_root<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(e, (const int32_t*)scratch);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));
     return BB_OK;
@@ -362,15 +390,13 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int eval_pending(int32_t* n_host, const int32_t** slots, const void** sts) override {
-    int rc = read_flags();
-    if (rc) return rc;
-    *n_host = host_flags[1];
+    *n_host = last_req;
     if (slots) *slots = d.req_slot;
     if (sts) *sts = d.req_state;
     return BB_OK;
   }
   int eval_fetch(void* sts, int32_t* slots) override {
-    int n = host_flags[1];
+    int n = last_req;
     if (n <= 0) return BB_OK;
     if (sts) BB_CUDA(cudaMemcpyAsync(sts, d.req_state, (size_t)n * sizeof(State), cudaMemcpyDeviceToDevice, stream));
     if (slots) BB_CUDA(cudaMemcpyAsync(slots, d.req_slot, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
@@ -378,7 +404,7 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int eval_submit(const float* pol, const float* val) override {
-    int n = host_flags[1];
+    int n = last_req;
     if (n <= 0) return BB_OK;
     BB_CUDA(cudaStreamSynchronize(stream));
     BB_CUDA(cudaMemcpyAsync(d.resp_policy, pol, (size_t)n * G::A * 4, cudaMemcpyDeviceToDevice, stream));
@@ -417,6 +443,29 @@ struct EngineT : bb_engine {
     d.temp_mode = temp == 1.0 ? 1 : 0;
     int rc = begin_move_budget(play_limit, n_moves);
     if (!rc) rc = run(nullptr);
+    d.autoplay = 0;
+    d.refill = 0;
+    return rc;
+  }
+  // steady state without a per-move barrier: slots keep playing (and restarting) until the engine
+  // as a whole has played target_moves further moves; slots are left mid-search
+  int stream_moves(long long target_moves, int play_limit, double temp, const double* u_host) override {
+    if (temp != 1.0 && temp != 0.0) { set_error("bb_selfplay_stream supports temp 1 and 0; got %g", temp); return BB_EINVAL; }
+    if (cfg.evaluator == BB_EVAL_EXTERNAL) { set_error("bb_selfplay_stream needs a device evaluator"); return BB_EINVAL; }
+    if (target_moves <= 0) { set_error("target_moves must be > 0"); return BB_EINVAL; }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    if (u_host) BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
+    d.autoplay = 1;
+    d.refill = 1;
+    d.play_limit = play_limit;
+    d.temp_mode = temp == 1.0 ? 1 : 0;
+    int rc = begin_move_budget(play_limit, -1);
+    if (!rc) rc = post_snapshot(0);
+    if (!rc) rc = wait_snapshot(0);
+    if (!rc) {
+      const unsigned long long goal = snap[0].moves + (unsigned long long)target_moves;
+      rc = tick_until([&](int i) { return snap[i].moves >= goal || snap[i].ctl.active[snap[i].par] == 0; });
+    }
     d.autoplay = 0;
     d.refill = 0;
     return rc;
@@ -508,6 +557,10 @@ int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* u) 
 int bb_selfplay_step(bb_engine* e, int n_moves, int play_limit, double temp, const double* u) {
   BB_NEED(e);
   return e->step(n_moves, play_limit, temp, u);
+}
+int bb_selfplay_stream(bb_engine* e, long long target_moves, int play_limit, double temp, const double* u) {
+  BB_NEED(e);
+  return e->stream_moves(target_moves, play_limit, temp, u);
 }
 int bb_profile_enable(bb_engine* e, int enable, int max_ticks) { BB_NEED(e); return e->profile(enable, max_ticks); }
 int bb_profile_read(bb_engine* e, double* adv_ms, double* eval_ms, int* ticks) { BB_NEED(e); return e->profile_read(adv_ms, eval_ms, ticks); }

@@ -1,12 +1,28 @@
-// Warp-cooperative search steps: PUCT select, expand, backup, final move choice, root motion.
+// Warp-cooperative search steps: PUCT select, expand, backup, final move choice, subtree copy.
 // One warp per game slot; all control variables are warp-uniform.  IEEE arithmetic is spelled out
 // with _rn intrinsics so nvcc cannot contract to FMA (numpy does not fuse).
 #pragma once
 #include "tree.cuh"
+#ifdef BB_DEBUG
+#include <assert.h>
+#define BB_ASSERT(c) assert(c)
+#else
+#define BB_ASSERT(c) ((void)0)
+#endif
 
 namespace bb {
 
 __constant__ PairwisePlan c_plan[3];   // indexed by G::ID
+
+constexpr int WARPS_PER_CTA = 4;       // k_advance block = 128 threads
+constexpr int STAGE_MAX = 128;         // children staged in shared memory per expansion
+
+struct WarpScratch {                   // per-warp shared memory
+  double prior[STAGE_MAX];             // unnormalised priors of the children being created
+  uint16_t action[STAGE_MAX];
+  uint32_t scan[33];                   // subtree copy: exclusive scan of child counts
+  uint32_t obase[32];                  // subtree copy: old child_base per scanned node
+};
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
@@ -16,30 +32,51 @@ __device__ __forceinline__ int nth_bit(uint64_t m, int j) {
   return ctz64(m);
 }
 
+__device__ __forceinline__ NodeHdr shfl_hdr(const NodeHdr& h, int src) {
+  NodeHdr r;
+  r.parent = __shfl_sync(0xFFFFFFFFu, h.parent, src);
+  r.child_base = __shfl_sync(0xFFFFFFFFu, h.child_base, src);
+  r.meta = __shfl_sync(0xFFFFFFFFu, h.meta, src);
+  r.eval = __shfl_sync(0xFFFFFFFFu, h.eval, src);
+  return r;
+}
+
 // ---- a23: _selectAction(exploring=True), MCTS.py:327-334 --------------------------------------
 // U_i = W_i + ((c * P_i) * sqrt(1 + sum N)) / (1 + N_i) in f64, W_i = f32(Value)/f32(Plays) widened;
 // first maximal index.  Children are stored in ascending action order, so "first" is preserved.
-// Returns child index j (warp-uniform); *best_u receives U_j.
-__device__ __forceinline__ int puct_select(const NodeStat* kids, int k, double c, double* best_u) {
+// Lane j loads child j's whole 32-byte record, so the winner's header (its own child block, action,
+// cached value) arrives with the same memory round trip.  Returns the child index (warp-uniform);
+// *best_u receives U_j and *chosen the winner's header.
+template <int CHUNKS>
+__device__ __forceinline__ int puct_select(const Node* kids, int k, double c, double* best_u, NodeHdr* chosen) {
   const int lane = lane_id();
-  NodeStat first = {0u, 0.f, 0.0};
+  Node r[CHUNKS];
   uint32_t tot = 0;
-  for (int j = lane; j < k; j += 32) {
-    NodeStat s = kids[j];
-    if (j < 32) first = s;
-    tot += s.plays;
+#pragma unroll
+  for (int ci = 0; ci < CHUNKS; ++ci) {
+    const int j = ci * 32 + lane;
+    if (j < k) {
+      r[ci] = kids[j];
+      tot += r[ci].s.plays;
+    }
   }
+  for (int j = CHUNKS * 32 + lane; j < k; j += 32) tot += kids[j].s.plays;
 #pragma unroll
   for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
   const double t = __dsqrt_rn(__dadd_rn(1.0, (double)tot));   // exact integer sum (builtin sum of f64 ints)
   double bu = -1.0;
   int bj = 0x7FFFFFFF;
-  for (int j = lane; j < k; j += 32) {
-    NodeStat s = (j < 32) ? first : kids[j];
-    float wr = s.plays > 0 ? __fdiv_rn(s.value, (float)s.plays) : 0.f;          // Node.WinRate, f32 (A.9)
+  auto score = [&](const NodeStat& s, int j) {
+    float wr = s.plays > 0 ? __fdiv_rn(s.value, (float)s.plays) : 0.f;            // Node.WinRate, f32 (A.9)
     double u = __dadd_rn((double)wr, __ddiv_rn(__dmul_rn(__dmul_rn(c, s.prior), t), __dadd_rn(1.0, (double)s.plays)));
     if (u > bu) { bu = u; bj = j; }
+  };
+#pragma unroll
+  for (int ci = 0; ci < CHUNKS; ++ci) {
+    const int j = ci * 32 + lane;
+    if (j < k) score(r[ci].s, j);
   }
+  for (int j = CHUNKS * 32 + lane; j < k; j += 32) score(kids[j].s, j);
 #pragma unroll
   for (int o = 16; o; o >>= 1) {
     double ou = __shfl_xor_sync(0xFFFFFFFFu, bu, o);
@@ -47,28 +84,45 @@ __device__ __forceinline__ int puct_select(const NodeStat* kids, int k, double c
     if (ou > bu || (ou == bu && oj < bj)) { bu = ou; bj = oj; }
   }
   *best_u = bu;
+  if (bj != 0x7FFFFFFF) {
+    const int chunk = bj >> 5;
+    if (chunk < CHUNKS) {
+      NodeHdr mine = r[0].h;
+#pragma unroll
+      for (int ci = 1; ci < CHUNKS; ++ci)
+        if (ci == chunk) mine = r[ci].h;
+      *chosen = shfl_hdr(mine, bj & 31);
+    } else {
+      *chosen = kids[bj].h;
+    }
+  }
   return bj;
 }
 
-// ---- a26: priors = f32 policy * f64 mask, / np.sum(...) with numpy's pairwise order (A.11) ------
-// Lane 0 walks the k sparse (action, numerator) pairs in ascending action order through the
-// host-built plan; zeros at illegal indices are identities and are skipped.
 template <class G>
-__device__ double pairwise_sum_sparse(const NodeHdr* khdr, const NodeStat* kstat, int k) {
+struct SelectChunks { static constexpr int N = G::A <= 32 ? 1 : 4; };
+
+// ---- a26: priors = f32 policy * f64 mask, / np.sum(...) with numpy's pairwise order (A.11) ------
+// One lane walks the k sparse (action, numerator) pairs in ascending action order through the
+// host-built plan; zeros at illegal indices are identities and are skipped.  get(j, &action)
+// returns the j-th numerator.
+template <class G, class Get>
+__device__ double pairwise_sum_sparse(int k, Get get) {
   const PairwisePlan& P = c_plan[G::ID];
-  double leaf_sum[PW_MAX_LEAVES];
+  constexpr int NL = G::A <= 128 ? 1 : PW_MAX_LEAVES;     // A <= 128 is a single leaf
+  double leaf_sum[NL];
   int j = 0;
+  int a = 0;
+  double v = 0.0;
+  if (k > 0) v = get(0, &a);
   for (int L = 0; L < P.n_leaves; ++L) {
     const int lo = P.leaf_lo[L], n = P.leaf_n[L];
     const int nfull = n < 8 ? 0 : n - (n & 7);
     double r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double res = 0.0;
     bool combined = false;
-    while (j < k) {
-      int a = meta_action(khdr[j].meta);
-      if (a >= lo + n) break;
-      double v = kstat[j].prior;
-      int i = a - lo;
+    while (j < k && a < lo + n) {
+      const int i = a - lo;
       if (i < nfull) {
         r[i & 7] = __dadd_rn(r[i & 7], v);
       } else {
@@ -80,12 +134,14 @@ __device__ double pairwise_sum_sparse(const NodeHdr* khdr, const NodeStat* kstat
         res = __dadd_rn(res, v);
       }
       ++j;
+      if (j < k) v = get(j, &a);
     }
     if (!combined)
       res = nfull ? __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
                               __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7]))) : 0.0;
     leaf_sum[L] = res;
   }
+  if (NL == 1) return leaf_sum[0];
   double stack[16];
   int sp = 0;
   for (int i = 0; i < P.n_ops; ++i) {
@@ -98,89 +154,168 @@ __device__ double pairwise_sum_sparse(const NodeHdr* khdr, const NodeStat* kstat
 
 // ---- a22: AddChildren (MCTS.py:122-139), lazily evaluated ---------------------------------------
 // Creates the k children of `node` (ascending action id) with Plays 0, Value 0 and
-// prior = f64(policy[a]) / sum.  Returns k, or -1 when the arena is full.
+// prior = f64(policy[a]) / sum.  Updates *node_hdr (and its copy in HBM).  Returns k, or -1 when
+// the half-arena is full.
 template <class G>
-__device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, NodeHdr* hdr, NodeStat* stat, uint32_t node,
-                           const float* policy) {
+__device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint32_t node, NodeHdr* node_hdr,
+                           const float* policy, WarpScratch& ws) {
   const int lane = lane_id();
-  constexpr int RPL = (G::NROWS + 31) / 32;             // action rows per lane
-  uint64_t m[RPL];
-  int cnt = 0;
-#pragma unroll
-  for (int r = 0; r < RPL; ++r) {
-    int row = lane * RPL + r;
-    m[r] = row < G::NROWS ? G::legal_row(s.cur_state, row) : 0ull;
-    cnt += popc64(m[r]);
-  }
-  int incl = cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if (lane >= o) incl += v;
-  }
-  const int k = __shfl_sync(0xFFFFFFFFu, incl, 31);
   const uint32_t base = s.n_nodes;
-  if (base + (uint32_t)k > E.node_cap) return -1;
-  int j = incl - cnt;
-#pragma unroll
-  for (int r = 0; r < RPL; ++r) {
-    uint64_t mm = m[r];
-    const int row = lane * RPL + r;
-    while (mm) {
-      int bit = ctz64(mm);
-      mm &= mm - 1;
-      int a = G::action_of(row, bit);
-      NodeHdr h;
-      h.parent = node;
-      h.child_base = NONE;
-      h.meta = meta_pack(a, 0, G::next_player(s.cur_state), false);
-      h.eval = 0.f;
-      hdr[base + j] = h;
-      NodeStat st;
-      st.plays = 0u;
-      st.value = 0.f;
-      st.prior = (double)policy[a];                       // f32 policy * 1.0 (f64 mask)
-      stat[base + j] = st;
-      ++j;
+  const int child_player = G::next_player(s.cur_state);
+  int k;
+  if (G::NROWS == 1) {
+    // small action spaces: the legal mask is warp-uniform, lane j creates the j-th child
+    const uint64_t m = G::legal_row(s.cur_state, 0);
+    k = popc64(m);
+    if (base + (uint32_t)k > E.node_cap) return -1;
+    int a = 0;
+    double p = 0.0;
+    if (lane < k) {
+      a = nth_bit(m, lane);
+      p = (double)policy[a];                                // f32 policy * 1.0 (f64 mask)
+      ws.prior[lane] = p;
+      ws.action[lane] = (uint16_t)a;
     }
+    __syncwarp();
+    double sum = 0.0;
+    if (lane == 0)
+      sum = pairwise_sum_sparse<G>(k, [&](int j, int* act) { *act = ws.action[j]; return ws.prior[j]; });
+    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+    if (lane < k) {
+      Node n;
+      n.s.plays = 0u;
+      n.s.value = 0.f;
+      n.s.prior = __ddiv_rn(p, sum);
+      n.h.parent = node;
+      n.h.child_base = NONE;
+      n.h.meta = meta_pack(a, 0, child_player, false);
+      n.h.eval = 0.f;
+      nodes[base + lane] = n;
+    }
+  } else {
+    constexpr int RPL = (G::NROWS + 31) / 32;             // action rows per lane
+    uint64_t m[RPL];
+    int cnt = 0;
+#pragma unroll
+    for (int r = 0; r < RPL; ++r) {
+      int row = lane * RPL + r;
+      m[r] = row < G::NROWS ? G::legal_row(s.cur_state, row) : 0ull;
+      cnt += popc64(m[r]);
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    k = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (base + (uint32_t)k > E.node_cap) return -1;
+    const bool staged = k <= STAGE_MAX;
+    int j = incl - cnt;
+#pragma unroll
+    for (int r = 0; r < RPL; ++r) {
+      uint64_t mm = m[r];
+      const int row = lane * RPL + r;
+      while (mm) {
+        int bit = ctz64(mm);
+        mm &= mm - 1;
+        int a = G::action_of(row, bit);
+        Node n;
+        n.s.plays = 0u;
+        n.s.value = 0.f;
+        n.s.prior = (double)policy[a];
+        n.h.parent = node;
+        n.h.child_base = NONE;
+        n.h.meta = meta_pack(a, 0, child_player, false);
+        n.h.eval = 0.f;
+        nodes[base + j] = n;
+        if (staged) { ws.prior[j] = n.s.prior; ws.action[j] = (uint16_t)a; }
+        ++j;
+      }
+    }
+    __syncwarp();
+    double sum = 0.0;
+    if (lane == 0) {
+      if (staged) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
+      else sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = meta_action(nodes[base + q].h.meta); return nodes[base + q].s.prior; });
+    }
+    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+    for (int i = lane; i < k; i += 32)
+      nodes[base + i].s.prior = __ddiv_rn(staged ? ws.prior[i] : nodes[base + i].s.prior, sum);
   }
-  __syncwarp();
-  double sum = 0.0;
-  if (lane == 0) sum = pairwise_sum_sparse<G>(hdr + base, stat + base, k);
-  sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
-  for (int i = lane; i < k; i += 32) stat[base + i].prior = __ddiv_rn(stat[base + i].prior, sum);
-  if (lane == 0) {
-    NodeHdr h = hdr[node];
-    h.child_base = base;
-    h.meta = (h.meta & ~(0x3FFu << 12)) | ((uint32_t)k << 12);
-    hdr[node] = h;
-  }
+  node_hdr->child_base = base;
+  node_hdr->meta = (node_hdr->meta & ~(0x3FFu << 12)) | ((uint32_t)k << 12);
+  if (lane == 0) nodes[node].h = *node_hdr;
   s.n_nodes = base + (uint32_t)k;
   __syncwarp();
   return k;
 }
 
+// ---- descent path: warp-distributed array, entry d = node id | (player to move at it - 1) << 31 --
+struct Path {
+  uint32_t r[PATH_LEN / 32];           // lane l holds entries l, 32 + l, ...
+  __device__ __forceinline__ void set(int d, uint32_t node, int player) {
+    if (d < PATH_LEN && lane_id() == (d & 31)) {
+#pragma unroll
+      for (int c = 0; c < PATH_LEN / 32; ++c)
+        if (c == (d >> 5)) r[c] = node | ((uint32_t)(player - 1) << 31);
+    }
+  }
+  __device__ __forceinline__ void load(const uint32_t* row) {
+#pragma unroll
+    for (int c = 0; c < PATH_LEN / 32; ++c) r[c] = row[c * 32 + lane_id()];
+  }
+  __device__ __forceinline__ void store(uint32_t* row) const {
+#pragma unroll
+    for (int c = 0; c < PATH_LEN / 32; ++c) row[c * 32 + lane_id()] = r[c];
+  }
+};
+
 // ---- a27 + a28: SampleValue transform (Blackbird.py:365-368) and _backProp (MCTS.py:238-258) -----
+// Every node on the path gets Plays += 1 and (if it has a parent) Value += v or 1 - v depending on
+// whether the PARENT's side to move is playerForValue.  The path is in registers, so all the
+// read-modify-writes are independent and issue in one memory round trip (lane d owns depth d).
+// Ancestors above Root are never read again in self-play (A.13) and are not kept.
 template <class G>
-__device__ void backup(const EngineDev<G>& E, const Slot<G>& s, NodeHdr* hdr, NodeStat* stat, float eval) {
-  if (lane_id() == 0) {
-    float v = __fmul_rn(__fadd_rn(eval, 1.0f), 0.5f);       // (value + 1) * 0.5 in f32
-    const int p = G::prev(s.cur_state);                      // playerForValue = PreviousPlayer (0 = None)
-    if (G::player(s.cur_state) != p) v = __fsub_rn(1.0f, v);
-    const float flip = __fsub_rn(1.0f, v);
-    uint32_t m = s.cur;
-    for (;;) {
-      NodeStat st = stat[m];
-      st.plays += 1;
-      int parent_player;
-      uint32_t parent = NONE;
-      if (m == s.root) parent_player = s.root_parent_player;   // ancestors above Root are never read again (A.13)
-      else { parent = hdr[m].parent; parent_player = meta_player(hdr[parent].meta); }
-      if (parent_player != 0) st.value = __fadd_rn(st.value, parent_player == p ? v : flip);
-      stat[m].plays = st.plays;
-      stat[m].value = st.value;
-      if (m == s.root) break;
-      m = parent;
+__device__ void backup(const Slot<G>& s, Node* nodes, const Path& path, float eval) {
+  const int lane = lane_id();
+  float v = __fmul_rn(__fadd_rn(eval, 1.0f), 0.5f);         // (value + 1) * 0.5 in f32
+  const int p = G::prev(s.cur_state);                        // playerForValue = PreviousPlayer (0 = None)
+  if (G::player(s.cur_state) != p) v = __fsub_rn(1.0f, v);
+  const float flip = __fsub_rn(1.0f, v);
+  int d = s.depth;
+  if (d >= PATH_LEN) {                                       // deeper than the register path: walk parents
+    if (lane == 0) {
+      uint32_t m = s.cur;
+      while (d >= PATH_LEN) {
+        const uint32_t parent = nodes[m].h.parent;
+        const int pp = meta_player(nodes[parent].h.meta);
+        NodeStat st = nodes[m].s;
+        nodes[m].s.plays = st.plays + 1;
+        nodes[m].s.value = __fadd_rn(st.value, pp == p ? v : flip);
+        m = parent;
+        --d;
+      }
+    }
+    d = PATH_LEN - 1;
+    __syncwarp();
+  }
+  uint32_t carry = 0;                                        // entry of depth 32*c - 1
+#pragma unroll
+  for (int c = 0; c < PATH_LEN / 32; ++c) {
+    const uint32_t e = path.r[c];
+    uint32_t up = __shfl_up_sync(0xFFFFFFFFu, e, 1);
+    if (lane == 0) up = carry;
+    carry = __shfl_sync(0xFFFFFFFFu, e, 31);
+    const int idx = c * 32 + lane;
+    if (idx <= d) {
+      const int parent_player = idx == 0 ? s.root_parent_player : 1 + (int)(up >> 31);
+      BB_ASSERT((e & 0x7FFFFFFFu) < s.n_nodes);
+      uint2* q = reinterpret_cast<uint2*>(&nodes[e & 0x7FFFFFFFu].s);
+      uint2 w = *q;                                          // (plays, value)
+      w.x += 1;
+      if (parent_player != 0) w.y = __float_as_uint(__fadd_rn(__uint_as_float(w.y), parent_player == p ? v : flip));
+      *q = w;
     }
   }
   __syncwarp();
@@ -188,21 +323,84 @@ __device__ void backup(const EngineDev<G>& E, const Slot<G>& s, NodeHdr* hdr, No
 
 // ---- a31: _selectAction(exploring=False), MCTS.py:335-338, temp == 1 -----------------------------
 // p_i = plays_i / sum(plays); np.random.choice == searchsorted(cumsum(p)/cumsum(p)[-1], u, 'right') (A.15)
-__device__ __forceinline__ int sample_child(const NodeStat* kids, int k, double u) {
+__device__ __forceinline__ int sample_child(const Node* kids, int k, double u) {
   int pick = 0;
   if (lane_id() == 0) {
     double tot = 0.0;
-    for (int j = 0; j < k; ++j) tot = __dadd_rn(tot, (double)kids[j].plays);
+    for (int j = 0; j < k; ++j) tot = __dadd_rn(tot, (double)kids[j].s.plays);
     double last = 0.0;
-    for (int j = 0; j < k; ++j) last = __dadd_rn(last, __ddiv_rn((double)kids[j].plays, tot));
+    for (int j = 0; j < k; ++j) last = __dadd_rn(last, __ddiv_rn((double)kids[j].s.plays, tot));
     double run = 0.0;
     pick = k - 1;
     for (int j = 0; j < k; ++j) {
-      run = __dadd_rn(run, __ddiv_rn((double)kids[j].plays, tot));
+      run = __dadd_rn(run, __ddiv_rn((double)kids[j].s.plays, tot));
       if (__ddiv_rn(run, last) > u) { pick = j; break; }
     }
   }
   return __shfl_sync(0xFFFFFFFFu, pick, 0);
+}
+
+// ---- a32: MoveRoot (MCTS.py:260-282) as a breadth-first subtree copy into the other half ---------
+// dst[0] = the new root; then, scanning dst in order, every node that has children gets a fresh
+// contiguous block at the end of dst and its children are copied there (ascending action order
+// is kept, statistics verbatim).  Up to `rounds` scans of 32 nodes per call so one tick's latency
+// stays bounded; returns true when the copy is complete.
+template <class G>
+__device__ bool subtree_copy(const EngineDev<G>& E, Slot<G>& s, const Node* __restrict__ src, Node* __restrict__ dst,
+                             WarpScratch& ws, int rounds) {
+  const int lane = lane_id();
+  if (s.cp_n == 0) {
+    if (lane == 0) {
+      BB_ASSERT(s.cp_src < s.n_nodes);
+      Node r = src[s.cp_src];
+      r.h.parent = NONE;
+      dst[0] = r;
+    }
+    s.cp_n = 1;
+    s.cp_head = 0;
+    __syncwarp();
+  }
+  for (int it = 0; it < rounds && s.cp_head < s.cp_n; ++it) {
+    const uint32_t i = s.cp_head + lane;
+    const bool valid = i < s.cp_n;
+    NodeHdr h;
+    h.child_base = NONE;
+    h.meta = 0;
+    if (valid) h = dst[i].h;
+    const uint32_t k = (valid && h.child_base != NONE) ? (uint32_t)meta_nchild(h.meta) : 0u;
+    uint32_t incl = k;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (s.cp_n + total > E.node_cap) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; return true; }
+    ws.scan[lane] = incl - k;
+    ws.obase[lane] = h.child_base;
+    if (lane == 31) ws.scan[32] = total;
+    if (k) {                                                 // re-point this node at its new block
+      h.child_base = s.cp_n + (incl - k);
+      dst[i].h = h;
+    }
+    __syncwarp();
+    for (uint32_t e = lane; e < total; e += 32) {            // flattened copy: every load independent
+      int lo = 0, hi = 31;                                   // last owner with scan[owner] <= e and k > 0
+      while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (ws.scan[mid] <= e) lo = mid; else hi = mid - 1;
+      }
+      const uint32_t off = e - ws.scan[lo];
+      BB_ASSERT(ws.obase[lo] + off < s.n_nodes && off < 1024 && s.cp_n + e < E.node_cap);
+      Node n = src[ws.obase[lo] + off];
+      n.h.parent = s.cp_head + (uint32_t)lo;
+      dst[s.cp_n + e] = n;
+    }
+    __syncwarp();
+    s.cp_head = min(s.cp_head + 32u, s.cp_n);                // only nodes that existed at the start of this round
+    s.cp_n += total;
+  }
+  return s.cp_head >= s.cp_n;
 }
 
 }  // namespace bb

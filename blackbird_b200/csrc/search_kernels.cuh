@@ -7,11 +7,15 @@ namespace bb {
 
 enum { ST_TOP = 0, ST_EXPAND = 1, ST_SELECT = 2, ST_LEAF = 3 };
 
+__device__ __forceinline__ bool phase_busy(int ph) {
+  return ph == BB_PH_RUN || ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF || ph == BB_PH_COMPACT;
+}
+
 template <class G>
-__device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, int g) {
+__device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, int g, unsigned parity) {
   int idx = 0;
   if (lane_id() == 0) {
-    idx = atomicAdd(E.req_count, 1);
+    idx = atomicAdd(&E.ctl->req[parity], 1);
     E.req_slot[idx] = g;
     E.req_state[idx] = s.cur_state;
   }
@@ -19,44 +23,51 @@ __device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, 
 }
 
 template <class G>
-__device__ __forceinline__ void start_descent(Slot<G>& s) {
+__device__ __forceinline__ void start_descent(Slot<G>& s, Path& path) {
   s.cur = s.root;
   s.cur_state = s.root_state;
   s.depth = 0;
   s.last_action = -1;
+  path.set(0, s.root, G::player(s.root_state));
 }
 
 // FindMove prologue (MCTS.py:184-186, 297): make a Root if there is none, fix endPlays.
 template <class G>
-__device__ __forceinline__ void begin_move(const EngineDev<G>& E, Slot<G>& s, NodeHdr* hdr, NodeStat* stat, int play_limit) {
+__device__ __forceinline__ void begin_move(const EngineDev<G>& E, Slot<G>& s, Node* nodes, Path& path, int play_limit) {
+  uint32_t root_plays;
   if (s.root == NONE) {
     if (lane_id() == 0) {
-      NodeHdr h;
-      h.parent = NONE;
-      h.child_base = NONE;
-      h.meta = meta_pack(0, 0, G::player(s.root_state), false);
-      h.eval = 0.f;
-      hdr[0] = h;
-      NodeStat st = {0u, 0.f, 0.0};
-      stat[0] = st;
+      Node n;
+      n.s.plays = 0u;
+      n.s.value = 0.f;
+      n.s.prior = 0.0;
+      n.h.parent = NONE;
+      n.h.child_base = NONE;
+      n.h.meta = meta_pack(0, 0, G::player(s.root_state), false);
+      n.h.eval = 0.f;
+      nodes[0] = n;
     }
     __syncwarp();
     s.root = 0;
     s.n_nodes = 1;
     s.root_parent_player = 0;
+    root_plays = 0;
+  } else {
+    root_plays = nodes[s.root].s.plays;
   }
-  s.end_plays = stat[s.root].plays + (uint32_t)play_limit;
+  s.root_plays = root_plays;
+  s.end_plays = root_plays + (uint32_t)play_limit;
   s.phase = BB_PH_RUN;
-  start_descent(s);
+  start_descent(s, path);
 }
 
 // Record the searched position, then state = nextState; MoveRoot(state); winner = state.Winner()
-// (Blackbird.py:246-253 and, at game end, :256-258).
+// (Blackbird.py:246-253 and, at game end, :256-258).  A game that goes on enters BB_PH_COMPACT:
+// the chosen child's subtree is copied into the other half-arena (subtree_copy).
 template <class G>
-__device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, NodeHdr* hdr, NodeStat* stat, int child_j,
-                          unsigned long long* games_done) {
+__device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, Node* nodes, int child_j, unsigned long long* games_done) {
   const int lane = lane_id();
-  const NodeHdr rh = hdr[s.root];
+  const NodeHdr rh = nodes[s.root].h;
   const int k = meta_nchild(rh.meta);
   const size_t rbase = (size_t)g * (E.max_plies + 1);
   const size_t obase = (size_t)g * (E.max_plies + 2);
@@ -64,8 +75,9 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, NodeHdr* hdr
   if (E.rec_states) {
     if (s.pool_used + (uint32_t)k > E.pool_cap) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; return; }
     for (int j = lane; j < k; j += 32) {
-      E.pool_actions[pbase + s.pool_used + j] = (uint16_t)meta_action(hdr[rh.child_base + j].meta);
-      E.pool_plays[pbase + s.pool_used + j] = stat[rh.child_base + j].plays;
+      const Node kid = nodes[rh.child_base + j];
+      E.pool_actions[pbase + s.pool_used + j] = (uint16_t)meta_action(kid.h.meta);
+      E.pool_plays[pbase + s.pool_used + j] = kid.s.plays;
     }
     if (lane == 0) {
       E.rec_states[rbase + s.ply] = s.root_state;
@@ -75,11 +87,10 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, NodeHdr* hdr
     s.pool_used += (uint32_t)k;
   }
   const uint32_t child = rh.child_base + (uint32_t)child_j;
-  const int action = meta_action(hdr[child].meta);
+  const int action = meta_action(nodes[child].h.meta);
   if (E.chosen && lane == 0) E.chosen[(size_t)g * E.max_plies + s.ply] = (uint16_t)action;
   s.root_parent_player = G::player(s.root_state);
   G::apply(s.root_state, action);
-  s.root = child;
   s.ply += 1;
   const int w = G::winner(s.root_state, -1);                 // lastAction is always None (Blackbird.py:242,253)
   if (w != WIN_NONE || s.ply >= E.max_plies) {
@@ -92,114 +103,160 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, NodeHdr* hdr
       if (E.winners) E.winners[g] = w;
       *games_done += 1;
     }
+    s.root = child;
     s.winner = w;
     s.phase = BB_PH_GAME_OVER;
   } else {
+    s.cp_src = child;
+    s.cp_n = 0;
+    s.cp_head = 0;
+    s.phase = BB_PH_COMPACT;
+  }
+}
+
+// BB_PH_COMPACT -> BB_PH_MOVE_READY: swap halves once the copy is complete
+template <class G>
+__device__ __forceinline__ void run_compaction(const EngineDev<G>& E, Slot<G>& s, int g, WarpScratch& ws, int rounds) {
+  const bool done = subtree_copy(E, s, E.half(g, s.half), E.half(g, s.half ^ 1u), ws, rounds);
+  if (done && s.phase == BB_PH_COMPACT) {
+    s.half ^= 1u;
+    s.root = 0;
+    s.n_nodes = s.cp_n;
     s.phase = BB_PH_MOVE_READY;
   }
 }
 
-template <class G>
-__global__ void __launch_bounds__(128) k_advance(EngineDev<G> E) {
-  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = lane_id();
-  if (g >= E.n_games) return;
-  Slot<G> s = E.slots[g];
-  if (s.phase != BB_PH_RUN && s.phase != BB_PH_WAIT_EXPAND && s.phase != BB_PH_WAIT_LEAF) return;
-  NodeHdr* hdr = E.hdr + (size_t)g * E.node_cap;
-  NodeStat* stat = E.stat + (size_t)g * E.node_cap;
-  unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0;
+constexpr int COMPACT_ROUNDS_PER_TICK = 8;
 
+template <class G>
+__device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws) {
+  const int lane = lane_id();
+  Slot<G> s = E.slots[g];
+  if (!phase_busy(s.phase)) return;
+  unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0;
+  uint32_t* prow = E.path + (size_t)g * PATH_LEN;
+  Path path;
+  Node* nodes = E.half(g, s.half);
+  NodeHdr ch;
+  ch.parent = NONE; ch.child_base = NONE; ch.meta = 0; ch.eval = 0.f;
   int step = ST_TOP;
-  if (s.phase != BB_PH_RUN) {                                  // an evaluation came back for s.cur
-    if (lane == 0) {
-      NodeHdr h = hdr[s.cur];
-      h.eval = E.resp_value[s.req_idx];
-      h.meta |= META_HAS_VALUE;
-      hdr[s.cur] = h;
-    }
-    __syncwarp();
+  if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) {   // an evaluation came back for s.cur
+    path.load(prow);
+    BB_ASSERT(s.cur < s.n_nodes && s.req_idx < (uint32_t)E.n_games);
+    ch = nodes[s.cur].h;
+    ch.eval = E.resp_value[s.req_idx];
+    ch.meta |= META_HAS_VALUE;
+    if (lane == 0) nodes[s.cur].h = ch;
     step = s.phase == BB_PH_WAIT_EXPAND ? ST_EXPAND : ST_LEAF;
     s.phase = BB_PH_RUN;
+  } else if (s.phase == BB_PH_RUN) {                                   // fresh from k_begin_move
+    path.load(prow);
+    BB_ASSERT(s.cur < s.n_nodes);
+    ch = nodes[s.cur].h;
   }
 
-  while (s.phase == BB_PH_RUN) {
+  for (;;) {
+    if (s.phase == BB_PH_COMPACT) {
+      run_compaction(E, s, g, ws, COMPACT_ROUNDS_PER_TICK);
+      if (s.phase != BB_PH_MOVE_READY || !E.autoplay || s.moves_budget == 0) break;
+      nodes = E.half(g, s.half);
+      begin_move(E, s, nodes, path, E.play_limit);
+      ch = nodes[s.cur].h;
+      step = ST_TOP;
+    }
+    if (s.phase != BB_PH_RUN) break;
     if (step == ST_TOP) {
       if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }     // FixedMCTS.py:23
-      const NodeHdr h = hdr[s.cur];
-      if (h.child_base == NONE) {                               // Children is None
+      if (ch.child_base == NONE) {                              // Children is None
         if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
-        post_request(E, s, g);                                  // GetPriors(state) of this node
+        post_request(E, s, g, par);                             // GetPriors(state) of this node
         n_evals += 1;
         s.phase = BB_PH_WAIT_EXPAND;
         break;
       }
-      step = meta_nchild(h.meta) == 0 ? ST_LEAF : ST_SELECT;    // np.sum(LegalActions) == 0
+      step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
-      const int k = expand_node(E, s, hdr, stat, s.cur, E.resp_policy + (size_t)s.req_idx * G::A);
+      const int k = expand_node(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)s.req_idx * G::A, ws);
       if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
       n_exp += 1;
       n_nodes += k;
       step = (E.search == BB_DYNAMIC || k == 0) ? ST_LEAF : ST_SELECT;                      // DynamicMCTS.py:27-28
     } else if (step == ST_SELECT) {
-      const NodeHdr h = hdr[s.cur];
       double u;
-      const int j = puct_select(stat + h.child_base, meta_nchild(h.meta), E.c, &u);
-      const int a = j == 0x7FFFFFFF ? 0 : meta_action(hdr[h.child_base + j].meta);
+      NodeHdr chosen = ch;
+#ifdef BB_DEBUG
+      if (ch.child_base + (uint32_t)meta_nchild(ch.meta) > s.n_nodes && lane == 0)
+        printf("DBG g=%d cur=%u depth=%d cb=%u nch=%d meta=%x n_nodes=%u ply=%d half=%u root=%u rp=%u cp_n=%u cp_head=%u\n", g, s.cur, s.depth,
+               ch.child_base, meta_nchild(ch.meta), ch.meta, s.n_nodes, s.ply, s.half, s.root, s.root_plays, s.cp_n, s.cp_head);
+#endif
+      BB_ASSERT(ch.child_base + (uint32_t)meta_nchild(ch.meta) <= s.n_nodes);
+      const int j = puct_select<SelectChunks<G>::N>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
+      const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
       // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
       if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
       G::apply(s.cur_state, a);
-      s.cur = h.child_base + (uint32_t)j;
+      s.cur = ch.child_base + (uint32_t)j;
+      ch = chosen;
       s.last_action = a;
       s.depth += 1;
+      path.set(s.depth, s.cur, meta_player(ch.meta));
       n_sel += 1;
       step = ST_TOP;
     } else {                                                    // ST_LEAF: SampleValue + _backProp
-      const NodeHdr h = hdr[s.cur];
-      if (!(h.meta & META_HAS_VALUE)) {
-        post_request(E, s, g);                                  // getEvaluation(state) of the leaf
+      if (!(ch.meta & META_HAS_VALUE)) {
+        post_request(E, s, g, par);                             // getEvaluation(state) of the leaf
         n_evals += 1;
         s.phase = BB_PH_WAIT_LEAF;
         break;
       }
-      backup(E, s, hdr, stat, h.eval);
+      backup(s, nodes, path, ch.eval);
+      s.root_plays += 1;
       n_sims += 1;
-      if (stat[s.root].plays >= s.end_plays) {                  // MCTS.py:298-299
+      if (s.root_plays >= s.end_plays) {                        // MCTS.py:298-299
         s.phase = BB_PH_MOVE_READY;
         if (E.autoplay) {
-          const NodeHdr rh = hdr[s.root];
+          BB_ASSERT(s.root < s.n_nodes);
+          const NodeHdr rh = nodes[s.root].h;
           const int k = meta_nchild(rh.meta);
+          BB_ASSERT(rh.child_base + (uint32_t)k <= s.n_nodes && s.ply < E.max_plies);
           int j;
           if (E.temp_mode == 1) {
             const int row = (int)(((unsigned)g + s.game_no) % (unsigned)E.n_games);   // refill: next game, next row
-            j = sample_child(stat + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
+            j = sample_child(nodes + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
           } else {
             double u;
-            j = puct_select(stat + rh.child_base, k, E.c, &u);
+            NodeHdr dummy;
+            j = puct_select<SelectChunks<G>::N>(nodes + rh.child_base, k, E.c, &u, &dummy);
           }
-          play_move(E, s, g, hdr, stat, j, &n_done);
+          play_move(E, s, g, nodes, j, &n_done);
           n_moves += 1;
           if (s.moves_budget > 0) s.moves_budget -= 1;
           if (s.phase == BB_PH_GAME_OVER && E.refill) {         // Model.Game(); DropRoot() for the next game
             s.game_no += 1;
             s.root_state = G::initial();
             s.root = NONE;
+            s.n_nodes = 0;
             s.ply = 0;
             s.pool_used = 0;
             s.winner = WIN_NONE;
             s.phase = BB_PH_MOVE_READY;
+            if (s.moves_budget != 0) {
+              begin_move(E, s, nodes, path, E.play_limit);
+              ch = nodes[s.cur].h;
+            }
           }
-          if (s.phase == BB_PH_MOVE_READY && s.moves_budget != 0) begin_move(E, s, hdr, stat, E.play_limit);
         }
       } else {
-        start_descent(s);
+        start_descent(s, path);
+        ch = nodes[s.cur].h;
       }
       step = ST_TOP;
     }
   }
+  if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) path.store(prow);
   if (lane == 0) {
     E.slots[g] = s;
-    if (s.phase == BB_PH_RUN || s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) atomicAdd(E.active, 1);
+    if (phase_busy(s.phase)) atomicAdd(&E.ctl->active[par], 1);
     Counters* c = E.counters;
     if (n_sims) atomicAdd(&c->sims, n_sims);
     if (n_evals) atomicAdd(&c->evals, n_evals);
@@ -211,9 +268,34 @@ __global__ void __launch_bounds__(128) k_advance(EngineDev<G> E) {
   }
 }
 
+// One tick.  `par` = tick parity (host-tracked): requests / activity of this tick accumulate in
+// ctl->req[par] / ctl->active[par]; the last CTA to finish clears the other parity for the next tick.
+template <class G>
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_advance(EngineDev<G> E, unsigned par) {
+  __shared__ WarpScratch s_ws[WARPS_PER_CTA];
+  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (g < E.n_games) advance_slot(E, g, par, s_ws[threadIdx.x >> 5]);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned ticket = atomicAdd(&E.ctl->blocks_done, 1u);
+    if (ticket == gridDim.x - 1) {
+      E.ctl->req[par ^ 1u] = 0;
+      E.ctl->active[par ^ 1u] = 0;
+      E.ctl->blocks_done = 0;
+      E.ctl->tick += 1;
+    }
+  }
+}
+
 template <class G>
 __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g == 0) {
+    E.ctl->blocks_done = 0;
+    E.ctl->req[0] = E.ctl->req[1] = 0;
+    E.ctl->active[0] = E.ctl->active[1] = 0;
+  }
   if (g >= E.n_games) return;
   Slot<G> s;
   s.root_state = init ? init[g] : G::initial();
@@ -224,6 +306,7 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.last_action = -1;
   s.n_nodes = 0;
   s.end_plays = 0;
+  s.root_plays = 0;
   s.phase = BB_PH_IDLE;
   s.status = BB_OK;
   s.ply = 0;
@@ -233,6 +316,8 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.pool_used = 0;
   s.moves_budget = -1;
   s.game_no = 0;
+  s.half = 0;
+  s.cp_head = s.cp_n = s.cp_src = 0;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;
   if (E.winners) E.winners[g] = WIN_NONE;
@@ -248,51 +333,59 @@ __global__ void k_drop_root(EngineDev<G> E) {
   E.slots[g].root_parent_player = 0;
 }
 
+// Slots that are in the middle of a search keep going (only their move budget is updated).
 template <class G>
-__global__ void k_begin_move(EngineDev<G> E, int play_limit, int moves_budget) {
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_begin_move(EngineDev<G> E, int play_limit, int moves_budget) {
   const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (g >= E.n_games) return;
   Slot<G> s = E.slots[g];
   if (s.phase == BB_PH_GAME_OVER || s.phase == BB_PH_ERROR) return;
   s.moves_budget = moves_budget;
-  begin_move(E, s, E.hdr + (size_t)g * E.node_cap, E.stat + (size_t)g * E.node_cap, play_limit);
+  if (!phase_busy(s.phase)) {
+    Path path;
+    begin_move(E, s, E.half(g, s.half), path, play_limit);
+    path.store(E.path + (size_t)g * PATH_LEN);
+  }
   if (lane_id() == 0) E.slots[g] = s;
 }
 
 // _selectAction(exploring=False): child index -> action per slot (temp 1: uniforms; temp 0: PUCT)
 template <class G>
-__global__ void k_choose(EngineDev<G> E, int temp_mode, const double* uniforms, int32_t* actions) {
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_choose(EngineDev<G> E, int temp_mode, const double* uniforms, int32_t* actions) {
   const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (g >= E.n_games) return;
   const Slot<G> s = E.slots[g];
-  if (s.phase != BB_PH_MOVE_READY) { if (lane_id() == 0) actions[g] = -1; return; }
-  NodeHdr* hdr = E.hdr + (size_t)g * E.node_cap;
-  NodeStat* stat = E.stat + (size_t)g * E.node_cap;
-  const NodeHdr rh = hdr[s.root];
+  if (s.phase != BB_PH_MOVE_READY || s.root == NONE) { if (lane_id() == 0) actions[g] = -1; return; }
+  const Node* nodes = E.half(g, s.half);
+  const NodeHdr rh = nodes[s.root].h;
   const int k = meta_nchild(rh.meta);
+  if (rh.child_base == NONE || k == 0) { if (lane_id() == 0) actions[g] = -1; return; }
   int j;
-  if (temp_mode == 1) j = sample_child(stat + rh.child_base, k, uniforms[g]);
-  else { double u; j = puct_select(stat + rh.child_base, k, E.c, &u); }
-  if (lane_id() == 0) actions[g] = meta_action(hdr[rh.child_base + j].meta);
+  NodeHdr chosen;
+  if (temp_mode == 1) { j = sample_child(nodes + rh.child_base, k, uniforms[g]); chosen = nodes[rh.child_base + j].h; }
+  else { double u; j = puct_select<SelectChunks<G>::N>(nodes + rh.child_base, k, E.c, &u, &chosen); }
+  if (lane_id() == 0) actions[g] = meta_action(chosen.meta);
 }
 
+// state = nextState; MoveRoot(state) by action, with the whole subtree copy done in this launch
 template <class G>
-__global__ void k_move_root(EngineDev<G> E, const int32_t* actions) {
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_move_root(EngineDev<G> E, const int32_t* actions) {
+  __shared__ WarpScratch s_ws[WARPS_PER_CTA];
   const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (g >= E.n_games) return;
   Slot<G> s = E.slots[g];
-  if (s.phase != BB_PH_MOVE_READY || actions[g] < 0) return;
-  NodeHdr* hdr = E.hdr + (size_t)g * E.node_cap;
-  NodeStat* stat = E.stat + (size_t)g * E.node_cap;
-  const NodeHdr rh = hdr[s.root];
-  const int k = meta_nchild(rh.meta);
+  if (s.phase != BB_PH_MOVE_READY || actions[g] < 0 || s.root == NONE) return;
+  Node* nodes = E.half(g, s.half);
+  const NodeHdr rh = nodes[s.root].h;
+  const int k = rh.child_base == NONE ? 0 : meta_nchild(rh.meta);
   int j = -1;
   for (int i = 0; i < k; ++i)
-    if (meta_action(hdr[rh.child_base + i].meta) == actions[g]) { j = i; break; }
+    if (meta_action(nodes[rh.child_base + i].h.meta) == actions[g]) { j = i; break; }
   if (j < 0) { s.phase = BB_PH_ERROR; s.status = BB_EILLEGAL; }
   else {
     unsigned long long done = 0;
-    play_move(E, s, g, hdr, stat, j, &done);
+    play_move(E, s, g, nodes, j, &done);
+    while (s.phase == BB_PH_COMPACT) run_compaction(E, s, g, s_ws[threadIdx.x >> 5], 1 << 20);
     if (lane_id() == 0 && done) atomicAdd(&E.counters->games_done, done);
     if (lane_id() == 0) atomicAdd(&E.counters->moves, 1ull);
   }

@@ -1,31 +1,44 @@
-// Tree pool layout and the per-slot search state (SoA arenas in HBM; DESIGN.md "data layout").
+// Tree pool layout and the per-slot search state (arenas in HBM; DESIGN.md "data layout").
 //
-// Per game slot g the arena holds node_cap nodes; node ids are arena-local u32.  Children of one
-// expansion are allocated contiguously (ascending action id), so PUCT select reads one coalesced
-// run of 16-byte NodeStat records and expansion writes one.  Child STATES are never stored: the
-// descent re-derives them by applying actions to the root state held in registers.
+// Per game slot g the pool holds two half-arenas of node_cap nodes each; node ids are
+// half-local u32.  A node is ONE 32-byte record (one DRAM sector): the statistics its parent's
+// PUCT select reads (Plays, Value, prior) next to its own header (parent, first child, action,
+// cached network value).  Children of one expansion are allocated contiguously in ascending
+// action order, so a select is one coalesced run of 32-byte loads (one lane per child) that
+// also brings in the header of whichever child wins -- one dependent memory latency per tree
+// level.  Child STATES are never stored: the descent re-derives them by applying actions to
+// the root state held in registers.  At MoveRoot the new root's subtree is copied breadth-first
+// into the other half (children stay contiguous and ordered), which bounds a slot's memory by
+// one move's growth plus the carried subtree instead of the whole game.
 //
-// Reference objects restated: MCTS.Node (MCTS.py:7-98) -> NodeHdr + NodeStat; MCTS.Root and the
-// _findLeaf locals (MCTS.py:120, DynamicMCTS.py:22-32) -> Slot.
+// Reference objects restated: MCTS.Node (MCTS.py:7-98) -> Node; MCTS.Root and the _findLeaf
+// locals (MCTS.py:120, DynamicMCTS.py:22-32) -> Slot.
 #pragma once
 #include "common.cuh"
 
 namespace bb {
 
 constexpr uint32_t NONE = 0xFFFFFFFFu;
+constexpr int PATH_LEN = 64;        // descent path kept in registers / the slot's path row
 
-struct __align__(16) NodeStat {   // one per node, read by the PARENT's select
+struct __align__(16) NodeStat {   // read by the PARENT's select
   uint32_t plays;                 // Node.Plays
   float value;                    // Node.Value, f32 accumulation
   double prior;                   // Parent.Priors[action] (f64, A.9)
 };
 
 struct __align__(16) NodeHdr {
-  uint32_t parent;                // Node.Parent (NONE for the game's first root)
+  uint32_t parent;                // Node.Parent (NONE for the root of the current half)
   uint32_t child_base;            // first child id; NONE = Children is None
   uint32_t meta;                  // action:12 | nchild:10 | player-1:1 | has_value:1
   float eval;                     // raw network value of this state (cached getEvaluation)
 };
+
+struct __align__(32) Node {
+  NodeStat s;
+  NodeHdr h;
+};
+
 constexpr uint32_t META_HAS_VALUE = 1u << 23;
 __host__ __device__ __forceinline__ uint32_t meta_pack(int action, int nchild, int player, bool has_value) {
   return (uint32_t)action | ((uint32_t)nchild << 12) | ((uint32_t)(player - 1) << 22) | (has_value ? META_HAS_VALUE : 0u);
@@ -40,16 +53,20 @@ struct Slot {
   typename G::State cur_state;    // state of `cur` during a descent
   uint32_t root, cur;             // NONE root = "Root is None"
   int32_t depth, last_action;     // _findLeaf locals
-  uint32_t n_nodes;               // arena bump pointer
+  uint32_t n_nodes;               // bump pointer of the current half
   uint32_t end_plays;             // endPlays (MCTS.py:297)
+  uint32_t root_plays;            // Root.Plays, mirrored in the slot (saves a dependent load per simulation)
   int32_t phase, status;          // BB_PH_*, BB_* error code
   int32_t ply;                    // moves played
   int32_t root_parent_player;     // Player of Root.Parent.State (0: Root has no parent), A.13
   int32_t winner;                 // BB_WIN_* after GAME_OVER
   uint32_t req_idx;               // index of the open evaluator request
   uint32_t pool_used;             // record pool bump pointer
-  int32_t moves_budget;           // steady-state stepping: moves this slot may still play (<0: unlimited)
+  int32_t moves_budget;           // moves this slot may still play (<0: unlimited)
   uint32_t game_no;               // games this slot has finished (refill mode)
+  uint32_t half;                  // which half-arena is live
+  uint32_t cp_head, cp_n;         // subtree copy in progress: next node to scan, nodes written
+  uint32_t cp_src;                // old id of the new root
 };
 
 // numpy pairwise-sum plan for a dense vector of length A, built on the host.
@@ -65,17 +82,27 @@ struct Counters {                 // mirrors bb_counters
   unsigned long long sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
 };
 
+// Per-tick control block.  Request / activity counters are double-buffered by tick parity so a
+// tick is exactly two kernels (advance, evaluator) with no memsets in between: the last CTA of
+// the advance kernel clears the other parity and publishes tick+1.
+struct TickCtl {
+  unsigned tick;                  // ticks completed
+  unsigned blocks_done;           // CTA ticket of the running advance kernel
+  int req[2];                     // evaluator requests posted in tick t -> req[t & 1]
+  int active[2];                  // slots still searching after tick t  -> active[t & 1]
+};
+
 template <class G>
 struct EngineDev {                // passed to kernels by value
   Slot<G>* slots;
-  NodeHdr* hdr;
-  NodeStat* stat;
+  Node* nodes;                    // [n_games][2][node_cap]
+  uint32_t* path;                 // [n_games][PATH_LEN] descent paths of blocked slots
   int n_games;
   uint32_t node_cap;
   int search, max_depth, max_plies;
   double c;                       // ExplorationRate
   // evaluator mailbox
-  int* req_count;
+  TickCtl* ctl;
   int* req_slot;
   typename G::State* req_state;
   float* resp_policy;             // [n_games][A], indexed by request
@@ -94,8 +121,9 @@ struct EngineDev {                // passed to kernels by value
   int32_t* n_moves;
   int32_t* winners;
   uint32_t pool_cap;
-  int* active;                    // slots still searching after this tick
   Counters* counters;
+
+  __device__ __forceinline__ Node* half(int g, uint32_t h) const { return nodes + ((size_t)g * 2 + h) * node_cap; }
 };
 
 }  // namespace bb

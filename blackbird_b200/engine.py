@@ -116,11 +116,15 @@ def kat_forward(game, states):
     return pol, val
 
 
-def default_node_cap(game, search, play_limit, max_plies):
+def default_node_cap(game, search, play_limit, max_depth=10):
+    """Nodes per half-arena: one move's growth plus the subtree carried over MoveRoot.
+
+    A dynamic simulation expands at most one node (<= A children); a fixed-depth one expands up to
+    max_depth nodes while the tree is young and ~3 on a fresh 800-simulation root (SURVEY.md
+    Appendix E).  Overflow is reported (BB_ENOMEM), never silent."""
     a = min(_ACTIONS[game], 48)
-    # fixed-depth search expands several fresh nodes per simulation while the tree is young
-    per_sim = a * ((3.5 if play_limit < 200 else 1.4) if search == 'fixed' else 1.0)
-    return int(min(1 << 22, max(4096, play_limit * per_sim * max_plies + 64)))
+    per_sim = a * ((min(max_depth, 10) if play_limit <= 64 else 4) if search == 'fixed' else 1)
+    return int(min(1 << 22, max(1024, 2.5 * play_limit * per_sim + 64)))
 
 
 _DEFAULT_PLIES = {'TicTacToe': 9, 'Connect4': 42, 'DragonChess': 512}
@@ -136,7 +140,7 @@ class Engine(object):
         self.A = _ACTIONS[game]
         self.state_bytes = _STATE_BYTES[game]
         self.max_plies = int(max_plies or _DEFAULT_PLIES[game])
-        self.node_cap = int(node_cap or default_node_cap(game, search, play_limit_hint, self.max_plies))
+        self.node_cap = int(node_cap or default_node_cap(game, search, play_limit_hint, int(max_depth or 10)))
         cfg = _lib.bb_config()
         cfg.game = _lib.GAME_IDS[game]
         cfg.search = {'fixed': _lib.FIXED, 'dynamic': _lib.DYNAMIC}[search]
@@ -266,6 +270,15 @@ class Engine(object):
             assert u.shape == (self.n_games, self.max_plies), u.shape
         check(lib.bb_selfplay_step(self._h, int(n_moves), int(play_limit), float(temp),
                                    None if u is None else u.ctypes.data_as(C.c_void_p)))
+
+    def stream_moves(self, target_moves, play_limit, temp=1.0, uniforms=None):
+        """Steady state without a per-move barrier: run until target_moves further moves were played."""
+        u = None
+        if uniforms is not None:
+            u = np.ascontiguousarray(uniforms, dtype=np.float64)
+            assert u.shape == (self.n_games, self.max_plies), u.shape
+        check(lib.bb_selfplay_stream(self._h, int(target_moves), int(play_limit), float(temp),
+                                     None if u is None else u.ctypes.data_as(C.c_void_p)))
 
     def stream(self):
         """torch view of the engine's CUDA stream (for CUDA-event timing)."""

@@ -31,7 +31,8 @@ enum { BB_EVAL_KAT = 0,        /* integer evaluator of SURVEY.md Appendix B.2 (p
 enum { BB_WIN_NONE = -1, BB_WIN_DRAW = 0, BB_WIN_P1 = 1, BB_WIN_P2 = 2, BB_WIN_FLOAT0 = 3 };
 /* per-game phases reported by bb_search_phases */
 enum { BB_PH_IDLE = 0, BB_PH_RUN = 1, BB_PH_WAIT_EXPAND = 2, BB_PH_WAIT_LEAF = 3,
-       BB_PH_MOVE_READY = 4, BB_PH_GAME_OVER = 5, BB_PH_ERROR = 6 };
+       BB_PH_MOVE_READY = 4, BB_PH_GAME_OVER = 5, BB_PH_ERROR = 6,
+       BB_PH_COMPACT = 7 /* copying the new root's subtree after a move (busy) */ };
 
 const char* bb_last_error(void);
 int bb_abi_version(void);
@@ -73,7 +74,8 @@ typedef struct bb_config {
   int32_t max_depth;         /* FixedMCTS maxDepth (FixedMCTS.py:9,15-16); ignored for dynamic   */
   int32_t evaluator;         /* BB_EVAL_*                                                        */
   int32_t n_games;           /* concurrent game slots on this GPU                                */
-  int32_t node_cap;          /* tree nodes per game arena (overflow -> BB_ENOMEM, never silent)  */
+  int32_t node_cap;          /* tree nodes per half-arena of a game: one move's growth + the
+                                subtree carried over MoveRoot (overflow -> BB_ENOMEM, never silent) */
   int32_t max_plies;         /* record slots per game; engine-side ply cap      */
   int32_t device;            /* CUDA device ordinal                                              */
   double exploration_rate;   /* MCTS.ExplorationRate (MCTS.py:119)                               */
@@ -143,6 +145,10 @@ int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* uni
  * n_moves further moves (play_limit simulations each); a slot whose game ends starts the next
  * game in place (Blackbird.py:238-244 loop).  uniforms_host may be NULL to keep the table. */
 int bb_selfplay_step(bb_engine* e, int n_moves, int play_limit, double temp, const double* uniforms_host);
+/* Steady state without a per-move barrier (throughput measurement, streaming generation): slots
+ * keep searching, moving and restarting finished games in place until the engine as a whole has
+ * played target_moves further moves; slots are left mid-search and a later call carries on. */
+int bb_selfplay_stream(bb_engine* e, long long target_moves, int play_limit, double temp, const double* uniforms_host);
 /* The cudaStream_t all engine kernels are launched on (for CUDA-event timing by the caller). */
 void* bb_engine_stream(bb_engine* e);
 /* Per-tick CUDA-event timing of the advance kernel and the evaluator kernel on the engine's

@@ -145,3 +145,41 @@ def test_full_size_properties(mods):
     want, _, _ = selfplay_np.play_game(s, GAMES['Connect4'], 1)
     assert records.build_records(eng, raw)[0][0] == want
     eng.close()
+
+
+def test_steady_state_stepping(mods):
+    """bb_selfplay_step (barrier per move round) and bb_selfplay_stream (no barrier): every
+    simulation is accounted for, slots refill in place, and a later bb_selfplay_run still
+    reproduces the oracle (no state leaks from the half-arena copies)."""
+    engine, records = mods
+    G, P = 64, 20
+    eng = engine.Engine('Connect4', 'dynamic', n_games=G, evaluator='kat', play_limit_hint=P)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
+    eng.reset()
+    eng.step(3, P, 1.0, u)
+    eng.check_status()
+    c = eng.counters(reset=True)
+    assert c['moves'] == 3 * G and c['sims'] == 3 * G * P
+    eng.stream_moves(40 * G, P)
+    eng.check_status()
+    c = eng.counters(reset=True)
+    assert c['moves'] >= 40 * G and c['games_done'] > 0
+    assert c['moves'] * P <= c['sims'] <= (c['moves'] + G) * P
+    eng.selfplay(P, 1.0, u)
+    got = records.build_records(eng)
+    for g in range(0, G, 7):
+        s = search_np.NetSearch(search_np.KatEvaluator(7), 'dynamic', maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        want, _, _ = selfplay_np.play_game(s, GAMES['Connect4'], 1)
+        assert got[g][0] == want, g
+    eng.close()
+
+
+def test_arena_overflow_is_loud(mods):
+    """A half-arena that is too small must raise, never truncate the tree silently."""
+    engine, _ = mods
+    eng = engine.Engine('Connect4', 'fixed', n_games=2, evaluator='kat', node_cap=64, play_limit_hint=50)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(2)])
+    with pytest.raises(MemoryError):
+        eng.selfplay(50, 1.0, u)
+    eng.close()
