@@ -40,6 +40,8 @@ def parse():
     ap.add_argument('--sims', type=int, default=800, help='simulations per move (playLimit)')
     ap.add_argument('--epsilon', type=float, default=0.0, help='policy noise weight (template: 0.3)')
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='CPU baseline sample length')
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
+    ap.add_argument('--engines', type=int, default=1, help='split the games over this many engine instances (own stream + host thread each)')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
     return ap.parse_args()
@@ -124,35 +126,45 @@ def run_reference(args):
 # GPU arm
 # ---------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    Q = 'index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,' \
-        'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+    """SM clock / throttle-reason samples during the timed region, through NVML in-process (spawning
+    nvidia-smi every 200 ms perturbs kernel launches of a latency-bound pipeline)."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
 
     def run(self):
+        nv = self.nv
+        if nv is None or os.environ.get('BB_NO_CLOCKS'):
+            return
+        bits = {'hw_slowdown': nv.nvmlClocksThrottleReasonHwSlowdown,
+                'hw_thermal_slowdown': nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                'sw_thermal_slowdown': nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                'sw_power_cap': nv.nvmlClocksThrottleReasonSwPowerCap}
         while not self.stop_flag:
             try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits'],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(',')])
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((sm, [k for k, b in bits.items() if mask & b]))
             except Exception:
                 pass
             time.sleep(0.2)
 
     def summary(self):
         self.stop_flag = True
-        sm = sorted(float(r[1]) for r in self.rows if r[1].replace('.', '').isdigit())
-        reasons = set()
-        for r in self.rows:
-            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[5:9]):
-                if v.lower().startswith('active'):
-                    reasons.add(name)
-        mx = max([float(r[2]) for r in self.rows if r[2].replace('.', '').isdigit()] or [0.0])
-        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx or None, 'reasons': sorted(reasons),
-                'samples': len(self.rows)}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = sorted({k for r in self.rows for k in r[1]})
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': getattr(self, 'max_sm', None), 'reasons': reasons,
+                'samples': len(self.rows), 'how': 'NVML in-process, 200 ms period'}
 
 
 def run_ours(args):
@@ -179,7 +191,7 @@ def run_ours(args):
     eng = Engine(GAME, SEARCH, n_games=G, max_depth=MAX_DEPTH, exploration_rate=C_PUCT, evaluator='net',
                  play_limit_hint=P, device=local)
     weights = netinit.random_weights(cin, 7, seed=0, **NET)
-    eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=args.epsilon, alpha=0.2, seed=rank)
+    eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=args.epsilon, alpha=0.2, seed=rank, precision=args.precision)
     # per-game move-sampling uniforms, game id = rank*G + slot (records identical for any GPU count)
     uniforms = np.stack([np.random.RandomState(1000 + rank * G + g).random_sample(eng.max_plies) for g in range(G)])
     stream = eng.stream()
@@ -242,7 +254,7 @@ def run_ours(args):
     # mailbox: state out/in + policy/value out/in; backup: 8-byte read-modify-write per path node
     b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * 16 + 2 * 4 * 8) + 16 * (d_bar + 1)
     tree_gbs = cp['sims'] * b_sim / (prof['advance_ms'] * 1e-3) / 1e9 if prof['advance_ms'] > 0 else 0.0
-    roofline = {'bound': 'tensor', 'kernel': 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks'])),
+    roofline = {'bound': 'tensor', 'kernel': ('k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' if args.precision == 'bf16' else 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)') % (cp['evals'] / max(1, prof['ticks'])),
                 'achieved': net_tflops, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / tensor_peak,
                 'traffic': None, 'peak_source': peak_src, 'flops_per_eval': flops,
                 'launch_ms_avg': prof['eval_ms'] / max(1, prof['ticks']),
@@ -284,7 +296,7 @@ def run_ours(args):
         print(json.dumps({
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': ms / max(1, args.steps), 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
-            'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(args, world),
+            'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
             'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
             'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
             'roofline': roofline, 'roofline_tree': roofline_tree, 'cpu_baseline': cpu, 'e2e': e2e,

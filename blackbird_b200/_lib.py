@@ -26,7 +26,7 @@ class bb_config(C.Structure):
 
 class bb_net_desc(C.Structure):
     _fields_ = [('blocks', C.c_int32), ('filters', C.c_int32), ('dense', C.c_int32), ('cin', C.c_int32),
-                ('epsilon', C.c_float), ('alpha', C.c_float), ('noise_seed', C.c_uint64), ('reserved', C.c_int32 * 4)]
+                ('epsilon', C.c_float), ('alpha', C.c_float), ('noise_seed', C.c_uint64), ('precision', C.c_int32), ('reserved', C.c_int32 * 3)]
 
 
 class bb_counters(C.Structure):

@@ -37,12 +37,19 @@ struct NetParams {
   unsigned long long* call_counter;
 };
 
+struct TcParams {
+  const uint4* w;          // [KB_IN*9 + (layers-1)*9] weight blocks of 512 bytes (bf16, canonical K-major layout)
+  int w_blocks;
+};
+
 struct NetDev {
   int game;
   bb_net_desc desc;
   NetParams p;
   std::vector<void*> allocs;
   int sm_count;
+  bool use_tc = false;     // bf16 tcgen05 kernel instead of the fp32 SIMT one (bb_net_desc.precision)
+  TcParams tc{};
 };
 
 template <class G>
@@ -124,7 +131,7 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
   if (lane == 0) red[wid] = v;
   __syncthreads();
   float r = red[0];
-  for (int i = 1; i < NET_THREADS / 32; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  for (int i = 1; i < (int)(blockDim.x >> 5); ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
   return r;
 }
 
@@ -156,6 +163,84 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
   float x = gamma_small(alpha, key, ctr), y = gamma_small(1.0f - alpha, key, ctr);
   return x / (x + y);
 }
+
+// Value and policy heads from the per-position sums over H,W of the three head feature maps
+// (hsum[p*4 + {0: value, 1,2: policy}]): value = tanh(dense(relu(dense(1->D)+sum))), policy =
+// softmax(dense(2->A)+sum), noise mix, renormalise (NetworkFactory.py:115-182).  Block-wide.
+template <class G>
+__device__ void heads_finish(const NetParams& np, const float* hsum, float* red, int base, int n, int P,
+                             unsigned long long call, float* __restrict__ policy, float* __restrict__ value) {
+  constexpr int HW = G::H * G::W;
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const float* hd = np.head;
+  const int D = np.dense;
+  const float* d1w = hd + 17 + 34;
+  const float* d1b = d1w + D;
+  const float* d2w = d1b + D;
+  const float d2b = d2w[D];
+  if (tid < P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
+    const float s = hsum[tid * 4];
+    float o = d2b;
+    for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
+    value[base + tid] = tanhf(o);
+  }
+  // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
+  if (G::A <= 32) {
+    if (tid < P && base + tid < n) {
+      const float s0 = hsum[tid * 4 + 1], s1 = hsum[tid * 4 + 2];
+      float z[G::A <= 32 ? G::A : 1];
+      float m = -INFINITY;
+#pragma unroll
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
+        z[a] = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)HW * np.pol_b[a]));
+        m = fmaxf(m, z[a]);
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) { z[a] = expf(z[a] - m); sum += z[a]; }
+      float tot = 0.f;
+#pragma unroll
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
+        float pa = z[a] / sum;
+        if (np.eps > 0.f)
+          pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + tid) * G::A + a);
+        z[a] = pa;
+        tot += pa;
+      }
+#pragma unroll
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[(size_t)(base + tid) * G::A + a] = z[a] / tot;
+    }
+  } else {
+    for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
+      const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
+      float* out = policy + (size_t)(base + p) * G::A;
+      float m = -INFINITY;
+      for (int a = tid; a < G::A; a += nthreads) {
+        float z = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)HW * np.pol_b[a]));
+        out[a] = z;
+        m = fmaxf(m, z);
+      }
+      m = block_reduce(m, red, true);
+      float sum = 0.f;
+      for (int a = tid; a < G::A; a += nthreads) { float e = expf(out[a] - m); out[a] = e; sum += e; }
+      sum = block_reduce(sum, red, false);
+      float tot = 0.f;
+      for (int a = tid; a < G::A; a += nthreads) {
+        float pa = out[a] / sum;
+        if (np.eps > 0.f)
+          pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + p) * G::A + a);
+        out[a] = pa;
+        tot += pa;
+      }
+      tot = block_reduce(tot, red, false);
+      for (int a = tid; a < G::A; a += nthreads) out[a] = out[a] / tot;
+    }
+  }
+}
+
+}  // namespace bb
+#include "net_tc.cuh"
+namespace bb {
 
 template <class G>
 __global__ void __launch_bounds__(NET_THREADS, 1)
@@ -195,7 +280,6 @@ k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_
   }
   constexpr int PLANE = Ge::P * Ge::CELLS;
   const float* hd = np.head;
-  const int D = np.dense;
   unsigned long long call = 0;
   if (np.eps > 0.f) call = *np.call_counter;
 
@@ -258,68 +342,7 @@ k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_
       hsum[p * 4 + k] = s;
     }
     __syncthreads();
-    const float* d1w = hd + 17 + 34;
-    const float* d1b = d1w + D;
-    const float* d2w = d1b + D;
-    const float d2b = d2w[D];
-    if (tid < Ge::P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
-      const float s = hsum[tid * 4];
-      float o = d2b;
-      for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)Ge::HW * d1b[d]), 0.f), d2w[d], o);
-      value[base + tid] = tanhf(o);
-    }
-    // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
-    if (G::A <= 32) {
-      if (tid < Ge::P && base + tid < n) {
-        const float s0 = hsum[tid * 4 + 1], s1 = hsum[tid * 4 + 2];
-        float z[G::A <= 32 ? G::A : 1];
-        float m = -INFINITY;
-#pragma unroll
-        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-          z[a] = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)Ge::HW * np.pol_b[a]));
-          m = fmaxf(m, z[a]);
-        }
-        float sum = 0.f;
-#pragma unroll
-        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) { z[a] = expf(z[a] - m); sum += z[a]; }
-        float tot = 0.f;
-#pragma unroll
-        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-          float pa = z[a] / sum;
-          if (np.eps > 0.f)
-            pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + tid) * G::A + a);
-          z[a] = pa;
-          tot += pa;
-        }
-#pragma unroll
-        for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[(size_t)(base + tid) * G::A + a] = z[a] / tot;
-      }
-    } else {
-      for (int p = 0; p < Ge::P && base + p < n; ++p) {      // block-wide over the 4032 actions
-        const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
-        float* out = policy + (size_t)(base + p) * G::A;
-        float m = -INFINITY;
-        for (int a = tid; a < G::A; a += NET_THREADS) {
-          float z = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)Ge::HW * np.pol_b[a]));
-          out[a] = z;
-          m = fmaxf(m, z);
-        }
-        m = block_reduce(m, red, true);
-        float sum = 0.f;
-        for (int a = tid; a < G::A; a += NET_THREADS) { float e = expf(out[a] - m); out[a] = e; sum += e; }
-        sum = block_reduce(sum, red, false);
-        float tot = 0.f;
-        for (int a = tid; a < G::A; a += NET_THREADS) {
-          float pa = out[a] / sum;
-          if (np.eps > 0.f)
-            pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + p) * G::A + a);
-          out[a] = pa;
-          tot += pa;
-        }
-        tot = block_reduce(tot, red, false);
-        for (int a = tid; a < G::A; a += NET_THREADS) out[a] = out[a] / tot;
-      }
-    }
+    heads_finish<G>(np, hsum, red, base, n, Ge::P, call, policy, value);
   }
 }
 
@@ -349,9 +372,32 @@ static int net_launch(NetDev* net, const void* states, int n, const int* count_d
   return BB_OK;
 }
 
+template <class G>
+static int net_launch_tc(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
+  using Ge = TcGeom<G>;
+  const TcSmem<G> L(net->tc.w_blocks, net->p.layers);
+  static bool configured[3] = {false, false, false};
+  static int ctas_per_sm[3] = {1, 1, 1};
+  if (!configured[G::ID]) {
+    BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    int occ = 1;
+    BB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_net_forward_tc<G>, TC_THREADS, L.total));
+    ctas_per_sm[G::ID] = occ < 1 ? 1 : (occ > 2 ? 2 : occ);
+    configured[G::ID] = true;
+  }
+  const int batches = (n + Ge::NP - 1) / Ge::NP;
+  const int cap = net->sm_count * ctas_per_sm[G::ID];
+  const int grid = batches < cap ? batches : cap;
+  k_net_forward_tc<G><<<grid, TC_THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value);
+  BB_CUDA(cudaGetLastError());
+  if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
+  return BB_OK;
+}
+
 int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
   if (n <= 0) return BB_OK;
-  BB_DISPATCH_GAME(net->game, return net_launch<G>(net, states, n, count_dev, policy, value, stream));
+  if (net->use_tc) { BB_DISPATCH_GAME(net->game, return net_launch_tc<G>(net, states, n, count_dev, policy, value, stream)); }
+  else { BB_DISPATCH_GAME(net->game, return net_launch<G>(net, states, n, count_dev, policy, value, stream)); }
   return BB_EINVAL;
 }
 
@@ -406,6 +452,41 @@ static int net_build(NetDev* net, const bb_net_desc* d, const float* w, size_t n
   if ((rc = upload(tw.data(), tw.size(), &net->p.tower_w))) return rc;
   if ((rc = upload(tb.data(), tb.size(), &net->p.tower_b))) return rc;
   if ((rc = upload(head.data(), head.size(), &net->p.head))) return rc;
+  net->use_tc = d->precision == 1;
+  if (net->use_tc) {
+    // bf16 B operands: per (layer, k-block, tap) one 16x16 block, element (n = cout, k = cin) at byte
+    // (k / 8) * 256 + n * 16 + (k % 8) * 2  (K-major, SWIZZLE_NONE: 8x8 core matrices of 128 bytes)
+    using Tg = TcGeom<G>;
+    const int blocks_n = Tg::KB_IN * 9 + (layers - 1) * 9;
+    std::vector<uint16_t> wb((size_t)blocks_n * 256, 0);
+    auto bf16_rn = [](float f) -> uint16_t {
+      uint32_t u;
+      memcpy(&u, &f, 4);
+      if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
+      u += 0x7FFFu + ((u >> 16) & 1u);
+      return (uint16_t)(u >> 16);
+    };
+    for (int l = 0; l < layers; ++l) {
+      const int kbs = l == 0 ? Tg::KB_IN : 1, ci_n = l == 0 ? cin : F, ci_pad = l == 0 ? Ge::CIN_PAD : F;
+      const float* lw = l == 0 ? tw.data() : tw.data() + Ge::STEM_W + (size_t)(l - 1) * Ge::LAYER_W;
+      const int blk0 = l == 0 ? 0 : Tg::KB_IN * 9 + (l - 1) * 9;
+      for (int kb = 0; kb < kbs; ++kb)
+        for (int t = 0; t < 9; ++t)
+          for (int k = 0; k < 16; ++k)
+            for (int o = 0; o < 16; ++o) {
+              const int ci = kb * 16 + k;
+              const float v = ci < ci_n ? lw[((size_t)t * ci_pad + ci) * F + o] : 0.f;
+              wb[(size_t)(blk0 + kb * 9 + t) * 256 + (k / 8) * 128 + o * 8 + (k % 8)] = bf16_rn(v);
+            }
+    }
+    void* q = nullptr;
+    BB_CUDA(cudaMalloc(&q, wb.size() * 2));
+    net->allocs.push_back(q);
+    BB_CUDA(cudaMemcpy(q, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
+    net->tc.w = (const uint4*)q;
+    net->tc.w_blocks = blocks_n;
+    if (TcSmem<G>(blocks_n, layers).total > 227 * 1024) { set_error("network too deep for the smem-resident tensor-core kernel (%d blocks)", blocks); return BB_EINVAL; }
+  }
   if ((rc = upload(pw, 2 * (size_t)A, &net->p.pol_w))) return rc;
   if ((rc = upload(pb, (size_t)A, &net->p.pol_b))) return rc;
   void* ctr = nullptr;

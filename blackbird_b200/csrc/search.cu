@@ -1,5 +1,7 @@
 // Engine host side: owns the tree pool in HBM, runs the tick loop (advance kernel + evaluator),
 // and implements the search / self-play / record entry points of include/bbengine.h.
+#include <chrono>
+#include <cstdlib>
 #include <vector>
 
 #include "search_kernels.cuh"
@@ -144,6 +146,10 @@ struct EngineT : bb_engine {
     d.max_depth = c.max_depth;
     d.max_plies = c.max_plies;
     d.c = c.exploration_rate;
+    {
+      const char* sb = getenv("BB_STEP_BUDGET");               // tuning knob; results do not depend on it
+      d.step_budget = sb ? atoi(sb) : (c.search == BB_FIXED ? c.max_depth + 6 : 24);
+    }
     d.pool_cap = (uint32_t)c.max_plies * (uint32_t)(G::A < 64 ? G::A : 64);
     int rc;
 #define A_(p, cnt) if ((rc = alloc(&p, cnt)) != BB_OK) return rc
@@ -286,16 +292,31 @@ struct EngineT : bb_engine {
   int tick_until(Done done) {
     const int burst = 16;
     int rc, i = 0;
+    using clk = std::chrono::steady_clock;
+    const bool trace = getenv("BB_TRACE") != nullptr;
+    double t_launch = 0, t_wait = 0;
+    long n_ticks = 0;
+    auto t0 = clk::now();
     for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
     if ((rc = post_snapshot(0))) return rc;
+    n_ticks += burst;
     for (;;) {
+      auto a = clk::now();
       for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
       if ((rc = post_snapshot(i ^ 1))) return rc;
+      n_ticks += burst;
+      auto b = clk::now();
       if ((rc = wait_snapshot(i))) return rc;
+      auto c = clk::now();
+      t_launch += std::chrono::duration<double>(b - a).count();
+      t_wait += std::chrono::duration<double>(c - b).count();
       if (done(i)) break;
       i ^= 1;
     }
     if ((rc = wait_snapshot(i ^ 1))) return rc;
+    if (trace)
+      fprintf(stderr, "[bb trace] %ld ticks in %.3f s: host launching %.3f s, host waiting %.3f s\n", n_ticks,
+              std::chrono::duration<double>(clk::now() - t0).count(), t_launch, t_wait);
     return BB_OK;
   }
   int run(int* pending) override {

@@ -155,8 +155,10 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
     ch = nodes[s.cur].h;
   }
 
+  int budget = E.step_budget;
   for (;;) {
     if (s.phase == BB_PH_COMPACT) {
+      budget -= COMPACT_ROUNDS_PER_TICK;
       run_compaction(E, s, g, ws, COMPACT_ROUNDS_PER_TICK);
       if (s.phase != BB_PH_MOVE_READY || !E.autoplay || s.moves_budget == 0) break;
       nodes = E.half(g, s.half);
@@ -201,6 +203,7 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
       s.depth += 1;
       path.set(s.depth, s.cur, meta_player(ch.meta));
       n_sel += 1;
+      budget -= 1;
       step = ST_TOP;
     } else {                                                    // ST_LEAF: SampleValue + _backProp
       if (!(ch.meta & META_HAS_VALUE)) {
@@ -251,6 +254,7 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
         ch = nodes[s.cur].h;
       }
       step = ST_TOP;
+      if (budget <= 0 && s.phase == BB_PH_RUN) { path.store(prow); break; }   // yield: next tick resumes at the root
     }
   }
   if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) path.store(prow);

@@ -100,6 +100,7 @@ struct EngineDev {                // passed to kernels by value
   int n_games;
   uint32_t node_cap;
   int search, max_depth, max_plies;
+  int step_budget;                // tree levels a slot may descend per tick before it yields (keeps ticks short)
   double c;                       // ExplorationRate
   // evaluator mailbox
   TickCtl* ctl;

@@ -160,11 +160,13 @@ class Engine(object):
     __del__ = close
 
     # -- network --------------------------------------------------------------------------------
-    def load_network(self, flat_weights, blocks, filters, dense, epsilon=0.0, alpha=0.2, seed=0):
+    def load_network(self, flat_weights, blocks, filters, dense, epsilon=0.0, alpha=0.2, seed=0, precision='fp32'):
+        """precision 'fp32': SIMT kernel, 1e-5 parity with the reference graph; 'bf16': tcgen05 tensor-core kernel."""
         w = np.ascontiguousarray(flat_weights, dtype=np.float32)
         d = _lib.bb_net_desc()
         d.blocks, d.filters, d.dense, d.cin = blocks, filters, dense, plane_shape(self.game)[2]
         d.epsilon, d.alpha, d.noise_seed = epsilon, alpha, seed
+        d.precision = {'fp32': 0, 'bf16': 1}[precision]
         check(lib.bb_net_load(self._h, C.byref(d), w.ctypes.data_as(C.c_void_p), w.size))
 
     def net_forward(self, states):

@@ -93,7 +93,8 @@ typedef struct bb_net_desc {
   float epsilon;                    /* policy noise weight (A.17); 0 = deterministic */
   float alpha;
   uint64_t noise_seed;
-  int32_t reserved[4];
+  int32_t precision;                /* 0: fp32 SIMT kernel (1e-5 parity); 1: bf16 tcgen05 tensor-core kernel (2e-2) */
+  int32_t reserved[3];
 } bb_net_desc;
 /* weights_host: flat fp32 in the order documented in DESIGN.md ("weight layout"). */
 int bb_net_load(bb_engine* e, const bb_net_desc* d, const float* weights_host, size_t n_floats);
