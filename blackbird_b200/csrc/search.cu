@@ -2,6 +2,8 @@
 // and implements the search / self-play / record entry points of include/bbengine.h.
 #include <chrono>
 #include <cstdlib>
+#include <string.h>
+#include <algorithm>
 #include <vector>
 
 #include "search_kernels.cuh"
@@ -91,6 +93,7 @@ struct bb_engine {
   virtual int records_export(int32_t*, int32_t*, void*, uint32_t*, uint16_t*, uint32_t*, uint16_t*) = 0;
   virtual int records_device(void**, void**, void**, void**, void**, void**, void**) = 0;
   virtual int counters(bb_counters*, int) = 0;
+  virtual int n_lanes() = 0;
 };
 
 template <class G>
@@ -98,20 +101,30 @@ struct EngineT : bb_engine {
   using State = typename G::State;
   EngineDev<G> d{};
   NetDev* net = nullptr;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;    // lane 0's stream; whole-engine kernels and copies run here while the lanes idle
   std::vector<void*> allocs;
   double* uniforms_dev = nullptr;
   struct Snap { TickCtl ctl; unsigned long long moves; unsigned par; };
-  Snap* snap = nullptr;            // pinned: two snapshots of the tick control block + move counter
-  cudaEvent_t snap_ev[2] = {nullptr, nullptr};
-  unsigned par = 0;                // parity of the next tick
+  // A lane is a contiguous range of game slots with its own stream, tick control block, evaluator
+  // mailbox and counters.  Lanes tick independently, so one lane's advance kernel (a latency-bound
+  // pointer chase whose length is set by its slowest warp) overlaps the other lane's network kernel.
+  struct Lane {
+    EngineDev<G> d{};
+    cudaStream_t stream = nullptr;
+    unsigned par = 0;               // parity of the next tick
+    Snap* snap = nullptr;           // pinned: two snapshots of the tick control block + move counter
+    cudaEvent_t snap_ev[2] = {nullptr, nullptr};
+    std::vector<cudaEvent_t> prof_ev;
+    size_t prof_used = 0;
+  };
+  std::vector<Lane> lanes;
+  TickCtl* ctl_dev = nullptr;
+  Counters* counters_dev = nullptr;
   int last_active = 0, last_req = 0;
   void* scratch = nullptr;         // device scratch for exports
   size_t scratch_bytes = 0;
   unsigned long long host_ticks = 0, host_launches = 0;
   bool prof = false;               // per-tick CUDA-event timing of the two kernels (bench only)
-  std::vector<cudaEvent_t> prof_ev;
-  size_t prof_used = 0;
 
   template <class T>
   int alloc(T** p, size_t count) {
@@ -135,12 +148,22 @@ struct EngineT : bb_engine {
   int init(const bb_config& c) {
     cfg = c;
     BB_CUDA(cudaSetDevice(c.device));
-    BB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    int n_lanes = c.lanes;
+    if (const char* e = getenv("BB_LANES")) n_lanes = atoi(e);
+    if (n_lanes <= 0) n_lanes = c.n_games >= 512 ? 2 : 1;
+    if (c.evaluator == BB_EVAL_EXTERNAL) n_lanes = 1;            // the caller serves one mailbox
+    if (n_lanes > c.n_games) n_lanes = c.n_games;
+    if (n_lanes > 8) n_lanes = 8;
+    lanes.resize(n_lanes);
+    for (Lane& L : lanes) BB_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    stream = lanes[0].stream;
     PairwisePlan P{};
     plan_rec(P, 0, G::A);
     BB_CUDA(cudaMemcpyToSymbol(c_plan, &P, sizeof P, sizeof(PairwisePlan) * G::ID));
     const size_t n = c.n_games, cap = c.node_cap;
     d.n_games = c.n_games;
+    d.g0 = 0;
+    d.n_total = c.n_games;
     d.node_cap = c.node_cap;
     d.search = c.search;
     d.max_depth = c.max_depth;
@@ -156,7 +179,7 @@ struct EngineT : bb_engine {
     A_(d.slots, n);
     A_(d.nodes, n * 2 * cap);
     A_(d.path, n * PATH_LEN);
-    A_(d.ctl, 1);
+    A_(ctl_dev, lanes.size());
     A_(d.req_slot, n);
     A_(d.req_state, n);
     A_(d.resp_policy, n * G::A);
@@ -168,29 +191,51 @@ struct EngineT : bb_engine {
     A_(d.chosen, n * c.max_plies);
     A_(d.n_moves, n);
     A_(d.winners, n);
-    A_(d.counters, 1);
+    A_(counters_dev, lanes.size());
     A_(uniforms_dev, n * c.max_plies);
 #undef A_
-    BB_CUDA(cudaMemset(d.counters, 0, sizeof(Counters)));
+    d.ctl = ctl_dev;
+    d.counters = counters_dev;
+    BB_CUDA(cudaMemset(counters_dev, 0, lanes.size() * sizeof(Counters)));
     BB_CUDA(cudaMemset(d.rec_off, 0, n * (c.max_plies + 2) * sizeof(uint32_t)));
-    BB_CUDA(cudaMemset(d.ctl, 0, sizeof(TickCtl)));
-    BB_CUDA(cudaMallocHost(&snap, 2 * sizeof(Snap)));
-    for (int i = 0; i < 2; ++i) BB_CUDA(cudaEventCreateWithFlags(&snap_ev[i], cudaEventDisableTiming));
+    BB_CUDA(cudaMemset(ctl_dev, 0, lanes.size() * sizeof(TickCtl)));
+    d.uniforms = uniforms_dev;
+    const int per = (c.n_games + n_lanes - 1) / n_lanes;
+    for (int l = 0; l < n_lanes; ++l) {
+      Lane& L = lanes[l];
+      BB_CUDA(cudaMallocHost(&L.snap, 2 * sizeof(Snap)));
+      for (int i = 0; i < 2; ++i) BB_CUDA(cudaEventCreateWithFlags(&L.snap_ev[i], cudaEventDisableTiming));
+      L.d = d;
+      L.d.g0 = l * per;
+      L.d.n_games = std::min(per, c.n_games - l * per);
+      L.d.ctl = ctl_dev + l;
+      L.d.counters = counters_dev + l;
+      L.d.req_slot = d.req_slot + L.d.g0;                          // the lane's own mailbox
+      L.d.req_state = d.req_state + L.d.g0;
+      L.d.resp_policy = d.resp_policy + (size_t)L.d.g0 * G::A;
+      L.d.resp_value = d.resp_value + L.d.g0;
+    }
     d.uniforms = uniforms_dev;
     return reset(nullptr);
   }
   ~EngineT() override {
     cudaSetDevice(cfg.device);
-    if (stream) cudaStreamSynchronize(stream);
+    for (Lane& L : lanes) if (L.stream) cudaStreamSynchronize(L.stream);
     for (void* p : allocs) cudaFree(p);
-    for (cudaEvent_t e : prof_ev) cudaEventDestroy(e);
     if (scratch) cudaFree(scratch);
-    if (snap) cudaFreeHost(snap);
-    for (int i = 0; i < 2; ++i) if (snap_ev[i]) cudaEventDestroy(snap_ev[i]);
+    for (Lane& L : lanes) {
+      for (cudaEvent_t e : L.prof_ev) cudaEventDestroy(e);
+      if (L.snap) cudaFreeHost(L.snap);
+      for (int i = 0; i < 2; ++i) if (L.snap_ev[i]) cudaEventDestroy(L.snap_ev[i]);
+    }
     if (net) net_destroy(net);
-    if (stream) cudaStreamDestroy(stream);
+    for (Lane& L : lanes) if (L.stream) cudaStreamDestroy(L.stream);
   }
 
+  void set_mode(int autoplay, int refill, int play_limit, int temp_mode) {
+    d.autoplay = autoplay; d.refill = refill; d.play_limit = play_limit; d.temp_mode = temp_mode;
+    for (Lane& L : lanes) { L.d.autoplay = autoplay; L.d.refill = refill; L.d.play_limit = play_limit; L.d.temp_mode = temp_mode; }
+  }
   unsigned warp_grid() const { return grid_for((long long)d.n_games * 32, 32 * WARPS_PER_CTA); }
 
   int net_load(const bb_net_desc* nd, const float* w, size_t nfl) override {
@@ -204,8 +249,12 @@ struct EngineT : bb_engine {
   }
   int reset(const void* states_dev) override {
     BB_CUDA(cudaSetDevice(cfg.device));
+    int rc = sync_lanes();
+    if (rc) return rc;
     k_reset<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d, (const State*)states_dev);
     BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaMemsetAsync(ctl_dev, 0, lanes.size() * sizeof(TickCtl), stream));
+    for (Lane& L : lanes) L.par = 0;
     BB_CUDA(cudaStreamSynchronize(stream));
     return BB_OK;
   }
@@ -222,114 +271,122 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
 
-  // one tick = advance kernel + evaluator kernel; request counters alternate by tick parity
-  int tick() {
-    const bool timed = prof && prof_used + 3 <= prof_ev.size();
-    if (timed) cudaEventRecord(prof_ev[prof_used], stream);
-    k_advance<G><<<warp_grid(), 32 * WARPS_PER_CTA, 0, stream>>>(d, par);
+  // one tick of one lane = advance kernel + evaluator kernel; request counters alternate by tick parity
+  int tick(Lane& L) {
+    const bool timed = prof && L.prof_used + 3 <= L.prof_ev.size();
+    if (timed) cudaEventRecord(L.prof_ev[L.prof_used], L.stream);
+    k_advance<G><<<grid_for((long long)L.d.n_games * 32, 32 * WARPS_PER_CTA), 32 * WARPS_PER_CTA, 0, L.stream>>>(L.d, L.par);
     BB_CUDA(cudaGetLastError());
-    if (timed) cudaEventRecord(prof_ev[prof_used + 1], stream);
+    if (timed) cudaEventRecord(L.prof_ev[L.prof_used + 1], L.stream);
     host_ticks++;
     host_launches++;
-    const int* count = &d.ctl->req[par];
+    const int* count = &L.d.ctl->req[L.par];
     if (cfg.evaluator == BB_EVAL_KAT) {
-      int rc = launch_kat(G::ID, d.req_state, d.n_games, count, d.resp_policy, d.resp_value, stream);
+      int rc = launch_kat(G::ID, L.d.req_state, L.d.n_games, count, L.d.resp_policy, L.d.resp_value, L.stream);
       if (rc) return rc;
       host_launches++;
     } else if (cfg.evaluator == BB_EVAL_NET) {
       if (!net) { set_error("evaluator is BB_EVAL_NET but no network is loaded"); return BB_ESTATE; }
-      int rc = net_forward(net, d.req_state, d.n_games, count, d.resp_policy, d.resp_value, stream);
+      int rc = net_forward(net, L.d.req_state, L.d.n_games, count, L.d.resp_policy, L.d.resp_value, L.stream);
       if (rc) return rc;
       host_launches++;
     }
-    if (timed) { cudaEventRecord(prof_ev[prof_used + 2], stream); prof_used += 3; }
-    par ^= 1u;
+    if (timed) { cudaEventRecord(L.prof_ev[L.prof_used + 2], L.stream); L.prof_used += 3; }
+    L.par ^= 1u;
     return BB_OK;
   }
   int profile(int enable, int max_ticks) override {
     prof = enable != 0;
-    prof_used = 0;
-    while (prof && prof_ev.size() < (size_t)max_ticks * 3) {
-      cudaEvent_t e;
-      BB_CUDA(cudaEventCreate(&e));
-      prof_ev.push_back(e);
+    for (Lane& L : lanes) {
+      L.prof_used = 0;
+      while (prof && L.prof_ev.size() < (size_t)max_ticks * 3) {
+        cudaEvent_t e;
+        BB_CUDA(cudaEventCreate(&e));
+        L.prof_ev.push_back(e);
+      }
     }
     return BB_OK;
   }
   int profile_read(double* adv_ms, double* eval_ms, int* ticks) override {
-    BB_CUDA(cudaStreamSynchronize(stream));
     double a = 0, b = 0;
-    for (size_t i = 0; i + 2 < prof_used + 0 && i < prof_used; i += 3) {
-      float t0 = 0, t1 = 0;
-      cudaEventElapsedTime(&t0, prof_ev[i], prof_ev[i + 1]);
-      cudaEventElapsedTime(&t1, prof_ev[i + 1], prof_ev[i + 2]);
-      a += t0;
-      b += t1;
+    size_t n = 0;
+    for (Lane& L : lanes) {
+      BB_CUDA(cudaStreamSynchronize(L.stream));
+      for (size_t i = 0; i + 2 < L.prof_used; i += 3) {
+        float t0 = 0, t1 = 0;
+        cudaEventElapsedTime(&t0, L.prof_ev[i], L.prof_ev[i + 1]);
+        cudaEventElapsedTime(&t1, L.prof_ev[i + 1], L.prof_ev[i + 2]);
+        a += t0;
+        b += t1;
+      }
+      n += L.prof_used / 3;
     }
     if (adv_ms) *adv_ms = a;
     if (eval_ms) *eval_ms = b;
-    if (ticks) *ticks = (int)(prof_used / 3);
+    if (ticks) *ticks = (int)n;
     return BB_OK;
   }
-  // snapshot of the control block after the ticks enqueued so far (async; wait on snap_ev[i])
-  int post_snapshot(int i) {
-    snap[i].par = par ^ 1u;                                    // parity of the last enqueued tick
-    BB_CUDA(cudaMemcpyAsync(&snap[i].ctl, d.ctl, sizeof(TickCtl), cudaMemcpyDeviceToHost, stream));
-    BB_CUDA(cudaMemcpyAsync(&snap[i].moves, &d.counters->moves, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
-    BB_CUDA(cudaEventRecord(snap_ev[i], stream));
+  // snapshot of a lane's control block after the ticks enqueued so far (async; wait on snap_ev[i])
+  int post_snapshot(Lane& L, int i) {
+    L.snap[i].par = L.par ^ 1u;                                // parity of the last enqueued tick
+    BB_CUDA(cudaMemcpyAsync(&L.snap[i].ctl, L.d.ctl, sizeof(TickCtl), cudaMemcpyDeviceToHost, L.stream));
+    BB_CUDA(cudaMemcpyAsync(&L.snap[i].moves, &L.d.counters->moves, sizeof(unsigned long long), cudaMemcpyDeviceToHost, L.stream));
+    BB_CUDA(cudaEventRecord(L.snap_ev[i], L.stream));
     return BB_OK;
   }
-  int wait_snapshot(int i) {
-    BB_CUDA(cudaEventSynchronize(snap_ev[i]));
-    last_active = snap[i].ctl.active[snap[i].par];
-    last_req = snap[i].ctl.req[snap[i].par];
+  // wait for snapshot i of every lane; totals over lanes
+  int wait_snapshots(int i, unsigned long long* moves) {
+    last_active = last_req = 0;
+    unsigned long long m = 0;
+    for (Lane& L : lanes) {
+      BB_CUDA(cudaEventSynchronize(L.snap_ev[i]));
+      last_active += L.snap[i].ctl.active[L.snap[i].par];
+      last_req += L.snap[i].ctl.req[L.snap[i].par];
+      m += L.snap[i].moves;
+    }
+    if (moves) *moves = m;
     return BB_OK;
   }
-  // Tick until `done(snapshot index)` holds.  Bursts are double-buffered: the next burst is
-  // already queued while the host waits for the previous snapshot, so the GPU never idles on the
-  // host round trip (the price is one surplus burst of near-empty ticks at the end).
+  int burst_all(int burst, int snap_i) {
+    int rc;
+    for (int t = 0; t < burst; ++t)
+      for (Lane& L : lanes) if ((rc = tick(L))) return rc;         // interleaved so the streams fill evenly
+    for (Lane& L : lanes) if ((rc = post_snapshot(L, snap_i))) return rc;
+    return BB_OK;
+  }
+  // Tick all lanes until done(active slots, moves played) holds.  Bursts are double-buffered: the
+  // next burst is already queued while the host waits for the previous snapshot, so the GPU never
+  // idles on the host round trip (the price is one surplus burst of near-empty ticks at the end).
   template <class Done>
   int tick_until(Done done) {
     const int burst = 16;
     int rc, i = 0;
-    using clk = std::chrono::steady_clock;
-    const bool trace = getenv("BB_TRACE") != nullptr;
-    double t_launch = 0, t_wait = 0;
-    long n_ticks = 0;
-    auto t0 = clk::now();
-    for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
-    if ((rc = post_snapshot(0))) return rc;
-    n_ticks += burst;
+    if ((rc = burst_all(burst, 0))) return rc;
     for (;;) {
-      auto a = clk::now();
-      for (int t = 0; t < burst; ++t) if ((rc = tick())) return rc;
-      if ((rc = post_snapshot(i ^ 1))) return rc;
-      n_ticks += burst;
-      auto b = clk::now();
-      if ((rc = wait_snapshot(i))) return rc;
-      auto c = clk::now();
-      t_launch += std::chrono::duration<double>(b - a).count();
-      t_wait += std::chrono::duration<double>(c - b).count();
-      if (done(i)) break;
+      if ((rc = burst_all(burst, i ^ 1))) return rc;
+      unsigned long long moves = 0;
+      if ((rc = wait_snapshots(i, &moves))) return rc;
+      if (done(last_active, moves)) break;
       i ^= 1;
     }
-    if ((rc = wait_snapshot(i ^ 1))) return rc;
-    if (trace)
-      fprintf(stderr, "[bb trace] %ld ticks in %.3f s: host launching %.3f s, host waiting %.3f s\n", n_ticks,
-              std::chrono::duration<double>(clk::now() - t0).count(), t_launch, t_wait);
+    return wait_snapshots(i ^ 1, nullptr);
+  }
+  int sync_lanes() {
+    for (Lane& L : lanes) BB_CUDA(cudaStreamSynchronize(L.stream));
     return BB_OK;
   }
   int run(int* pending) override {
     BB_CUDA(cudaSetDevice(cfg.device));
     int rc;
+    BB_CUDA(cudaStreamSynchronize(stream));                     // whole-engine kernels (begin_move ...) before the lanes tick
     if (cfg.evaluator == BB_EVAL_EXTERNAL) {
-      if ((rc = tick())) return rc;
-      if ((rc = post_snapshot(0))) return rc;
-      if ((rc = wait_snapshot(0))) return rc;
+      if ((rc = tick(lanes[0]))) return rc;
+      if ((rc = post_snapshot(lanes[0], 0))) return rc;
+      if ((rc = wait_snapshots(0, nullptr))) return rc;
       if (pending) *pending = last_req;
       return BB_OK;
     }
-    rc = tick_until([&](int i) { return snap[i].ctl.active[snap[i].par] == 0; });
+    rc = tick_until([&](int active, unsigned long long) { return active == 0; });
     if (pending) *pending = 0;
     return rc;
   }
@@ -443,12 +500,10 @@ struct EngineT : bb_engine {
     }
     int rc = reset(nullptr);
     if (rc) return rc;
-    d.autoplay = 1;
-    d.play_limit = play_limit;
-    d.temp_mode = temp == 1.0 ? 1 : 0;
+    set_mode(1, 0, play_limit, temp == 1.0 ? 1 : 0);
     rc = begin_move(play_limit);
     if (!rc) rc = run(nullptr);
-    d.autoplay = 0;
+    set_mode(0, 0, play_limit, 0);
     return rc;
   }
   // steady-state stepping: every slot plays n_moves moves (finished games restart in place)
@@ -458,14 +513,10 @@ struct EngineT : bb_engine {
     if (n_moves <= 0) { set_error("n_moves must be > 0"); return BB_EINVAL; }
     BB_CUDA(cudaSetDevice(cfg.device));
     if (u_host) BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
-    d.autoplay = 1;
-    d.refill = 1;
-    d.play_limit = play_limit;
-    d.temp_mode = temp == 1.0 ? 1 : 0;
+    set_mode(1, 1, play_limit, temp == 1.0 ? 1 : 0);
     int rc = begin_move_budget(play_limit, n_moves);
     if (!rc) rc = run(nullptr);
-    d.autoplay = 0;
-    d.refill = 0;
+    set_mode(0, 0, play_limit, 0);
     return rc;
   }
   // steady state without a per-move barrier: slots keep playing (and restarting) until the engine
@@ -476,19 +527,17 @@ struct EngineT : bb_engine {
     if (target_moves <= 0) { set_error("target_moves must be > 0"); return BB_EINVAL; }
     BB_CUDA(cudaSetDevice(cfg.device));
     if (u_host) BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
-    d.autoplay = 1;
-    d.refill = 1;
-    d.play_limit = play_limit;
-    d.temp_mode = temp == 1.0 ? 1 : 0;
+    set_mode(1, 1, play_limit, temp == 1.0 ? 1 : 0);
     int rc = begin_move_budget(play_limit, -1);
-    if (!rc) rc = post_snapshot(0);
-    if (!rc) rc = wait_snapshot(0);
+    if (!rc) rc = sync_lanes();
+    unsigned long long start = 0;
+    for (Lane& L : lanes) if (!rc) rc = post_snapshot(L, 0);
+    if (!rc) rc = wait_snapshots(0, &start);
     if (!rc) {
-      const unsigned long long goal = snap[0].moves + (unsigned long long)target_moves;
-      rc = tick_until([&](int i) { return snap[i].moves >= goal || snap[i].ctl.active[snap[i].par] == 0; });
+      const unsigned long long goal = start + (unsigned long long)target_moves;
+      rc = tick_until([&](int active, unsigned long long moves) { return moves >= goal || active == 0; });
     }
-    d.autoplay = 0;
-    d.refill = 0;
+    set_mode(0, 0, play_limit, 0);
     return rc;
   }
   void* stream_handle() override { return (void*)stream; }
@@ -513,15 +562,20 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int counters(bb_counters* out, int do_reset) override {
-    Counters c;
-    BB_CUDA(cudaStreamSynchronize(stream));
-    BB_CUDA(cudaMemcpy(&c, d.counters, sizeof c, cudaMemcpyDeviceToHost));
-    out->sims = c.sims; out->evals = c.evals; out->nodes = c.nodes; out->expansions = c.expansions;
-    out->select_steps = c.select_steps; out->moves = c.moves; out->games_done = c.games_done;
-    out->ticks = host_ticks; out->kernel_launches = host_launches;
-    if (do_reset) { BB_CUDA(cudaMemset(d.counters, 0, sizeof c)); host_ticks = host_launches = 0; }
+    std::vector<Counters> c(lanes.size());
+    int rc = sync_lanes();
+    if (rc) return rc;
+    BB_CUDA(cudaMemcpy(c.data(), counters_dev, c.size() * sizeof(Counters), cudaMemcpyDeviceToHost));
+    memset(out, 0, sizeof *out);
+    for (const Counters& x : c) {
+      out->sims += x.sims; out->evals += x.evals; out->nodes += x.nodes; out->expansions += x.expansions;
+      out->select_steps += x.select_steps; out->moves += x.moves; out->games_done += x.games_done;
+    }
+    out->ticks = host_ticks / lanes.size(); out->kernel_launches = host_launches;
+    if (do_reset) { BB_CUDA(cudaMemset(counters_dev, 0, c.size() * sizeof(Counters))); host_ticks = host_launches = 0; }
     return BB_OK;
   }
+  int n_lanes() override { return (int)lanes.size(); }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -596,5 +650,6 @@ int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off
   return e->records_device(nm, win, st, off, pa, pp, ch);
 }
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
+int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
 
 }  // extern "C"

@@ -224,7 +224,7 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
           BB_ASSERT(rh.child_base + (uint32_t)k <= s.n_nodes && s.ply < E.max_plies);
           int j;
           if (E.temp_mode == 1) {
-            const int row = (int)(((unsigned)g + s.game_no) % (unsigned)E.n_games);   // refill: next game, next row
+            const int row = (int)(((unsigned)g + s.game_no) % (unsigned)E.n_total);   // refill: next game, next row
             j = sample_child(nodes + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
           } else {
             double u;
@@ -277,8 +277,8 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
 template <class G>
 __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_advance(EngineDev<G> E, unsigned par) {
   __shared__ WarpScratch s_ws[WARPS_PER_CTA];
-  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (g < E.n_games) advance_slot(E, g, par, s_ws[threadIdx.x >> 5]);
+  const int gl = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // lane-local slot
+  if (gl < E.n_games) advance_slot(E, E.g0 + gl, par, s_ws[threadIdx.x >> 5]);
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();

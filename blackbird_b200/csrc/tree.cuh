@@ -97,7 +97,9 @@ struct EngineDev {                // passed to kernels by value
   Slot<G>* slots;
   Node* nodes;                    // [n_games][2][node_cap]
   uint32_t* path;                 // [n_games][PATH_LEN] descent paths of blocked slots
-  int n_games;
+  int n_games;                    // slots served by this launch (a lane of the engine, or all of them)
+  int g0;                         // first global slot id of the lane
+  int n_total;                    // slots in the whole engine
   uint32_t node_cap;
   int search, max_depth, max_plies;
   int step_budget;                // tree levels a slot may descend per tick before it yields (keeps ticks short)

@@ -134,7 +134,7 @@ class Engine(object):
     """n_games concurrent searches / self-play games on one GPU."""
 
     def __init__(self, game, search='dynamic', n_games=1, max_depth=10, exploration_rate=0.85, evaluator='kat',
-                 node_cap=None, max_plies=None, play_limit_hint=100, device=0):
+                 node_cap=None, max_plies=None, play_limit_hint=100, device=0, lanes=0):
         _need_cuda()
         self.game, self.search, self.n_games, self.device = game, search, int(n_games), device
         self.A = _ACTIONS[game]
@@ -148,9 +148,11 @@ class Engine(object):
         cfg.evaluator = {'kat': _lib.EVAL_KAT, 'net': _lib.EVAL_NET, 'external': _lib.EVAL_EXTERNAL}[evaluator]
         cfg.n_games, cfg.node_cap, cfg.max_plies, cfg.device = self.n_games, self.node_cap, self.max_plies, device
         cfg.exploration_rate = float(exploration_rate)
+        cfg.lanes = int(lanes)
         self._h = C.c_void_p()
         check(lib.bb_engine_create(C.byref(cfg), C.byref(self._h)))
         self.evaluator = evaluator
+        self.lanes = lib.bb_engine_lanes(self._h)
 
     def close(self):
         if getattr(self, '_h', None):

@@ -80,7 +80,9 @@ typedef struct bb_config {
   int32_t device;            /* CUDA device ordinal                                              */
   double exploration_rate;   /* MCTS.ExplorationRate (MCTS.py:119)                               */
   int32_t value_f64;         /* 0: Node.Value accumulates in f32 (Model path, A.9); 1: f64       */
-  int32_t reserved[7];
+  int32_t lanes;             /* independent sub-populations of slots (own stream + mailbox each) whose ticks
+                                overlap on the GPU; 0 = choose (2 from 512 slots up).  Results do not depend on it. */
+  int32_t reserved[6];
 } bb_config;
 
 int bb_engine_create(const bb_config* cfg, bb_engine** out);
@@ -174,6 +176,7 @@ typedef struct bb_counters {
   uint64_t sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
 } bb_counters;
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset);
+int bb_engine_lanes(bb_engine* e);   /* lanes the engine runs with */
 
 #ifdef __cplusplus
 }

@@ -183,3 +183,20 @@ def test_arena_overflow_is_loud(mods):
     with pytest.raises(MemoryError):
         eng.selfplay(50, 1.0, u)
     eng.close()
+
+
+def test_lanes_do_not_change_results(mods):
+    """Lanes (sub-populations of slots ticking on their own streams) are a scheduling device:
+    records, winners and counters are the same for 1 and 3 lanes."""
+    engine, records = mods
+    G, P = 48, 24
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(42) for g in range(G)])
+    outs = []
+    for lanes in (1, 3):
+        eng = engine.Engine('Connect4', 'fixed', n_games=G, evaluator='kat', play_limit_hint=P, lanes=lanes)
+        assert eng.lanes == lanes
+        eng.selfplay(P, 1.0, u)
+        c = eng.counters()
+        outs.append((records.build_records(eng), c['sims'], c['evals'], c['nodes'], c['moves']))
+        eng.close()
+    assert outs[0] == outs[1]
