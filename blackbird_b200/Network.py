@@ -1,0 +1,122 @@
+"""Network mirror: the inference half of the reference's TF session wrapper (Network.py:9-64).
+
+getPolicy / getEvaluation take the reference's input array (int8 [n, H, W, C] from
+BoardState.AsInputArray) and return policy f32 [A] / value f32 of the first row, computed by the
+engine's network kernels (bb_net_forward) -- there is no TensorFlow and no CPU path here.  Weights
+are a flat fp32 vector in the layout of netinit.py / DESIGN.md "weight layout"; a fresh Network is
+randomly initialised like tf.global_variables_initializer (Network.py:24).  train() is trainer
+side; saveModel / loadModel keep the reference's directory convention but store
+the flat vector (TF Saver bundles are SURVEY.md 8f-4).
+"""
+import os
+
+import numpy as np
+import torch
+
+from . import engine as _engine
+from . import netinit
+
+
+def states_from_planes(game, planes, device=0):
+    """Packed states whose AsInputArray() equals `planes` (int8 [n, H, W, C]).  The planes do not
+    carry everything (e.g. whose move it is in DragonChess), only what the network sees."""
+    planes = np.asarray(planes)
+    n = planes.shape[0]
+    if game == 'DragonChess':
+        from .DragonChess import BoardState
+        cells = np.zeros((n, 64), np.int8)
+        for code, ch in BoardState.piece_map.items():
+            cells[planes[:, :, :, ch].reshape(n, 64) == 1] = code
+        castle = sum((planes[:, 0, 0, 12 + i] == 1).astype(np.uint8) << i for i in range(4))
+        second = planes[:, 0, 0, 16] == 1                            # plane 16: White's second move (A.18)
+        player = np.where(second, 1, 2).astype(np.uint8)
+        prev = np.ones(n, np.uint8)
+        return _engine.pack(game, cells, player, prev, castle, device=device)
+    h, w = planes.shape[1:3]
+    cells = (planes[:, :, :, 0] + 2 * planes[:, :, :, 1]).reshape(n, h * w).astype(np.int8)
+    player = np.where(planes[:, 0, 0, 2] == 1, 1, 2).astype(np.uint8)
+    return _engine.pack(game, cells, player, np.zeros(n, np.uint8), None, device=device)
+
+
+class Network(object):
+    PRECISION = 'fp32'                 # 'fp32': 1e-5 parity kernel; 'bf16': tcgen05 kernel (bulk self-play default)
+
+    def __init__(self, name, networkConstructor=None, tensorflowConfig={}, game=None, seed=0, device=0):
+        self._net_name = name
+        self._net_game = game
+        self._net_device = device
+        self._net_eng = None
+        self._net_loaded_weights = None
+        self.batchCount = 0
+        if self.loadModel(name):                                      # Network.py:21: a saved network wins
+            return
+        if networkConstructor is None:
+            raise FileNotFoundError('no saved network %r and no networkConfig to build one' % name)
+        self._net_shape = networkConstructor
+        cin = _engine.plane_shape(game)[2]
+        self.setWeights(netinit.random_weights(cin, networkConstructor.policyShape, blocks=networkConstructor.blocks,
+                                               filters=networkConstructor.filters, dense=networkConstructor.dense, seed=seed))
+        self.saveModel(name)                                          # Network.py:25
+
+    # -- weights ----------------------------------------------------------------------------------
+    def setWeights(self, flat):
+        self._net_loaded_weights = np.ascontiguousarray(flat, dtype=np.float32)
+        if self._net_eng is not None:
+            self._load_network_into(self._net_eng, precision=self.PRECISION)
+        eng = getattr(self, '_eng', None)                             # a live search engine (MCTS mirror)
+        if eng is not None and eng.evaluator == 'net':
+            self._load_network_into(eng)
+
+    def getWeights(self):
+        return self._net_loaded_weights
+
+    def _load_network_into(self, eng, precision=None, epsilon=None, seed=0):
+        s = self._net_shape
+        eng.load_network(self._net_loaded_weights, s.blocks, s.filters, s.dense,
+                         epsilon=s.epsilon if epsilon is None else epsilon, alpha=s.alpha, seed=seed,
+                         precision=precision or self.PRECISION)
+
+    def _forward(self, planes):
+        if self._net_eng is None:
+            self._net_eng = _engine.Engine(self._net_game, 'dynamic', n_games=1, evaluator='net', node_cap=64,
+                                           device=self._net_device, lanes=1)
+            self._load_network_into(self._net_eng)
+        st = states_from_planes(self._net_game, planes, device=self._net_device)
+        pol, val = self._net_eng.net_forward(st)
+        torch.cuda.synchronize()
+        return pol.cpu().numpy(), val.cpu().numpy()
+
+    # -- reference API (Network.py:48-64) ---------------------------------------------------------
+    def getEvaluation(self, state):
+        return self._forward(state)[1][0]
+
+    def getPolicy(self, state):
+        return self._forward(state)[0][0]
+
+    def train(self, state, eval, policy, learningRate=0.01, teacher=None):
+        raise NotImplementedError('training (Network.py:66-84, NetworkFactory.py:185-245) is trainer side: SURVEY.md 8f-1')
+
+    def saveModel(self, name=None):
+        name = name or getattr(self, 'Name', None) or self._net_name   # Network.py:90-91 uses Model.Name
+        saveDir = os.path.join('blackbird_models', name)
+        os.makedirs(saveDir, exist_ok=True)
+        s = self._net_shape
+        np.savez(os.path.join(saveDir, 'best.npz'), weights=self._net_loaded_weights,
+                 shape=np.array([s.blocks, s.filters, s.dense, s.policyShape]), noise=np.array([s.epsilon, s.alpha]))
+
+    def loadModel(self, name):
+        path = os.path.join('blackbird_models', name, 'best.npz')
+        if not os.path.isfile(path):
+            return False
+        from .NetworkFactory import NetworkFactory
+        z = np.load(path)
+        b, f, d, a = (int(x) for x in z['shape'])
+        self._net_shape = NetworkFactory({'blocks': b, 'filters': f, 'eval': {'dense': d},
+                                          'policy': {'dirichlet': {'epsilon': float(z['noise'][0]), 'alpha': float(z['noise'][1])}}}, a)
+        self.setWeights(z['weights'])
+        return True
+
+    def __del__(self):
+        eng = getattr(self, '_net_eng', None)
+        if eng is not None:
+            eng.close()

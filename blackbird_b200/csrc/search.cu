@@ -380,9 +380,11 @@ struct EngineT : bb_engine {
     int rc;
     BB_CUDA(cudaStreamSynchronize(stream));                     // whole-engine kernels (begin_move ...) before the lanes tick
     if (cfg.evaluator == BB_EVAL_EXTERNAL) {
-      if ((rc = tick(lanes[0]))) return rc;
-      if ((rc = post_snapshot(lanes[0], 0))) return rc;
-      if ((rc = wait_snapshots(0, nullptr))) return rc;
+      do {                                                       // a tick can end on the step budget with nothing to ask
+        if ((rc = tick(lanes[0]))) return rc;
+        if ((rc = post_snapshot(lanes[0], 0))) return rc;
+        if ((rc = wait_snapshots(0, nullptr))) return rc;
+      } while (last_req == 0 && last_active > 0);
       if (pending) *pending = last_req;
       return BB_OK;
     }

@@ -1,0 +1,156 @@
+"""GPU: the reference-facing Python surface (blackbird_b200.MCTS / FixedMCTS / DynamicMCTS /
+Blackbird / DataManager) used the way main.py and Blackbird.py use the reference, checked against
+golden vectors produced by the unmodified reference (tests/golden/make_golden.py)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+
+
+@pytest.fixture(scope='module')
+def bb():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    import blackbird_b200.Blackbird as Blackbird
+    from blackbird_b200 import Connect4, DragonChess, TicTacToe
+    from blackbird_b200.DynamicMCTS import DynamicMCTS
+    from blackbird_b200.FixedMCTS import FixedMCTS
+    games = {'TicTacToe': TicTacToe.BoardState, 'Connect4': Connect4.BoardState, 'DragonChess': DragonChess.BoardState}
+    return dict(Blackbird=Blackbird, games=games, DynamicMCTS=DynamicMCTS, FixedMCTS=FixedMCTS)
+
+
+# Appendix B.2 integer evaluator, written against the reference's Network interface (planes in,
+# f32 policy / value out) exactly as tests/golden/make_golden.py patches it over the TF wrapper.
+def _h(planes):
+    x = planes.astype(np.int64).ravel()
+    return int(sum((j + 1) * int(v) for j, v in enumerate(x)) % 1000003)
+
+
+class KatNet(object):
+    def getPolicy(self, planes):
+        h = _h(planes)
+        n = [1 + (h * (i + 1)) % 97 for i in range(self._nActions)]
+        return np.array(n, dtype=np.float32) / np.float32(sum(n))
+
+    def getEvaluation(self, planes):
+        h = _h(planes)
+        return np.float32((h % 1009) * 2 - 1008) / np.float32(1009)
+
+
+def wbits(v):
+    return 0 if isinstance(v, int) else np.float32(v).tobytes().hex()
+
+
+@pytest.mark.parametrize('index', [0, 1, 2, 3, 5, 6, 7])
+def test_findmove_moveroot_vs_reference(bb, golden, index):
+    """np.random.seed(0); FindMove(state, 1); MoveRoot(next) ... on a search object whose evaluator
+    is plain Python -- visit counts, chosen action, Root.WinRate() bits, probabilities."""
+    case = golden('mcts_kat.json')[index]
+    base = bb['DynamicMCTS'] if case['kind'] == 'dynamic' else bb['FixedMCTS']
+    cls = type('KatSearch', (base, KatNet), {})
+    m = cls(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=case['playLimit'])
+    state_cls = bb['games'][case['game']]
+    m._nActions = state_cls.LegalMoves
+    np.random.seed(case['seed'])
+    s = state_cls()
+    for i, want in enumerate(case['moves']):
+        nxt, v, probs = m.FindMove(s, 1)
+        plays = m.Root.ChildPlays()
+        nz = np.flatnonzero(plays).astype(int).tolist()
+        action = next(a for a in range(len(plays)) if m.Root.Children[a] is not None and m._last_action == a)
+        got = {'plays_idx': nz, 'plays': plays[nz].astype(int).tolist(), 'action': action, 'winrate': wbits(v),
+               'root_plays': int(m.Root.Plays), 'probs_sha': hashlib.sha256(probs.tobytes()).hexdigest()[:16]}
+        assert got == want, (case['game'], case['kind'], i, got, want)
+        applied = s.Copy()
+        applied.ApplyAction(action)
+        assert applied == nxt
+        s = nxt
+        m.MoveRoot(s)
+        assert m.Root is None or m.Root.State == s
+
+
+def test_api_errors(bb):
+    """Argument checks of MCTS.FindMove / FixedMCTS.__init__ (MCTS.py:170-182, FixedMCTS.py:15-16)."""
+    with pytest.raises(ValueError, match='MaxDepth for MCTS must be > 0.'):
+        bb['FixedMCTS'](maxDepth=0, explorationRate=0.85)
+    m = type('S', (bb['DynamicMCTS'], KatNet), {})(explorationRate=0.85)
+    m._nActions = 7
+    with pytest.raises(TypeError, match='State not of type GameState'):
+        m.FindMove(object())
+    s = bb['games']['Connect4']()
+    with pytest.raises(ValueError, match='Not enough information to decide a stop time.'):
+        m.FindMove(s)
+    nxt, v, probs = m.FindMove(s, 1, playLimit=20)
+    assert probs.shape == (7,) and abs(probs.sum() - 1) < 1e-12 and m.Root.Plays == 20
+    other = s.Copy()
+    other.ApplyAction(3)
+    with pytest.raises(AssertionError):                     # Root primed for another state (MCTS.py:193)
+        m.FindMove(other, 1, playLimit=20)
+    m.DropRoot()
+    assert m.Root is None
+    m.MoveRoot(other)                                       # no-op on a dropped root (MCTS.py:274-275)
+    m.FindMove(other, 1, playLimit=20)
+    # wall-clock mode (A.25): runs, result not deterministic
+    m.DropRoot()
+    nxt, v, probs = m.FindMove(s, 1, moveTime=0.05)
+    assert m.Root.Plays >= 8
+
+
+def test_generate_training_samples_records(bb, golden, tmp_path, monkeypatch):
+    """Blackbird.GenerateTrainingSamples(model, 1, 1) -> Conn.PutGames -> sqlite -> GetGames: the bytes the
+    unmodified reference wrote for the same seeds (records.json), through the mirror's public API."""
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    for case in golden('records.json'):
+        base = B.Model if case['kind'] == 'dynamic' else B.FixedModel
+        cls = type('KatModel', (base,), {'_SELFPLAY_EVALUATOR': 'kat'})
+        cfg = {'maxDepth': 10, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': case['playLimit'],
+               'temperature': {'exploration': 1, 'exploitation': 0.1}}
+        net = {'blocks': 1, 'filters': 16, 'eval': {'dense': 16}, 'policy': {'dirichlet': {'alpha': 0.2, 'epsilon': 0.0}}}
+        name = 'gold_%s_%s_%d' % (case['game'], case['kind'], case['seed'])
+        m = cls(bb['games'][case['game']], name, cfg, net, {})
+        np.random.seed(case['seed'])
+        n = B.GenerateTrainingSamples(m, 1, 1)
+        got = m.Conn.GetGames(m.Name, m.Version)
+        assert n == len(got)
+        assert [bytes(r).hex() for r in got] == case['records'], (case['game'], case['kind'], case['seed'])
+        ex = B.ExampleState.FromSerialized(got[0])
+        assert ex.Board.shape == tuple(m.Game().AsInputArray().shape) and ex.MctsPolicy.shape == (m.Game.LegalMoves,)
+        assert B.ExampleState(ex.MctsEval[0], ex.MctsPolicy, ex.Board).SerializeState() == bytes(got[0])
+        m.Conn.Close()
+    assert os.path.isfile(tmp_path / 'data' / 'blackbird.db')
+
+
+def test_model_network_selfplay_and_arena(bb, tmp_path, monkeypatch):
+    """main.py's sequence with the template config on TicTacToe (BASELINE configs[0]): Model(...),
+    GenerateTrainingSamples with the built-in network, then a TestPrevious-style arena game."""
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    cfg = {'maxDepth': 10, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': 10,
+           'temperature': {'exploration': 1, 'exploitation': 0.1}}
+    net = {'hasTeacher': False, 'blocks': 4, 'filters': 16, 'eval': {'dense': 16},
+           'policy': {'dirichlet': {'epsilon': 0.3, 'alpha': 0.2}}}
+    model = B.FixedModel(bb['games']['TicTacToe'], 'Blackbird', cfg, net, {'GPUOptions': {'per_process_gpu_memory_fraction': 0.25}})
+    assert model.Version == 1
+    n = B.GenerateTrainingSamples(model, 64, cfg['temperature']['exploration'])
+    recs = model.Conn.GetGames(model.Name, model.Version)
+    assert n == len(recs) and 64 * 6 <= n <= 64 * 10
+    ex = B.ExampleState.FromSerialized(recs[0])
+    assert ex.Board.shape == (1, 3, 3, 3) and ex.MctsPolicy.shape == (9,)
+    assert abs(ex.MctsPolicy.sum() - 1) < 1e-12
+    # network hooks answer in the reference's shapes
+    s = model.Game()
+    p, v = model.getPolicy(s.AsInputArray()), model.getEvaluation(s.AsInputArray())
+    assert p.shape == (9,) and p.dtype == np.float32 and -1 <= float(v) <= 1
+    pri = model.GetPriors(s)
+    assert abs(pri.sum() - 1) < 1e-12
+    assert 0 <= float(model.SampleValue(s, 1)) <= 1
+    # arena: two engines follow one game
+    res = B.TestModels(model, model.LastVersion(), 0.1, 1)
+    assert res in (1, 0, -1)
+    model.Conn.Close()
