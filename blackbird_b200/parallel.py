@@ -1,0 +1,120 @@
+"""Multi-GPU self-play: independent game shards, one collective to collect the examples.
+
+The reference plays its games one after another in one process (Blackbird.py:238) and has no
+distributed code; SURVEY.md 8(e) defines the sharding used here.  One process per GPU
+(torch.distributed, NCCL over NVLink on the B200 box, gloo in the CPU tests):
+
+* global game id g in [0, n_games) lives on rank g // per_rank (contiguous blocks); its move-sampling
+  uniforms come from RandomState(seed0 + g), so every game's record bytes are identical for any
+  number of GPUs (tests/test_parallel_host.py, tests/test_gpu_search.py);
+* there is NO data-path collective during search -- the tree pools never talk to each other;
+* after a batch of games one all_gather of the fixed-stride raw record buffers (bb_records_device
+  views: packed states, sparse child visit counts, offsets, winners) delivers every example to
+  every rank (the trainer rank reads them; DataManager.PutGames is called by rank 0 only).  The
+  buffers are fixed-stride per slot, so no count exchange is needed; they stay on the GPU for NCCL.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+RAW_KEYS = ('n_moves', 'winner', 'states', 'rec_off', 'pool_actions', 'pool_plays', 'chosen')
+
+
+def shard_range(n_games, rank, world):
+    """Contiguous block of global game ids owned by `rank` (the last ranks may hold one game less)."""
+    base, extra = divmod(n_games, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def game_uniforms(game_ids, max_plies, seed0=1000):
+    """One RandomState stream per GLOBAL game id: the doubles np.random.choice would draw for the
+    game's moves (MCTS.py:336-338)."""
+    return np.stack([np.random.RandomState(seed0 + int(g)).random_sample(max_plies) for g in game_ids]) \
+        if len(game_ids) else np.zeros((0, max_plies))
+
+
+def _records_device_views(eng):
+    """torch views (no copy) of the engine's record buffers on its GPU."""
+    import ctypes as C
+    from ._lib import lib, check
+    ptrs = [C.c_void_p() for _ in range(7)]
+    check(lib.bb_records_device(eng._h, *[C.byref(p) for p in ptrs]))
+    n, mp, cap, sb = eng.n_games, eng.max_plies, lib.bb_records_pool_cap(eng._h), eng.state_bytes
+    shapes = {'n_moves': ((n,), torch.int32), 'winner': ((n,), torch.int32), 'states': ((n, mp + 1, sb), torch.uint8),
+              'rec_off': ((n, mp + 2), torch.int32), 'pool_actions': ((n, cap), torch.int16),
+              'pool_plays': ((n, cap), torch.int32), 'chosen': ((n, mp), torch.int16)}
+    out = {}
+    for key, p in zip(RAW_KEYS, ptrs):
+        shape, dtype = shapes[key]
+        out[key] = _from_ptr(p.value, shape, dtype, eng.device)
+    return out
+
+
+def _from_ptr(ptr, shape, dtype, device):
+    """Wrap a raw device pointer as a tensor through the CUDA array interface (no ownership)."""
+    nbytes = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+
+    class _Holder(object):
+        __cuda_array_interface__ = {'shape': (nbytes,), 'typestr': '|u1', 'data': (int(ptr), False), 'version': 2}
+
+    flat = torch.as_tensor(_Holder(), device=torch.device('cuda', device))
+    return flat.view(dtype).view(*shape)
+
+
+_NP_VIEW = {'rec_off': np.uint32, 'pool_actions': np.uint16, 'pool_plays': np.uint32, 'chosen': np.uint16}
+
+
+def allgather_raw(raw, group=None):
+    """raw: dict of per-rank buffers (torch tensors on this rank's device, or numpy arrays for the
+    gloo/CPU tests), identical shapes on every rank.  Returns numpy arrays with a leading
+    concatenation over ranks in rank order (= global game order for contiguous shards).
+
+    One flat byte buffer per rank and ONE all_gather: the records are small (C4: ~0.9 KB per game),
+    so the collective is latency-bound and a single launch is what matters."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    tensors = {k: (torch.as_tensor(raw[k]) if not torch.is_tensor(raw[k]) else raw[k]) for k in RAW_KEYS}
+    parts = [tensors[k].contiguous().view(-1).view(torch.uint8) for k in RAW_KEYS]
+    flat = torch.cat(parts)
+    if world > 1:
+        gathered = torch.empty((world * flat.numel(),), dtype=torch.uint8, device=flat.device)
+        dist.all_gather_into_tensor(gathered, flat, group=group)
+        gathered = gathered.view(world, flat.numel())
+    else:
+        gathered = flat[None]
+    host = gathered.cpu().numpy()
+    out, off = {}, 0
+    for k, p in zip(RAW_KEYS, parts):
+        t = tensors[k]
+        chunk = host[:, off:off + p.numel()]
+        off += p.numel()
+        arr = np.ascontiguousarray(chunk).view(torch.empty((), dtype=t.dtype).numpy().dtype)
+        arr = arr.reshape((world * t.shape[0],) + tuple(t.shape[1:]))
+        out[k] = arr.view(_NP_VIEW[k]) if k in _NP_VIEW else arr
+    return out
+
+
+def selfplay_sharded(make_engine, n_games, play_limit, temp=1.0, seed0=1000, group=None, gather=True):
+    """Play global games [0, n_games) across the ranks of `group` and all-gather the raw records.
+
+    make_engine(n_slots) -> Engine on this rank's GPU (every rank must build the same configuration).
+    Every rank runs the same number of slots (the largest shard) so the gathered buffers are
+    fixed-stride; surplus slots play a game that is dropped.  Returns (raw_all, owner_slices):
+    raw_all as allgather_raw, owner_slices[r] = (first row of rank r in raw_all, games it owns)."""
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    slots = shard_range(n_games, 0, world)[1]               # rank 0 holds the largest shard
+    lo, hi = shard_range(n_games, rank, world)
+    eng = make_engine(slots)
+    u = np.ones((slots, eng.max_plies))
+    u[:hi - lo] = game_uniforms(range(lo, hi), eng.max_plies, seed0)
+    eng.selfplay(play_limit, temp, u)
+    if gather and world > 1:
+        raw_all = allgather_raw(_records_device_views(eng), group)
+    else:
+        raw_all = eng.records_raw()
+    owners = []
+    for r in range(world if (gather and world > 1) else 1):
+        a, b = shard_range(n_games, r, world) if world > 1 else (0, n_games)
+        owners.append((r * slots, b - a))
+    return eng, raw_all, owners

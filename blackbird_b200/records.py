@@ -44,20 +44,21 @@ def encode_record(evaluation, policy_f64, planes_i8):
 
 
 def build_records(eng, raw=None):
-    """-> list over games of (records: list[bytes], winner code, n_moves)."""
+    """-> list over games of (records: list[bytes], winner code, n_moves).  `raw` defaults to this engine's
+    buffers; the all-gathered buffers of several GPUs (parallel.allgather_raw) have more rows than eng.n_games."""
     raw = raw or eng.records_raw()
     game, A = eng.game, eng.A
     h, w, c = _engine.plane_shape(game)
     n_moves = raw['n_moves']
     # decode every recorded state's planes + player in one batched kernel call
-    idx = [(g, r) for g in range(eng.n_games) for r in range(int(n_moves[g]) + 1)]
+    idx = [(g, r) for g in range(len(n_moves)) for r in range(int(n_moves[g]) + 1)]
     flat = np.stack([raw['states'][g, r] for g, r in idx]) if idx else np.zeros((0, eng.state_bytes), np.uint8)
     st = torch.as_tensor(flat).to(torch.device('cuda', eng.device))
     planes = _engine.planes(game, st).cpu().numpy()
     players = _engine.unpack(game, st)[1].cpu().numpy()
     out = []
     k = 0
-    for g in range(eng.n_games):
+    for g in range(len(n_moves)):
         winner = int(raw['winner'][g])
         recs = []
         for r in range(int(n_moves[g]) + 1):

@@ -148,3 +148,18 @@ def test_datamanager_schema_and_roundtrip(lib, tmp_path, monkeypatch):
     assert db.execute("SELECT Name, Version FROM ModelDim ORDER BY ModelKey LIMIT 2").fetchall() == [('RANDOM', 0), ('MCTS', 0)]
     cols = [r[1] for r in db.execute('PRAGMA table_info(GameStateFact)')]
     assert cols == ['GameStateKey', 'ModelKey', 'GameType', 'State']
+
+
+def test_product_does_not_import_oracle():
+    """oracle/ is test infrastructure: no module of the product package may import or execute it."""
+    pkg = os.path.join(ROOT, 'blackbird_b200')
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h')):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r'^\s*(from|import)\s+oracle\b', text, flags=re.M), f
+    import subprocess
+    import sys
+    code = ('import sys; sys.path.insert(0, %r); import blackbird_b200.Blackbird, blackbird_b200.records, blackbird_b200.parallel; '
+            'assert not [m for m in sys.modules if m == "oracle" or m.startswith("oracle.")]') % ROOT
+    subprocess.check_call([sys.executable, '-c', code])
