@@ -7,6 +7,7 @@
 //
 // Persistent grid (one CTA per SM), 256 threads, 2 output cells x 16 filters per thread.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -168,12 +169,12 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 // (hsum[p*4 + {0: value, 1,2: policy}]): value = tanh(dense(relu(dense(1->D)+sum))), policy =
 // softmax(dense(2->A)+sum), noise mix, renormalise (NetworkFactory.py:115-182).  Block-wide.
 template <class G>
-__device__ void heads_finish(const NetParams& np, const float* hsum, float* red, int base, int n, int P,
-                             unsigned long long call, float* __restrict__ policy, float* __restrict__ value) {
+__device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
+                             float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
+                             float* __restrict__ value) {
   constexpr int HW = G::H * G::W;
   const int tid = threadIdx.x, nthreads = blockDim.x;
-  const float* hd = np.head;
-  const int D = np.dense;
+  const int D = np.dense;                               // hd / pol_w / pol_b: np.head / np.pol_w / np.pol_b or copies in shared memory
   const float* d1w = hd + 17 + 34;
   const float* d1b = d1w + D;
   const float* d2w = d1b + D;
@@ -192,7 +193,7 @@ __device__ void heads_finish(const NetParams& np, const float* hsum, float* red,
       float m = -INFINITY;
 #pragma unroll
       for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-        z[a] = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)HW * np.pol_b[a]));
+        z[a] = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
         m = fmaxf(m, z[a]);
       }
       float sum = 0.f;
@@ -216,7 +217,7 @@ __device__ void heads_finish(const NetParams& np, const float* hsum, float* red,
       float* out = policy + (size_t)(base + p) * G::A;
       float m = -INFINITY;
       for (int a = tid; a < G::A; a += nthreads) {
-        float z = fmaf(s0, np.pol_w[a], fmaf(s1, np.pol_w[G::A + a], (float)HW * np.pol_b[a]));
+        float z = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
         out[a] = z;
         m = fmaxf(m, z);
       }
@@ -342,7 +343,7 @@ k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_
       hsum[p * 4 + k] = s;
     }
     __syncthreads();
-    heads_finish<G>(np, hsum, red, base, n, Ge::P, call, policy, value);
+    heads_finish<G>(np, np.head, np.pol_w, np.pol_b, hsum, red, base, n, Ge::P, call, policy, value);
   }
 }
 
@@ -380,15 +381,27 @@ static int net_launch_tc(NetDev* net, const void* states, int n, const int* coun
   static int ctas_per_sm[3] = {1, 1, 1};
   if (!configured[G::ID]) {
     BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     int occ = 1;
-    BB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_net_forward_tc<G>, TC_THREADS, L.total));
+    BB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_net_forward_tc<G>, Ge::THREADS, L.total));
     ctas_per_sm[G::ID] = occ < 1 ? 1 : (occ > 2 ? 2 : occ);
+    if (getenv("BB_DEBUG_OCC")) {
+      cudaFuncAttributes fa;
+      cudaFuncGetAttributes(&fa, k_net_forward_tc<G>);
+      int o2 = 0, o3 = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_net_forward_tc<G>, Ge::THREADS, 40000);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, k_net_forward_tc<G>, 256, L.total);
+      fprintf(stderr, "[bbengine] regs %d static smem %zu local %zu maxthreads %d; occ(smem 40000)=%d occ(256 thr)=%d\n", fa.numRegs,
+              fa.sharedSizeBytes, fa.localSizeBytes, fa.maxThreadsPerBlock, o2, o3);
+    }
+    if (getenv("BB_DEBUG_OCC")) fprintf(stderr, "[bbengine] k_net_forward_tc<%d>: %d threads, %d B smem, occupancy %d CTAs/SM\n", G::ID, Ge::THREADS, L.total, occ);
+    if (const char* e = getenv("BB_TC_CTAS_PER_SM")) ctas_per_sm[G::ID] = atoi(e) > 0 ? atoi(e) : 1;   // tuning knob
     configured[G::ID] = true;
   }
-  const int batches = (n + Ge::NP - 1) / Ge::NP;
+  // the kernel spreads the (device-side) request count evenly over the grid, so launch one full wave
   const int cap = net->sm_count * ctas_per_sm[G::ID];
-  const int grid = batches < cap ? batches : cap;
-  k_net_forward_tc<G><<<grid, TC_THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value);
+  const int grid = n < cap ? n : cap;
+  k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value);
   BB_CUDA(cudaGetLastError());
   if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
   return BB_OK;

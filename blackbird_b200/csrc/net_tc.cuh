@@ -15,23 +15,33 @@
 //   B tile  = one tap's 16x16 weight block (BN folded on the host), bf16, K-major;
 //   D tile  = 128 rows x 16 output channels, fp32, in TMEM (16 columns per tile).
 //
-// One thread issues the 9 (x k-blocks) tcgen05.mma of every tile of the layer and commits each tile
-// to its own mbarrier; all 8 warps then run the epilogue tile by tile while later tiles are still
-// in the tensor pipe: tcgen05.ld (32 lanes x 16 columns per warp), + bias, (+ skip), ReLU, pack to
-// bf16, two 16-byte st.shared per row into the next layer's A buffer.  The last layer's epilogue
-// feeds the heads from the fp32 registers (1x1 convs -> per-cell ReLU -> fixed-order sums).
+// Warp roles (32 * (4 * TILES + 1) threads): the LAST warp issues every tcgen05.mma (one elected
+// lane) and owns the TMEM allocation; each tile has its own four epilogue warps (one per TMEM lane
+// quarter), so all tiles of a layer drain in parallel.  There is no CTA-wide barrier inside the
+// tower: tile t of layer l+1 is issued as soon as the epilogues of tiles t-1, t, t+1 of layer l have
+// arrived on their `ready` mbarriers (the 3x3 halo never reaches further than one tile), and an
+// epilogue starts when the tile's tcgen05.commit arrives on its `full` mbarrier -- layers flow
+// through the tiles as a wavefront.  Epilogue: tcgen05.ld (32 lanes x 16 columns per warp), + bias,
+// (+ skip), ReLU, pack to bf16, two 16-byte st.shared per row into the next layer's A buffer.  The
+// weights arrive with one cp.async.bulk (TMA) while the first batch's planes are decoded.  The
+// last layer's epilogue feeds the heads from the fp32 registers (1x1 convs -> per-cell ReLU ->
+// fixed-order sums).
 #pragma once
 #include <cuda_bf16.h>
 
 namespace bb {
 
-constexpr int TC_THREADS = 256;
+constexpr int TC_HEAD_FLOATS = 384;      // head parameters staged in shared memory: 51 + 3*dense + 1 (+ 3*A when A <= 32)
 constexpr int TC_MARGIN = 16;            // zero rows in front of / behind the raster (|tap offset| <= W+2)
 
 template <class G> struct TcBatch;
-template <> struct TcBatch<TicTacToe> { static constexpr int NP = 32; };     // 32 * 16 rows = 4 tiles
-template <> struct TcBatch<Connect4> { static constexpr int NP = 16; };      // 16 * 56 rows = 7 tiles
-template <> struct TcBatch<DragonChess> { static constexpr int NP = 8; };    // 8 * 81 rows  = 6 tiles (5.06)
+// Largest batch of one CTA: seven 128-row tiles.  A kernel that allocates TMEM runs ONE CTA per SM
+// (cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for any kernel with tcgen05.alloc, and the
+// measured two-wave step agrees), so a launch is one wave of 148 CTAs and the CTA must be able to take
+// its share of a lane's requests (2048 slots / 148 SMs = 14 Connect4 positions) in a single batch.
+template <> struct TcBatch<TicTacToe> { static constexpr int NP = 56; };     // 56 * 16 rows = 896
+template <> struct TcBatch<Connect4> { static constexpr int NP = 14; };      // 14 * 56 rows = 784
+template <> struct TcBatch<DragonChess> { static constexpr int NP = 11; };   // 11 * 81 rows = 891
 
 template <class G>
 struct TcGeom {
@@ -47,7 +57,10 @@ struct TcGeom {
   static constexpr int TMEM_COLS = TILES * 16 <= 32 ? 32 : (TILES * 16 <= 64 ? 64 : (TILES * 16 <= 128 ? 128 : 256));
   static_assert(LW + 1 <= TC_MARGIN, "tap offsets must stay inside the margin");
   static_assert(TILES * 16 <= 256, "too many tiles for TMEM");
-  static_assert(TILES <= 8, "one mbarrier per tile");
+  static_assert(TILES <= 8, "two tiles per epilogue warp group");
+  static constexpr int EPI_GROUPS = 4;                      // groups of four warps (one per TMEM lane quarter); group g drains tiles g, g+4
+  static constexpr int EPI_THREADS = EPI_GROUPS * 128;
+  static constexpr int THREADS = EPI_THREADS + 32;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -86,6 +99,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "setp.ne.b32 p, %4, 0;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
       "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// warp-uniform variant: the whole warp executes it, one elected lane commits (keeps the operands in
+// uniform registers: UTCHMMA / UTCBAR read URs, and a divergent `if (lane == 0)` costs a R2UR waterfall per MMA)
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred pe;\n"
+      "elect.sync _|pe, 0xFFFFFFFF;\n"
+      "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+      "}\n" ::"r"(smem_u32(bar)) : "memory");
 }
 // all MMAs issued so far by this thread -> one arrival on `bar` when they have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -127,193 +150,312 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
   return __bfloat1622float2(h);
 }
 
+// bulk global -> shared copy (TMA, non-tensor form) completing on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// barrier among the epilogue threads only (the MMA warp never joins barrier 1)
+__device__ __forceinline__ void epi_bar_sync(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
+
+// The nine taps of one 128-row tile in ONE asm block: per tap a 32-bit add on the low descriptor word
+// (start-address field, 16-byte units) for A (shifted rows) and for B (next 512-byte weight block).
+// A single thread issues every MMA, so its instruction count per MMA is what paces the tensor pipe at
+// this tiny N (measured: ~125 cycles per MMA with descriptors rebuilt in C, 8-cycle floor).
+template <int LW, bool FIRST>
+__device__ __forceinline__ void umma_taps9(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred pz, po, pe;\n"
+      ".reg .b32 al, bl;\n"
+      "elect.sync _|pe, 0xFFFFFFFF;\n"
+      ".reg .b64 ad, bd;\n"
+      "setp.ne.u32 pz, %15, 0;\n"
+      "setp.eq.u32 po, 0, 0;\n"
+      "add.s32 al, %1, %6;\n  mov.b64 ad, {al, %2};\n  mov.b64 bd, {%3, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, pz;\n"
+      "add.s32 al, %1, %7;\n  mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 32;\n  mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %8;\n  mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 64;\n  mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %9;\n  mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 96;\n  mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %10;\n mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 128;\n mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %11;\n mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 160;\n mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %12;\n mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 192;\n mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %13;\n mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 224;\n mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "add.s32 al, %1, %14;\n mov.b64 ad, {al, %2};\n  add.s32 bl, %3, 256;\n mov.b64 bd, {bl, %4};\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %5, po;\n"
+      "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc),
+      "n"(-LW - 1), "n"(-LW), "n"(-LW + 1), "n"(-1), "n"(0), "n"(1), "n"(LW - 1), "n"(LW), "n"(LW + 1), "n"(FIRST ? 0 : 1)
+      : "memory");
+}
+
 template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
-  int w, bias, x, y, in, hsum, red, sst, mbar, tmem, total;
+  int w, bias, head, x, y, in, hsum, red, mbar, tmem, total;
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
     bias = o; o += layers * 16 * 4;
+    head = o; o += TC_HEAD_FLOATS * 4;
     o = (o + 127) & ~127;
     x = o; o += Ge::BUF;
     y = o; o += Ge::BUF;
     if (Ge::KB_IN == 1) in = y; else { in = o; o += Ge::KB_IN * Ge::BUF; }
     hsum = o; o += Ge::NP * 4 * 4;
-    red = o; o += 16 * 4;
-    sst = o; o += Ge::NP * (int)sizeof(typename G::State);
+    red = o; o += 32 * 4;
     o = (o + 7) & ~7;
-    mbar = o; o += 8 * 8;
+    mbar = o; o += (2 * Ge::TILES + 1) * 8;      // full[TILES], ready[TILES], weights
     tmem = o; o += 16;
     total = o;
   }
 };
 
 template <class G>
-__global__ void __launch_bounds__(TC_THREADS)
+__global__ void __launch_bounds__(TcGeom<G>::THREADS, 2)   // 56 registers: leaves half the register file to co-resident search CTAs
 k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict__ states, int n_max,
                  const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value) {
   using Ge = TcGeom<G>;
   using State = typename G::State;
+  constexpr int TILES = Ge::TILES;
   extern __shared__ __align__(128) uint8_t tc_smem[];
   const int n = count_dev ? min(n_max, *count_dev) : n_max;
-  const int n_batches = (n + Ge::NP - 1) / Ge::NP;
+  // positions per CTA: spread the requests of this launch evenly over the grid (a tick of the engine is
+  // latency-bound, one wave of equally loaded CTAs is what matters), at most NP (= TILES tiles) per batch
+  const int ppc = min(Ge::NP, max(1, (n + (int)gridDim.x - 1) / (int)gridDim.x));
+  const int n_batches = (n + ppc - 1) / ppc;
   if ((int)blockIdx.x >= n_batches) return;                 // before any allocation
   const TcSmem<G> L(tp.w_blocks, np.layers);
   uint8_t* sW = tc_smem + L.w;
   float* sBias = reinterpret_cast<float*>(tc_smem + L.bias);
+  float* sHead = reinterpret_cast<float*>(tc_smem + L.head);
   uint8_t* bufX = tc_smem + L.x;
   uint8_t* bufY = tc_smem + L.y;
   uint8_t* bufIn = tc_smem + L.in;
   float* hsum = reinterpret_cast<float*>(tc_smem + L.hsum);
   float* red = reinterpret_cast<float*>(tc_smem + L.red);
-  State* sst = reinterpret_cast<State*>(tc_smem + L.sst);
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(tc_smem + L.mbar);
+  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + L.mbar);     // MMA -> epilogue, per tile
+  uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
+  uint64_t* wbar = ready + TILES;                                     // weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tc_smem + L.tmem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int q = warp & 3, hsel = warp >> 2;                 // TMEM lane quarter of this warp; tile parity it serves
+  const bool is_mma = warp == 4 * Ge::EPI_GROUPS;
+  const int layers = np.layers;
+#ifdef BB_TC_TIMING
+  long long tq[64];
+  int tqn = 0;
+#define TQ() do { if (tqn < 64) tq[tqn++] = clock64(); } while (0)
+#else
+#define TQ() ((void)0)
+#endif
+  TQ();
 
-  // one-time setup: weights + biases resident, activation buffers (and their zero padding) cleared
-  for (int i = tid; i < tp.w_blocks * 32; i += TC_THREADS) reinterpret_cast<uint4*>(sW)[i] = tp.w[i];
-  for (int i = tid; i < np.layers * 16; i += TC_THREADS) sBias[i] = np.tower_b[i];
-  {
-    const int zero_bytes = L.hsum - L.x;                    // X, Y (and the separate input buffer)
-    for (int i = tid; i < zero_bytes / 16; i += TC_THREADS) reinterpret_cast<uint4*>(bufX)[i] = make_uint4(0, 0, 0, 0);
-  }
-  __syncwarp();
-  if (warp == 0) tmem_alloc(tmem_slot, Ge::TMEM_COLS);
-  if (tid == 0) {
-    for (int t = 0; t < Ge::TILES; ++t) mbar_init(&mbar[t], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  // ---- one-time setup ---------------------------------------------------------------------------
+  if (is_mma) {
+    if (lane == 0) {
+      for (int t = 0; t < TILES; ++t) { mbar_init(&full[t], 1); mbar_init(&ready[t], 4); }
+      mbar_init(wbar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      bulk_g2s(sW, tp.w, (uint32_t)tp.w_blocks * 512u, wbar);
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Ge::TMEM_COLS);
+  } else {
+    for (int i = tid; i < layers * 16; i += Ge::EPI_THREADS) sBias[i] = np.tower_b[i];
+    {
+      const int nh = 51 + 3 * np.dense + 1;                 // value conv, policy conv, d1 w/b, d2 w/b
+      for (int i = tid; i < nh; i += Ge::EPI_THREADS) sHead[i] = np.head[i];
+      if (G::A <= 32) {
+        for (int i = tid; i < 2 * G::A; i += Ge::EPI_THREADS) sHead[nh + i] = np.pol_w[i];
+        for (int i = tid; i < G::A; i += Ge::EPI_THREADS) sHead[nh + 2 * G::A + i] = np.pol_b[i];
+      }
+    }
+    const int zero_bytes = L.hsum - L.x;                    // X, Y (and the separate input buffer), padding included
+    for (int i = tid; i < zero_bytes / 16; i += Ge::EPI_THREADS) reinterpret_cast<uint4*>(bufX)[i] = make_uint4(0, 0, 0, 0);
   }
   tc_fence_before();
   fence_async_smem();
   __syncthreads();
   tc_fence_after();
+  TQ();
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t IDESC = umma_idesc_bf16(128, 16);
-  const float* hd = np.head;
   unsigned long long call = 0;
   if (np.eps > 0.f) call = *np.call_counter;
-  uint32_t phase = 0;
+  uint32_t n_full = 0;          // completions of full[t] consumed so far (epilogue side), same for every tile
+  uint32_t n_ready = 0;         // completions of ready[t] consumed so far (MMA side)
 
   for (int batch = blockIdx.x; batch < n_batches; batch += gridDim.x) {
-    const int base = batch * Ge::NP;
-    __syncthreads();
-    if (tid < Ge::NP) sst[tid] = states[min(base + tid, n - 1)];
-    __syncthreads();
-    // input planes (AsInputArray) decoded straight from the packed states into the raster
-    for (int row = tid; row < Ge::R; row += TC_THREADS) {
-      const int p = row / Ge::RPP, l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
-      if (line >= 1 && col < G::W) {
-        const int cell = (line - 1) * G::W + col;
-        const State s = sst[p];
-#pragma unroll
-        for (int kb = 0; kb < Ge::KB_IN; ++kb)
-#pragma unroll
-          for (int kh = 0; kh < 2; ++kh) {
-            uint32_t w4[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int c0 = kb * 16 + kh * 8 + 2 * i;
-              const float a = c0 < G::C ? (float)G::plane(s, cell, c0) : 0.f;
-              const float b = c0 + 1 < G::C ? (float)G::plane(s, cell, c0 + 1) : 0.f;
-              w4[i] = pack_bf16(a, b);
+    const int base = batch * ppc;
+    const int cnt = min(ppc, n - base);                     // positions of this batch
+    const int tiles = (cnt * Ge::RPP + 127) >> 7;           // 128-row tiles in use
+    if (is_mma) {
+      // ---- MMA issuer: layers x tiles as a wavefront ---------------------------------------------
+      {                                                       // warp-uniform: every lane waits, one elected lane issues
+        if (n_ready == 0) mbar_wait(wbar, 0);
+        const uint32_t w_addr = smem_u32(sW);
+        for (int layer = 0; layer < layers; ++layer) {
+          const bool odd = layer & 1;
+          const uint32_t in_addr = smem_u32(layer == 0 ? bufIn : (odd ? bufX : bufY));
+          const int kblocks = layer == 0 ? Ge::KB_IN : 1;
+          const int wblk0 = layer == 0 ? 0 : Ge::KB_IN * 9 + (layer - 1) * 9;
+          const uint32_t par = n_ready & 1u;
+          for (int t = 0; t < tiles; ++t) {
+            // inputs of tile t live in tiles t-1..t+1 of the previous layer's output; t-1 and t were
+            // observed while issuing tile t-1 (they cannot advance further before this tile is issued)
+            if (t == 0) mbar_wait(&ready[0], par);
+            if (t + 1 < tiles) mbar_wait(&ready[t + 1], par);
+            tc_fence_after();
+            {
+              const uint64_t adesc = umma_desc(in_addr + (t * 128 + TC_MARGIN) * 16, Ge::PLANE, 128);
+              const uint64_t bdesc = umma_desc(w_addr + wblk0 * 512, 256, 128);
+              const uint32_t a_lo = (uint32_t)adesc, a_hi = (uint32_t)(adesc >> 32), b_lo = (uint32_t)bdesc, b_hi = (uint32_t)(bdesc >> 32);
+              umma_taps9<Ge::LW, true>(tmem_base + t * 16, a_lo, a_hi, b_lo, b_hi, IDESC);
+              for (int kb = 1; kb < kblocks; ++kb)          // further 16-channel blocks of the input planes (layer 0 only)
+                umma_taps9<Ge::LW, false>(tmem_base + t * 16, a_lo + kb * (Ge::BUF >> 4), a_hi, b_lo + kb * 9 * 32, b_hi, IDESC);
             }
-            *reinterpret_cast<uint4*>(bufIn + kb * Ge::BUF + kh * Ge::PLANE + (row + TC_MARGIN) * 16) =
-                make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            umma_commit_elect(&full[t]);
           }
-      }
-    }
-    fence_async_smem();
-    __syncthreads();
-
-    for (int layer = 0; layer < np.layers; ++layer) {
-      const bool odd = layer & 1;
-      uint8_t* in = layer == 0 ? bufIn : (odd ? bufX : bufY);
-      uint8_t* out = odd ? bufY : bufX;
-      const bool skip = !odd && layer > 0;                  // conv_2 + BN + block input (NetworkFactory.py:95-98)
-      const bool last = layer == np.layers - 1;
-      if (tid == 0) {                                       // the whole layer's MMAs, one commit per tile
-        tc_fence_after();
-        const int kblocks = layer == 0 ? Ge::KB_IN : 1;
-        const int wblk0 = layer == 0 ? 0 : Ge::KB_IN * 9 + (layer - 1) * 9;
-        const uint32_t in_addr = smem_u32(in), w_addr = smem_u32(sW);
-        for (int t = 0; t < Ge::TILES; ++t) {
-          for (int kb = 0; kb < kblocks; ++kb)
-#pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const int off = (tap / 3 - 1) * Ge::LW + (tap % 3 - 1);
-              const uint64_t adesc = umma_desc(in_addr + kb * Ge::BUF + (t * 128 + TC_MARGIN + off) * 16, Ge::PLANE, 128);
-              const uint64_t bdesc = umma_desc(w_addr + (wblk0 + kb * 9 + tap) * 512, 256, 128);
-              umma_bf16(tmem_base + t * 16, adesc, bdesc, IDESC, (kb | tap) != 0);
-            }
-          umma_commit(&mbar[t]);
+          n_ready += 1;
         }
       }
       __syncwarp();
-      const float* bias = sBias + layer * 16;
-      for (int t = hsel; t < Ge::TILES; t += 2) {
-        mbar_wait(&mbar[t], phase);
-        tc_fence_after();
-        float acc[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + t * 16, acc);
+    } else {
+      // ---- epilogue warps: group wg = warp / 4 drains tiles wg, wg + 4; TMEM lane quarter q = warp % 4 -----
+      const int wg = warp >> 2, q = warp & 3;
+      // input planes (AsInputArray) decoded straight from the packed states into the raster rows
+      for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
         const int row = t * 128 + q * 32 + lane;
-        const int l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
-        if (row < Ge::R && line >= 1 && col < G::W) {
-          uint8_t* slot = out + (row + TC_MARGIN) * 16;
+        const int pos = row / Ge::RPP, l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
+        if (row < cnt * Ge::RPP && line >= 1 && col < G::W) {
+          const int cell = (line - 1) * G::W + col;
+          const State s = states[base + pos];
 #pragma unroll
-          for (int c = 0; c < 16; ++c) acc[c] += bias[c];
-          if (skip) {
-            const uint4 s0 = *reinterpret_cast<const uint4*>(slot), s1 = *reinterpret_cast<const uint4*>(slot + Ge::PLANE);
-            const uint32_t sw[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+          for (int kb = 0; kb < Ge::KB_IN; ++kb)
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float2 f = unpack_bf16(sw[i]);
-              acc[2 * i] += f.x;
-              acc[2 * i + 1] += f.y;
+            for (int kh = 0; kh < 2; ++kh) {
+              uint32_t w4[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int c0 = kb * 16 + kh * 8 + 2 * i;
+                const float a = c0 < G::C ? (float)G::plane(s, cell, c0) : 0.f;
+                const float b = c0 + 1 < G::C ? (float)G::plane(s, cell, c0 + 1) : 0.f;
+                w4[i] = pack_bf16(a, b);
+              }
+              *reinterpret_cast<uint4*>(bufIn + kb * Ge::BUF + kh * Ge::PLANE + (row + TC_MARGIN) * 16) =
+                  make_uint4(w4[0], w4[1], w4[2], w4[3]);
             }
-          }
-#pragma unroll
-          for (int c = 0; c < 16; ++c) acc[c] = fmaxf(acc[c], 0.f);
-          if (!last) {
-            *reinterpret_cast<uint4*>(slot) = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
-                                                         pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-            *reinterpret_cast<uint4*>(slot + Ge::PLANE) = make_uint4(pack_bf16(acc[8], acc[9]), pack_bf16(acc[10], acc[11]),
-                                                                     pack_bf16(acc[12], acc[13]), pack_bf16(acc[14], acc[15]));
-          } else {
-            // heads from the fp32 registers: 1x1 convs (1 value + 2 policy filters) + BN + ReLU; the three
-            // per-cell values replace this row's (now dead) slot in X
-            float v = hd[16], p0 = hd[17 + 32], p1 = hd[17 + 33];
-#pragma unroll
-            for (int c = 0; c < 16; ++c) {
-              v = fmaf(acc[c], hd[c], v);
-              p0 = fmaf(acc[c], hd[17 + c * 2], p0);
-              p1 = fmaf(acc[c], hd[17 + c * 2 + 1], p1);
-            }
-            *reinterpret_cast<float4*>(slot) = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
-          }
         }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ready[t]);
       }
-      phase ^= 1u;
-      tc_fence_before();
-      fence_async_smem();
-      __syncthreads();
+      TQ();
+
+      for (int layer = 0; layer < layers; ++layer) {
+        const bool odd = layer & 1;
+        uint8_t* out = odd ? bufY : bufX;
+        const bool skip = !odd && layer > 0;                // conv_2 + BN + block input (NetworkFactory.py:95-98)
+        const bool last = layer == layers - 1;
+        const float* bias = sBias + layer * 16;
+        for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
+          const int row = t * 128 + q * 32 + lane;
+          const int l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
+          const bool cell_ok = row < cnt * Ge::RPP && line >= 1 && col < G::W;
+          mbar_wait(&full[t], n_full & 1u);
+          TQ();
+          tc_fence_after();
+          float acc[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + t * 16, acc);
+          if (cell_ok) {
+            uint8_t* slot = out + (row + TC_MARGIN) * 16;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) acc[c] += bias[c];
+            if (skip) {
+              const uint4 s0 = *reinterpret_cast<const uint4*>(slot), s1 = *reinterpret_cast<const uint4*>(slot + Ge::PLANE);
+              const uint32_t sw[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float2 f = unpack_bf16(sw[i]);
+                acc[2 * i] += f.x;
+                acc[2 * i + 1] += f.y;
+              }
+            }
+#pragma unroll
+            for (int c = 0; c < 16; ++c) acc[c] = fmaxf(acc[c], 0.f);
+            if (!last) {
+              *reinterpret_cast<uint4*>(slot) = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
+                                                           pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+              *reinterpret_cast<uint4*>(slot + Ge::PLANE) = make_uint4(pack_bf16(acc[8], acc[9]), pack_bf16(acc[10], acc[11]),
+                                                                       pack_bf16(acc[12], acc[13]), pack_bf16(acc[14], acc[15]));
+            } else {
+              // heads from the fp32 registers: 1x1 convs (1 value + 2 policy filters) + BN + ReLU; the three
+              // per-cell values replace this row's (now dead) slot in X
+              float v = sHead[16], p0 = sHead[17 + 32], p1 = sHead[17 + 33];
+#pragma unroll
+              for (int c = 0; c < 16; ++c) {
+                v = fmaf(acc[c], sHead[c], v);
+                p0 = fmaf(acc[c], sHead[17 + c * 2], p0);
+                p1 = fmaf(acc[c], sHead[17 + c * 2 + 1], p1);
+              }
+              *reinterpret_cast<float4*>(slot) = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
+            }
+          }
+          if (!last) {
+            tc_fence_before();
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ready[t]);
+          }
+          TQ();
+        }
+        n_full += 1;
+      }
     }
-    // sum over H,W in a fixed order, then the dense heads
-    if (tid < Ge::NP * 3) {
-      const int p = tid / 3, k = tid % 3;
+    // ---- heads: the whole CTA (MMA warp included) meets here once per batch --------------------------
+    __syncthreads();
+    // per-position sums over H,W of the three head maps: one warp per (position, map), fixed-order tree
+    for (int pk = warp; pk < cnt * 3; pk += Ge::THREADS / 32) {
+      const int p = pk / 3, k = pk % 3;
       float s = 0.f;
-      for (int y = 0; y < G::H; ++y)
-        for (int x = 0; x < G::W; ++x)
-          s += reinterpret_cast<const float*>(bufX + (p * Ge::RPP + (y + 1) * Ge::LW + x + TC_MARGIN) * 16)[k];
-      hsum[p * 4 + k] = s;
+      for (int c = lane; c < G::H * G::W; c += 32)
+        s += reinterpret_cast<const float*>(bufX + (p * Ge::RPP + (c / G::W + 1) * Ge::LW + c % G::W + TC_MARGIN) * 16)[k];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+      if (lane == 0) hsum[p * 4 + k] = s;
     }
     __syncthreads();
-    heads_finish<G>(np, hsum, red, base, n, Ge::NP, call, policy, value);
+    TQ();
+    {
+      const int nh = 51 + 3 * np.dense + 1;
+      const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
+      const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
+      heads_finish<G>(np, sHead, pw, pb, hsum, red, base, n, cnt, call, policy, value);
+    }
+    __syncthreads();                                          // X / hsum are rewritten by the next batch
+    TQ();
+#ifdef BB_TC_TIMING
+    if (blockIdx.x == 0 && tid == 0 && batch == 0) {
+      printf("TCT");
+      for (int i = 1; i < tqn; ++i) printf(" %lld", tq[i] - tq[0]);
+      printf("\n");
+    }
+#endif
   }
+  tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_base, Ge::TMEM_COLS);
+  if (is_mma) tmem_dealloc(tmem_base, Ge::TMEM_COLS);
 }
 
 }  // namespace bb

@@ -172,6 +172,9 @@ struct EngineT : bb_engine {
     {
       const char* sb = getenv("BB_STEP_BUDGET");               // tuning knob; results do not depend on it
       d.step_budget = sb ? atoi(sb) : (c.search == BB_FIXED ? c.max_depth + 6 : 24);
+      const char* cr = getenv("BB_COMPACT_ROUNDS");
+      d.compact_rounds = cr ? atoi(cr) : 8;
+      if (d.compact_rounds < 1) d.compact_rounds = 1;
     }
     d.pool_cap = (uint32_t)c.max_plies * (uint32_t)(G::A < 64 ? G::A : 64);
     int rc;

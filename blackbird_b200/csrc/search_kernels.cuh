@@ -126,13 +126,21 @@ __device__ __forceinline__ void run_compaction(const EngineDev<G>& E, Slot<G>& s
   }
 }
 
-constexpr int COMPACT_ROUNDS_PER_TICK = 8;
+
+#ifndef BB_ADV_MIN_CTAS
+#define BB_ADV_MIN_CTAS 1
+#endif
 
 template <class G>
 __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws) {
   const int lane = lane_id();
   Slot<G> s = E.slots[g];
   if (!phase_busy(s.phase)) return;
+#ifdef BB_ADV_TIMING
+  const long long dbg_t0 = clock64();
+  const int dbg_phase0 = s.phase;
+  int dbg_iters = 0, dbg_compact = 0;
+#endif
   unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0;
   uint32_t* prow = E.path + (size_t)g * PATH_LEN;
   Path path;
@@ -157,9 +165,13 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
 
   int budget = E.step_budget;
   for (;;) {
+#ifdef BB_ADV_TIMING
+    dbg_iters++;
+    if (s.phase == BB_PH_COMPACT) dbg_compact++;
+#endif
     if (s.phase == BB_PH_COMPACT) {
-      budget -= COMPACT_ROUNDS_PER_TICK;
-      run_compaction(E, s, g, ws, COMPACT_ROUNDS_PER_TICK);
+      budget -= 2 * E.compact_rounds;                        // a copy round costs about two tree levels of latency
+      run_compaction(E, s, g, ws, E.compact_rounds);
       if (s.phase != BB_PH_MOVE_READY || !E.autoplay || s.moves_budget == 0) break;
       nodes = E.half(g, s.half);
       begin_move(E, s, nodes, path, E.play_limit);
@@ -258,6 +270,15 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
     }
   }
   if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) path.store(prow);
+#ifdef BB_ADV_TIMING
+  {
+    const long long dt = clock64() - dbg_t0;
+    const unsigned tk = E.ctl->tick;
+    if (lane == 0 && (tk % 997) == 5 && (dt > 30000 || (g & 63) == 0))
+      printf("ADV tick %u g %d cyc %lld ph %d->%d iters %d compact %d sel %llu sims %llu exp %llu evals %llu moves %llu depth %d nodes %u\n", tk, g, dt,
+             dbg_phase0, s.phase, dbg_iters, dbg_compact, n_sel, n_sims, n_exp, n_evals, n_moves, s.depth, s.n_nodes);
+  }
+#endif
   if (lane == 0) {
     E.slots[g] = s;
     if (phase_busy(s.phase)) atomicAdd(&E.ctl->active[par], 1);
@@ -275,7 +296,7 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
 // One tick.  `par` = tick parity (host-tracked): requests / activity of this tick accumulate in
 // ctl->req[par] / ctl->active[par]; the last CTA to finish clears the other parity for the next tick.
 template <class G>
-__global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_advance(EngineDev<G> E, unsigned par) {
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA, BB_ADV_MIN_CTAS) k_advance(EngineDev<G> E, unsigned par) {
   __shared__ WarpScratch s_ws[WARPS_PER_CTA];
   const int gl = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // lane-local slot
   if (gl < E.n_games) advance_slot(E, E.g0 + gl, par, s_ws[threadIdx.x >> 5]);

@@ -103,6 +103,7 @@ struct EngineDev {                // passed to kernels by value
   uint32_t node_cap;
   int search, max_depth, max_plies;
   int step_budget;                // tree levels a slot may descend per tick before it yields (keeps ticks short)
+  int compact_rounds;             // subtree-copy rounds (32 scanned nodes each) a slot in BB_PH_COMPACT runs per tick
   double c;                       // ExplorationRate
   // evaluator mailbox
   TickCtl* ctl;
