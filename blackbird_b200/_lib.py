@@ -77,6 +77,7 @@ SIGNATURES = {
     'bb_records_device': (I, [VP] + [C.POINTER(VP)] * 7),
     'bb_counters_read': (I, [VP, C.POINTER(bb_counters), I]),
     'bb_engine_lanes': (I, [VP]),
+    'bb_engine_streaming': (I, [VP]),
 }
 
 

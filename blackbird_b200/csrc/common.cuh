@@ -32,8 +32,40 @@ void set_error(const char* fmt, ...);
 // Appendix B.2 evaluator over n (or min(n, *count_dev)) packed states (rules.cu)
 int launch_kat(int game, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream);
 
+// Streaming (asynchronous) mode: a persistent search kernel and a persistent network kernel run side by
+// side and talk through a request ring in global memory, so a slot that blocks on the evaluator gets its
+// answer one network batch later instead of one whole tick later (DESIGN.md "streaming engine").
+// Ticket i lives in ring entry i & mask; entry_seq[e] == i + 1 publishes the request, resp_seq[slot] == i + 1
+// publishes the answer.  Every slot has at most one open request, so a ring of >= n_games entries never wraps
+// onto a live entry.
+struct StreamCtl {
+  unsigned tail;                  // tickets handed out to the search warps
+  unsigned head;                  // tickets claimed by the network CTAs
+  unsigned stop;                  // search warps leave after their current pass
+  unsigned search_ctas;           // grid of the running search kernel
+  unsigned search_done;           // search CTAs that have left
+  unsigned servers;               // grid of the running network kernel (claims are sized as open / servers)
+  unsigned long long goal_moves;  // stop once the engine-wide move counter reaches this (0 = no goal)
+  unsigned long long batches;     // network batches served (measurement)
+  unsigned long long cyc_claim, cyc_tower, cyc_heads;   // SM cycles the network CTAs spent waiting for work / in the tower / in the heads (measurement)
+};
+
 // Built-in network (net.cu)
 struct NetDev;
+struct NetServe {                 // the request ring as the persistent network kernel sees it
+  StreamCtl* q;
+  unsigned* q_seq;
+  const int* q_slot;
+  const void* q_state;
+  unsigned* resp_seq;
+  unsigned q_mask;
+};
+// persistent network kernel for streaming mode: serves the ring until the search kernel has left and the ring is empty;
+// answers go to policy[slot][A] / value[slot]
+int net_serve(NetDev* net, const NetServe& sv, float* policy, float* value, cudaStream_t stream);
+int net_sm_count(NetDev* net);
+int net_tc_footprint(NetDev* net, int* regs, int* smem);
+bool net_is_tc(NetDev* net);
 int net_create(int game, const bb_net_desc* d, const float* w_host, size_t n_floats, NetDev** out);
 void net_destroy(NetDev* net);
 int net_forward(NetDev* net, const void* states_dev, int n, const int* count_dev, float* policy, float* value,

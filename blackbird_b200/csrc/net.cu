@@ -171,7 +171,7 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 template <class G>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
-                             float* __restrict__ value) {
+                             float* __restrict__ value, const int* out_idx = nullptr) {
   constexpr int HW = G::H * G::W;
   const int tid = threadIdx.x, nthreads = blockDim.x;
   const int D = np.dense;                               // hd / pol_w / pol_b: np.head / np.pol_w / np.pol_b or copies in shared memory
@@ -183,7 +183,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
     const float s = hsum[tid * 4];
     float o = d2b;
     for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
-    value[base + tid] = tanhf(o);
+    value[out_idx ? out_idx[tid] : base + tid] = tanhf(o);
   }
   // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
   if (G::A <= 32) {
@@ -208,13 +208,14 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
         z[a] = pa;
         tot += pa;
       }
+      const size_t orow = out_idx ? (size_t)out_idx[tid] : (size_t)(base + tid);
 #pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[(size_t)(base + tid) * G::A + a] = z[a] / tot;
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[orow * G::A + a] = z[a] / tot;
     }
   } else {
     for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
       const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
-      float* out = policy + (size_t)(base + p) * G::A;
+      float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
       float m = -INFINITY;
       for (int a = tid; a < G::A; a += nthreads) {
         float z = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
@@ -401,11 +402,42 @@ static int net_launch_tc(NetDev* net, const void* states, int n, const int* coun
   // the kernel spreads the (device-side) request count evenly over the grid, so launch one full wave
   const int cap = net->sm_count * ctas_per_sm[G::ID];
   const int grid = n < cap ? n : cap;
-  k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value);
+  k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value, NetServe{});
   BB_CUDA(cudaGetLastError());
   if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
   return BB_OK;
 }
+
+template <class G>
+static int net_serve_tc(NetDev* net, const NetServe& sv, float* policy, float* value, cudaStream_t stream) {
+  using Ge = TcGeom<G>;
+  const TcSmem<G> L(net->tc.w_blocks, net->p.layers);
+  BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+  // one CTA per SM (a kernel that allocates TMEM never gets more), all resident for the whole launch
+  k_net_forward_tc<G><<<net->sm_count, Ge::THREADS, L.total, stream>>>(net->p, net->tc, nullptr, 0, nullptr, policy, value, sv);
+  BB_CUDA(cudaGetLastError());
+  return BB_OK;
+}
+
+int net_serve(NetDev* net, const NetServe& sv, float* policy, float* value, cudaStream_t stream) {
+  if (!net->use_tc) { set_error("streaming mode needs the tensor-core network kernel (precision bf16)"); return BB_EINVAL; }
+  BB_DISPATCH_GAME(net->game, return net_serve_tc<G>(net, sv, policy, value, stream));
+  return BB_EINVAL;
+}
+template <class G>
+static void tc_footprint(NetDev* net, int* regs, int* smem) {
+  cudaFuncAttributes fa{};
+  cudaFuncGetAttributes(&fa, k_net_forward_tc<G>);
+  *regs = ((fa.numRegs * 32 + 511) / 512 * 512) * (TcGeom<G>::THREADS / 32);    // per-warp allocations are rounded up (512 assumed)
+  *smem = TcSmem<G>(net->tc.w_blocks, net->p.layers).total + 1024;
+}
+// registers and shared memory one CTA of the tensor-core kernel holds on its SM
+int net_tc_footprint(NetDev* net, int* regs, int* smem) {
+  BB_DISPATCH_GAME(net->game, tc_footprint<G>(net, regs, smem); return BB_OK);
+  return BB_EINVAL;
+}
+int net_sm_count(NetDev* net) { return net->sm_count; }
+bool net_is_tc(NetDev* net) { return net->use_tc; }
 
 int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
   if (n <= 0) return BB_OK;

@@ -203,7 +203,7 @@ __device__ __forceinline__ void umma_taps9(uint32_t tmem_d, uint32_t a_lo, uint3
 template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
-  int w, bias, head, x, y, in, hsum, red, mbar, tmem, total;
+  int w, bias, head, x, y, in, hsum, red, idx, claim, mbar, tmem, total;
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
@@ -215,6 +215,8 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     if (Ge::KB_IN == 1) in = y; else { in = o; o += Ge::KB_IN * Ge::BUF; }
     hsum = o; o += Ge::NP * 4 * 4;
     red = o; o += 32 * 4;
+    idx = o; o += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
+    claim = o; o += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     o = (o + 7) & ~7;
     mbar = o; o += (2 * Ge::TILES + 1) * 8;      // full[TILES], ready[TILES], weights
     tmem = o; o += 16;
@@ -223,19 +225,20 @@ struct TcSmem {                                  // byte offsets into dynamic sh
 };
 
 template <class G>
-__global__ void __launch_bounds__(TcGeom<G>::THREADS, 2)   // 56 registers: leaves half the register file to co-resident search CTAs
+__global__ void __launch_bounds__(TcGeom<G>::THREADS + 96, 2)   // 48 registers: the CTA must share its SM's register file with a search CTA
 k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict__ states, int n_max,
-                 const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value) {
+                 const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value, NetServe sv) {
   using Ge = TcGeom<G>;
   using State = typename G::State;
   constexpr int TILES = Ge::TILES;
   extern __shared__ __align__(128) uint8_t tc_smem[];
-  const int n = count_dev ? min(n_max, *count_dev) : n_max;
+  const bool serve = sv.q != nullptr;                       // streaming mode: batches are claimed from the request ring
+  const int n = serve ? 0x7FFFFFFF : (count_dev ? min(n_max, *count_dev) : n_max);
   // positions per CTA: spread the requests of this launch evenly over the grid (a tick of the engine is
   // latency-bound, one wave of equally loaded CTAs is what matters), at most NP (= TILES tiles) per batch
   const int ppc = min(Ge::NP, max(1, (n + (int)gridDim.x - 1) / (int)gridDim.x));
   const int n_batches = (n + ppc - 1) / ppc;
-  if ((int)blockIdx.x >= n_batches) return;                 // before any allocation
+  if (!serve && (int)blockIdx.x >= n_batches) return;       // before any allocation
   const TcSmem<G> L(tp.w_blocks, np.layers);
   uint8_t* sW = tc_smem + L.w;
   float* sBias = reinterpret_cast<float*>(tc_smem + L.bias);
@@ -245,6 +248,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   uint8_t* bufIn = tc_smem + L.in;
   float* hsum = reinterpret_cast<float*>(tc_smem + L.hsum);
   float* red = reinterpret_cast<float*>(tc_smem + L.red);
+  int* sIdx = reinterpret_cast<int*>(tc_smem + L.idx);
+  volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(tc_smem + L.claim);
   uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + L.mbar);     // MMA -> epilogue, per tile
   uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
   uint64_t* wbar = ready + TILES;                                     // weights landed
@@ -293,29 +298,90 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   constexpr uint32_t IDESC = umma_idesc_bf16(128, 16);
   unsigned long long call = 0;
   if (np.eps > 0.f) call = *np.call_counter;
-  uint32_t n_full = 0;          // completions of full[t] consumed so far (epilogue side), same for every tile
-  uint32_t n_ready = 0;         // completions of ready[t] consumed so far (MMA side)
+  // mbarrier phase parities, one bit per tile: batches use different numbers of tiles, so every tile's barriers
+  // advance at their own pace (full: epilogue side, ready: MMA side)
+  uint32_t full_par = 0, ready_par = 0;
+  bool weights_in = false;
 
-  for (int batch = blockIdx.x; batch < n_batches; batch += gridDim.x) {
-    const int base = batch * ppc;
-    const int cnt = min(ppc, n - base);                     // positions of this batch
+  int batch = blockIdx.x;
+  for (;;) {
+    int base, cnt;
+    unsigned ticket0 = 0;
+    long long tm0 = 0, tm1 = 0, tm2 = 0;
+    if (serve && tid == 0) tm0 = clock64();
+    if (serve) {
+      if (tid == 0) {
+        // Claim tickets with ONE atomicAdd (a compare-and-swap loop serialises the 148 CTAs: ~55 us of waiting per
+        // batch was measured).  The size is open / servers (at least 1, at most NP) from a possibly stale view, so a
+        // claim can run past the tail; those tickets are waited for, or dropped when the search has already left.
+        unsigned c = 0, hh = 0, idle = 0;
+        volatile unsigned* vt = reinterpret_cast<volatile unsigned*>(&sv.q->tail);
+        volatile unsigned* vh = reinterpret_cast<volatile unsigned*>(&sv.q->head);
+        volatile unsigned* vdone = reinterpret_cast<volatile unsigned*>(&sv.q->search_done);
+        const unsigned srv = sv.q->servers, ctas = sv.q->search_ctas;
+        for (;;) {
+          const int open = (int)(*vt - *vh);
+          if (open > 0) {
+            c = min((unsigned)Ge::NP, max(1u, ((unsigned)open + srv - 1u) / srv));
+            hh = atomicAdd(&sv.q->head, c);
+            for (;;) {                                          // the claim may be ahead of the tail
+              if ((int)(*vt - (hh + c)) >= 0) break;
+              if (*vdone >= ctas) {
+                __threadfence();
+                const int have = (int)(*vt - hh);
+                c = have > 0 ? min(c, (unsigned)have) : 0u;
+                break;
+              }
+              __nanosleep(100);
+            }
+            if (c) break;
+            continue;
+          }
+          if (*vdone >= ctas) {
+            __threadfence();
+            if ((int)(*vt - *vh) <= 0) { c = 0; break; }        // nobody left to ask
+            continue;
+          }
+          __nanosleep(200);
+          if (++idle > (16u << 20)) {                           // seconds without a request or a finished search: give up, never hang
+            if (blockIdx.x == 0) printf("[bbengine] streaming watchdog: network kernel idle (head %u tail %u, search CTAs done %u of %u)\n", *vh, *vt,
+                                        *vdone, ctas);
+            *reinterpret_cast<volatile unsigned*>(&sv.q->stop) = 2u;
+            c = 0;
+            break;
+          }
+        }
+        sClaim[0] = hh;
+        sClaim[1] = c;
+      }
+      __syncthreads();
+      ticket0 = sClaim[0];
+      cnt = (int)sClaim[1];
+      base = 0;
+      if (cnt == 0) break;
+      if (tid == 0) tm1 = clock64();
+    } else {
+      if (batch >= n_batches) break;
+      base = batch * ppc;
+      cnt = min(ppc, n - base);                             // positions of this batch
+      batch += gridDim.x;
+    }
     const int tiles = (cnt * Ge::RPP + 127) >> 7;           // 128-row tiles in use
     if (is_mma) {
       // ---- MMA issuer: layers x tiles as a wavefront ---------------------------------------------
       {                                                       // warp-uniform: every lane waits, one elected lane issues
-        if (n_ready == 0) mbar_wait(wbar, 0);
+        if (!weights_in) { mbar_wait(wbar, 0); weights_in = true; }
         const uint32_t w_addr = smem_u32(sW);
         for (int layer = 0; layer < layers; ++layer) {
           const bool odd = layer & 1;
           const uint32_t in_addr = smem_u32(layer == 0 ? bufIn : (odd ? bufX : bufY));
           const int kblocks = layer == 0 ? Ge::KB_IN : 1;
           const int wblk0 = layer == 0 ? 0 : Ge::KB_IN * 9 + (layer - 1) * 9;
-          const uint32_t par = n_ready & 1u;
           for (int t = 0; t < tiles; ++t) {
             // inputs of tile t live in tiles t-1..t+1 of the previous layer's output; t-1 and t were
             // observed while issuing tile t-1 (they cannot advance further before this tile is issued)
-            if (t == 0) mbar_wait(&ready[0], par);
-            if (t + 1 < tiles) mbar_wait(&ready[t + 1], par);
+            if (t == 0) { mbar_wait(&ready[0], ready_par & 1u); ready_par ^= 1u; }
+            if (t + 1 < tiles) { mbar_wait(&ready[t + 1], (ready_par >> (t + 1)) & 1u); ready_par ^= 1u << (t + 1); }
             tc_fence_after();
             {
               const uint64_t adesc = umma_desc(in_addr + (t * 128 + TC_MARGIN) * 16, Ge::PLANE, 128);
@@ -327,7 +393,6 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             }
             umma_commit_elect(&full[t]);
           }
-          n_ready += 1;
         }
       }
       __syncwarp();
@@ -340,7 +405,19 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         const int pos = row / Ge::RPP, l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
         if (row < cnt * Ge::RPP && line >= 1 && col < G::W) {
           const int cell = (line - 1) * G::W + col;
-          const State s = states[base + pos];
+          State s;
+          if (serve) {                                      // wait for the ticket's entry to be published, read it through L2
+            const unsigned tk = ticket0 + (unsigned)pos, e = tk & sv.q_mask;
+            for (unsigned spin = 0; *reinterpret_cast<volatile unsigned*>(&sv.q_seq[e]) != tk + 1u && spin < (64u << 20); ++spin) {}
+            __threadfence();
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(reinterpret_cast<const State*>(sv.q_state) + e);
+            uint32_t* dst = reinterpret_cast<uint32_t*>(&s);
+#pragma unroll
+            for (int i = 0; i < (int)(sizeof(State) / 4); ++i) dst[i] = __ldcg(src + i);
+            if (l == Ge::LW) sIdx[pos] = __ldcg(sv.q_slot + e);   // the position's first cell records where the answer goes
+          } else {
+            s = states[base + pos];
+          }
 #pragma unroll
           for (int kb = 0; kb < Ge::KB_IN; ++kb)
 #pragma unroll
@@ -373,7 +450,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           const int row = t * 128 + q * 32 + lane;
           const int l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
           const bool cell_ok = row < cnt * Ge::RPP && line >= 1 && col < G::W;
-          mbar_wait(&full[t], n_full & 1u);
+          mbar_wait(&full[t], (full_par >> t) & 1u);
+          full_par ^= 1u << t;
           TQ();
           tc_fence_after();
           float acc[16];
@@ -420,11 +498,11 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           }
           TQ();
         }
-        n_full += 1;
       }
     }
     // ---- heads: the whole CTA (MMA warp included) meets here once per batch --------------------------
     __syncthreads();
+    if (serve && tid == 0) tm2 = clock64();
     // per-position sums over H,W of the three head maps: one warp per (position, map), fixed-order tree
     for (int pk = warp; pk < cnt * 3; pk += Ge::THREADS / 32) {
       const int p = pk / 3, k = pk % 3;
@@ -441,12 +519,24 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
-      heads_finish<G>(np, sHead, pw, pb, hsum, red, base, n, cnt, call, policy, value);
+      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, serve ? sIdx : nullptr);
+    }
+    if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
+      __threadfence();
+      __syncthreads();
+      if (tid < cnt) *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
+      if (tid == 0) {
+        const long long tm3 = clock64();
+        atomicAdd(&sv.q->batches, 1ull);
+        atomicAdd(&sv.q->cyc_claim, (unsigned long long)(tm1 - tm0));
+        atomicAdd(&sv.q->cyc_tower, (unsigned long long)(tm2 - tm1));
+        atomicAdd(&sv.q->cyc_heads, (unsigned long long)(tm3 - tm2));
+      }
     }
     __syncthreads();                                          // X / hsum are rewritten by the next batch
     TQ();
 #ifdef BB_TC_TIMING
-    if (blockIdx.x == 0 && tid == 0 && batch == 0) {
+    if (blockIdx.x == 0 && tid == 0 && batch == (int)gridDim.x) {
       printf("TCT");
       for (int i = 1; i < tqn; ++i) printf(" %lld", tq[i] - tq[0]);
       printf("\n");

@@ -62,6 +62,16 @@ __global__ void k_gather_slots(EngineDev<G> E, typename G::State* states, int32_
   if (status) status[g] = E.slots[g].status;
 }
 
+// streaming mode: (re)arm the control block for one launch pair; tickets (head / tail) carry over
+__global__ void k_stream_arm(StreamCtl* q, unsigned search_ctas, unsigned servers, unsigned long long goal) {
+  q->stop = 0;
+  q->head = q->tail;              // tickets claimed past the tail by the previous launch were never issued
+  q->search_done = 0;
+  q->search_ctas = search_ctas;
+  q->servers = servers;
+  q->goal_moves = goal;
+}
+
 }  // namespace bb
 
 using namespace bb;
@@ -94,6 +104,7 @@ struct bb_engine {
   virtual int records_device(void**, void**, void**, void**, void**, void**, void**) = 0;
   virtual int counters(bb_counters*, int) = 0;
   virtual int n_lanes() = 0;
+  virtual int streaming() = 0;
 };
 
 template <class G>
@@ -120,6 +131,12 @@ struct EngineT : bb_engine {
   std::vector<Lane> lanes;
   TickCtl* ctl_dev = nullptr;
   Counters* counters_dev = nullptr;
+  // streaming mode (built-in tensor-core network only): request ring + persistent kernel pair
+  StreamCtl* q_dev = nullptr;
+  cudaStream_t net_stream = nullptr;
+  cudaEvent_t st_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  double st_search_ms = 0, st_net_ms = 0;
+  unsigned long long st_runs = 0, st_batches0 = 0;
   int last_active = 0, last_req = 0;
   void* scratch = nullptr;         // device scratch for exports
   size_t scratch_bytes = 0;
@@ -196,6 +213,22 @@ struct EngineT : bb_engine {
     A_(d.winners, n);
     A_(counters_dev, lanes.size());
     A_(uniforms_dev, n * c.max_plies);
+    {
+      size_t qn = 1;
+      while (qn < n) qn <<= 1;
+      d.q_mask = (unsigned)(qn - 1);
+      A_(q_dev, 1);
+      A_(d.q_seq, qn);
+      A_(d.q_slot, qn);
+      A_(d.q_state, qn);
+      A_(d.resp_seq, n);
+      BB_CUDA(cudaMemset(q_dev, 0, sizeof(StreamCtl)));
+      BB_CUDA(cudaMemset(d.q_seq, 0, qn * sizeof(unsigned)));
+      BB_CUDA(cudaMemset(d.resp_seq, 0, n * sizeof(unsigned)));
+      d.q = nullptr;                                               // set only in the copy handed to the streaming kernels
+      BB_CUDA(cudaStreamCreateWithFlags(&net_stream, cudaStreamNonBlocking));
+      for (int i = 0; i < 4; ++i) BB_CUDA(cudaEventCreate(&st_ev[i]));
+    }
 #undef A_
     d.ctl = ctl_dev;
     d.counters = counters_dev;
@@ -219,6 +252,11 @@ struct EngineT : bb_engine {
       L.d.resp_value = d.resp_value + L.d.g0;
     }
     d.uniforms = uniforms_dev;
+    // Kernels that should share an SM must agree on its shared-memory / L1 split: an SM is reconfigured only when
+    // it is idle, so a search CTA with the default (small) carve-out could never join an SM that runs a network
+    // CTA (which needs ~100 KB and therefore the large carve-out).  Same preference for all three.
+    BB_CUDA(cudaFuncSetAttribute(k_search_stream<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    BB_CUDA(cudaFuncSetAttribute(k_advance<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     return reset(nullptr);
   }
   ~EngineT() override {
@@ -233,6 +271,8 @@ struct EngineT : bb_engine {
     }
     if (net) net_destroy(net);
     for (Lane& L : lanes) if (L.stream) cudaStreamDestroy(L.stream);
+    if (net_stream) cudaStreamDestroy(net_stream);
+    for (int i = 0; i < 4; ++i) if (st_ev[i]) cudaEventDestroy(st_ev[i]);
   }
 
   void set_mode(int autoplay, int refill, int play_limit, int temp_mode) {
@@ -243,6 +283,7 @@ struct EngineT : bb_engine {
 
   int net_load(const bb_net_desc* nd, const float* w, size_t nfl) override {
     BB_CUDA(cudaSetDevice(cfg.device));
+    stream_fits = -1;
     if (net) { net_destroy(net); net = nullptr; }
     return net_create(G::ID, nd, w, nfl, &net);
   }
@@ -257,6 +298,9 @@ struct EngineT : bb_engine {
     k_reset<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d, (const State*)states_dev);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaMemsetAsync(ctl_dev, 0, lanes.size() * sizeof(TickCtl), stream));
+    BB_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(StreamCtl), stream));
+    BB_CUDA(cudaMemsetAsync(d.q_seq, 0, ((size_t)d.q_mask + 1) * sizeof(unsigned), stream));
+    BB_CUDA(cudaMemsetAsync(d.resp_seq, 0, (size_t)d.n_games * sizeof(unsigned), stream));
     for (Lane& L : lanes) L.par = 0;
     BB_CUDA(cudaStreamSynchronize(stream));
     return BB_OK;
@@ -299,6 +343,14 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int profile(int enable, int max_ticks) override {
+    if (use_stream()) {                                         // nothing to arm: the launch pair is always timed
+      StreamCtl h{};
+      BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
+      st_batches0 = h.batches;
+      st_search_ms = st_net_ms = 0;
+      st_runs = 0;
+      return BB_OK;
+    }
     prof = enable != 0;
     for (Lane& L : lanes) {
       L.prof_used = 0;
@@ -311,6 +363,14 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int profile_read(double* adv_ms, double* eval_ms, int* ticks) override {
+    if (use_stream()) {                                         // streaming mode: the two persistent kernels, launches as "ticks" -> batches served
+      StreamCtl h{};
+      BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
+      if (adv_ms) *adv_ms = st_search_ms;
+      if (eval_ms) *eval_ms = st_net_ms;
+      if (ticks) *ticks = (int)(h.batches - st_batches0);
+      return BB_OK;
+    }
     double a = 0, b = 0;
     size_t n = 0;
     for (Lane& L : lanes) {
@@ -378,6 +438,72 @@ struct EngineT : bb_engine {
     for (Lane& L : lanes) BB_CUDA(cudaStreamSynchronize(L.stream));
     return BB_OK;
   }
+  // Streaming mode is used whenever the evaluator is the built-in tensor-core network (BB_STREAM=0 falls back
+  // to ticks).  Results are identical in both modes (tests/test_gpu_network.py).
+  int stream_fits = -1;             // the two persistent kernels must share an SM, or the search would spin on a network that never starts
+  bool use_stream() {
+    if (cfg.evaluator != BB_EVAL_NET || !net || !net_is_tc(net)) return false;
+    const char* e = getenv("BB_STREAM");
+    if (e && atoi(e) == 0) return false;
+    if (stream_fits < 0) {
+      int nregs = 0, nsmem = 0;
+      cudaFuncAttributes fa{};
+      stream_fits = 0;
+      if (net_tc_footprint(net, &nregs, &nsmem) == BB_OK && cudaFuncGetAttributes(&fa, k_search_stream<G>) == cudaSuccess) {
+        const int sregs = ((fa.numRegs * 32 + 511) / 512 * 512) * STREAM_WARPS_PER_CTA;
+        stream_fits = (nregs + sregs <= 65536 && nsmem + (int)fa.sharedSizeBytes + 1024 <= 227 * 1024) ? 1 : 0;
+        if (getenv("BB_DEBUG_OCC"))
+          fprintf(stderr, "[bbengine] streaming: network CTA %d regs %d B smem, search CTA %d regs %zu B smem -> %s\n", nregs, nsmem, sregs,
+                  fa.sharedSizeBytes, stream_fits ? "co-resident" : "do NOT fit one SM, tick mode");
+      }
+    }
+    return stream_fits == 1;
+  }
+  // One launch pair: the persistent network kernel (one CTA per SM) and the persistent search kernel
+  // (one 8-warp CTA per SM; both fit an SM's register file together) run until every slot has left the
+  // busy phases, or until the engine-wide move counter reaches goal_moves.
+  int run_stream(unsigned long long goal_moves) {
+    int rc = sync_lanes();
+    if (rc) return rc;
+    EngineDev<G> e = d;
+    e.q = q_dev;
+    const int sms = net_sm_count(net);
+    const int per_cta = STREAM_WARPS_PER_CTA * STREAM_MAX_OWN;
+    int grid = (d.n_games + STREAM_WARPS_PER_CTA - 1) / STREAM_WARPS_PER_CTA;
+    if (grid > sms) grid = sms;
+    if ((long long)grid * per_cta < d.n_games) grid = (d.n_games + per_cta - 1) / per_cta;
+    if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
+    int div = sms;                                              // a claim takes open / div tickets (1 .. NP)
+    if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : sms;
+    k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    NetServe sv{q_dev, d.q_seq, d.q_slot, d.q_state, d.resp_seq, d.q_mask};
+    // the network kernel goes first so that its CTAs are resident before the search CTAs spin on it
+    BB_CUDA(cudaEventRecord(st_ev[2], net_stream));
+    if ((rc = net_serve(net, sv, d.resp_policy, d.resp_value, net_stream))) return rc;
+    BB_CUDA(cudaEventRecord(st_ev[3], net_stream));
+    BB_CUDA(cudaEventRecord(st_ev[0], stream));
+    k_search_stream<G><<<grid, 32 * STREAM_WARPS_PER_CTA, 0, stream>>>(e);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaEventRecord(st_ev[1], stream));
+    host_launches += 3;
+    BB_CUDA(cudaStreamSynchronize(stream));
+    BB_CUDA(cudaStreamSynchronize(net_stream));
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, st_ev[0], st_ev[1]);
+    cudaEventElapsedTime(&b, st_ev[2], st_ev[3]);
+    st_search_ms += a;
+    st_net_ms += b;
+    st_runs += 1;
+    StreamCtl h{};
+    BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
+    if (getenv("BB_DEBUG_STREAM") && h.batches)
+      fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles\n", h.batches,
+              (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches);
+    if (h.stop == 2u) { set_error("streaming watchdog fired: a search warp or the network kernel waited for seconds (see stderr)"); return BB_ESTATE; }
+    return BB_OK;
+  }
   int run(int* pending) override {
     BB_CUDA(cudaSetDevice(cfg.device));
     int rc;
@@ -391,7 +517,8 @@ struct EngineT : bb_engine {
       if (pending) *pending = last_req;
       return BB_OK;
     }
-    rc = tick_until([&](int active, unsigned long long) { return active == 0; });
+    if (use_stream()) rc = run_stream(0);
+    else rc = tick_until([&](int active, unsigned long long) { return active == 0; });
     if (pending) *pending = 0;
     return rc;
   }
@@ -540,7 +667,8 @@ struct EngineT : bb_engine {
     if (!rc) rc = wait_snapshots(0, &start);
     if (!rc) {
       const unsigned long long goal = start + (unsigned long long)target_moves;
-      rc = tick_until([&](int active, unsigned long long moves) { return moves >= goal || active == 0; });
+      if (use_stream()) rc = run_stream(goal);
+      else rc = tick_until([&](int active, unsigned long long moves) { return moves >= goal || active == 0; });
     }
     set_mode(0, 0, play_limit, 0);
     return rc;
@@ -581,6 +709,7 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
   int n_lanes() override { return (int)lanes.size(); }
+  int streaming() override { return use_stream() ? 1 : 0; }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -656,5 +785,6 @@ int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off
 }
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
+int bb_engine_streaming(bb_engine* e) { BB_NEED(e); return e->streaming(); }
 
 }  // extern "C"

@@ -172,7 +172,7 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     double p = 0.0;
     if (lane < k) {
       a = nth_bit(m, lane);
-      p = (double)policy[a];                                // f32 policy * 1.0 (f64 mask)
+      p = (double)__ldcg(policy + a);                       // f32 policy * 1.0 (f64 mask); L2 load: written by another SM in streaming mode
       ws.prior[lane] = p;
       ws.action[lane] = (uint16_t)a;
     }
@@ -223,7 +223,7 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
         Node n;
         n.s.plays = 0u;
         n.s.value = 0.f;
-        n.s.prior = (double)policy[a];
+        n.s.prior = (double)__ldcg(policy + a);
         n.h.parent = node;
         n.h.child_base = NONE;
         n.h.meta = meta_pack(a, 0, child_player, false);

@@ -14,6 +14,18 @@ __device__ __forceinline__ bool phase_busy(int ph) {
 template <class G>
 __device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, int g, unsigned parity) {
   int idx = 0;
+  if (E.q) {                                                  // streaming mode: take a ticket, fill the ring entry, publish it
+    if (lane_id() == 0) {
+      idx = (int)atomicAdd(&E.q->tail, 1u);
+      const unsigned e = (unsigned)idx & E.q_mask;
+      E.q_slot[e] = g;
+      E.q_state[e] = s.cur_state;
+      __threadfence();
+      *reinterpret_cast<volatile unsigned*>(&E.q_seq[e]) = (unsigned)idx + 1u;
+    }
+    s.req_idx = (uint32_t)__shfl_sync(0xFFFFFFFFu, idx, 0);
+    return;
+  }
   if (lane_id() == 0) {
     idx = atomicAdd(&E.ctl->req[parity], 1);
     E.req_slot[idx] = g;
@@ -127,15 +139,16 @@ __device__ __forceinline__ void run_compaction(const EngineDev<G>& E, Slot<G>& s
 }
 
 
+constexpr int STREAM_WARPS_PER_CTA = 8;
 #ifndef BB_ADV_MIN_CTAS
 #define BB_ADV_MIN_CTAS 1
 #endif
 
 template <class G>
-__device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws) {
+__device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws, uint32_t* ticket = nullptr) {
   const int lane = lane_id();
   Slot<G> s = E.slots[g];
-  if (!phase_busy(s.phase)) return;
+  if (!phase_busy(s.phase)) return s.phase;
 #ifdef BB_ADV_TIMING
   const long long dbg_t0 = clock64();
   const int dbg_phase0 = s.phase;
@@ -150,9 +163,9 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
   int step = ST_TOP;
   if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) {   // an evaluation came back for s.cur
     path.load(prow);
-    BB_ASSERT(s.cur < s.n_nodes && s.req_idx < (uint32_t)E.n_games);
+    BB_ASSERT(s.cur < s.n_nodes && (E.q || s.req_idx < (uint32_t)E.n_games));
     ch = nodes[s.cur].h;
-    ch.eval = E.resp_value[s.req_idx];
+    ch.eval = E.q ? __ldcg(&E.resp_value[g]) : E.resp_value[s.req_idx];   // streaming mode answers by slot
     ch.meta |= META_HAS_VALUE;
     if (lane == 0) nodes[s.cur].h = ch;
     step = s.phase == BB_PH_WAIT_EXPAND ? ST_EXPAND : ST_LEAF;
@@ -190,7 +203,7 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
       }
       step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
-      const int k = expand_node(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)s.req_idx * G::A, ws);
+      const int k = expand_node(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws);
       if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
       n_exp += 1;
       n_nodes += k;
@@ -279,9 +292,10 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
              dbg_phase0, s.phase, dbg_iters, dbg_compact, n_sel, n_sims, n_exp, n_evals, n_moves, s.depth, s.n_nodes);
   }
 #endif
+  if (ticket) *ticket = s.req_idx;
   if (lane == 0) {
     E.slots[g] = s;
-    if (phase_busy(s.phase)) atomicAdd(&E.ctl->active[par], 1);
+    if (!E.q && phase_busy(s.phase)) atomicAdd(&E.ctl->active[par], 1);
     Counters* c = E.counters;
     if (n_sims) atomicAdd(&c->sims, n_sims);
     if (n_evals) atomicAdd(&c->evals, n_evals);
@@ -290,6 +304,87 @@ __device__ void advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScr
     if (n_sel) atomicAdd(&c->select_steps, n_sel);
     if (n_moves) atomicAdd(&c->moves, n_moves);
     if (n_done) atomicAdd(&c->games_done, n_done);
+  }
+  __syncwarp();
+  return s.phase;
+}
+
+// ---- streaming mode: persistent search kernel ------------------------------------------------------
+// Every warp owns the slots g = w, w + W, w + 2W ... (W = warps of the grid) for the whole launch and
+// round-robins over them: a slot whose answer has not arrived is skipped, every other busy slot is
+// advanced until it blocks again (or its step budget ends).  Nothing here is a barrier between slots, so a
+// slot costs one network batch of latency per evaluation instead of one engine-wide tick.  Results do not
+// depend on the interleaving: each slot's tree is private and the evaluator is a pure function.
+constexpr int STREAM_MAX_OWN = 32;      // slots per warp
+constexpr unsigned STREAM_WATCHDOG_SPINS = 4u << 20;   // idle polls (~0.5 us each) before a warp gives up
+
+template <class G>
+__global__ void __launch_bounds__(32 * STREAM_WARPS_PER_CTA, 2) k_search_stream(EngineDev<G> E) {   // <= 128 registers: one CTA fits an SM NEXT TO the network CTA
+  __shared__ WarpScratch s_ws[STREAM_WARPS_PER_CTA];
+  __shared__ uint32_t s_ticket[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];
+  __shared__ uint8_t s_state[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];   // 0 runnable, 1 waiting for an answer, 2 finished
+  const int wl = threadIdx.x >> 5, lane = lane_id();
+  const int W = gridDim.x * STREAM_WARPS_PER_CTA;
+  const int w = blockIdx.x * STREAM_WARPS_PER_CTA + wl;
+  int n_own = 0;
+  for (int g = w; g < E.n_games && n_own < STREAM_MAX_OWN; g += W) {
+    if (lane == 0) {
+      const int ph = E.slots[g].phase;
+      // a slot left waiting by an earlier launch keeps its ticket (the answer is in flight or already there)
+      s_state[wl][n_own] = (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) ? 1 : (phase_busy(ph) ? 0 : 2);
+      s_ticket[wl][n_own] = E.slots[g].req_idx;
+    }
+    ++n_own;
+  }
+  __syncwarp();
+  volatile unsigned* stop = &E.q->stop;
+  const volatile unsigned long long* moves = reinterpret_cast<const volatile unsigned long long*>(&E.counters->moves);
+  const unsigned long long goal = E.q->goal_moves;
+  unsigned idle = 0;
+  for (;;) {
+    bool progressed = false, any_busy = false;
+    for (int j = 0; j < n_own; ++j) {
+      const int st = s_state[wl][j];
+      if (st == 2) continue;
+      const int g = w + j * W;
+      if (st == 1) {
+        const unsigned have = *reinterpret_cast<volatile unsigned*>(&E.resp_seq[g]);
+        if (have != s_ticket[wl][j] + 1u) { any_busy = true; continue; }
+        __threadfence();                                     // acquire: the answer was written before its sequence number
+      }
+      uint32_t ticket = 0;
+      const int ph = advance_slot(E, g, 0u, s_ws[wl], &ticket);
+      progressed = true;
+      int nst = 2;
+      if (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) nst = 1;
+      else if (phase_busy(ph)) nst = 0;
+      if (lane == 0) { s_state[wl][j] = (uint8_t)nst; s_ticket[wl][j] = ticket; }
+      __syncwarp();
+      any_busy |= nst != 2;
+    }
+    if (!any_busy) break;
+    if (goal && lane == 0 && *moves >= goal) *stop = 1u;
+    __syncwarp();
+    if (*stop) break;
+    if (progressed) idle = 0;
+    else {
+      __nanosleep(400);
+      if (++idle > STREAM_WATCHDOG_SPINS) {                  // no answer for seconds: never hang the device, report instead
+        if (lane == 0) {
+          int j0 = 0;
+          while (j0 < n_own && s_state[wl][j0] != 1) ++j0;
+          printf("[bbengine] streaming watchdog: warp %d waited too long (slot %d ticket %u, answer seq %u, head %u tail %u)\n", w,
+                 w + j0 * W, j0 < n_own ? s_ticket[wl][j0] : 0u, j0 < n_own ? E.resp_seq[w + j0 * W] : 0u, E.q->head, E.q->tail);
+          *stop = 2u;
+        }
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(&E.q->search_done, 1u);
   }
 }
 

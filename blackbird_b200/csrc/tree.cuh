@@ -109,8 +109,15 @@ struct EngineDev {                // passed to kernels by value
   TickCtl* ctl;
   int* req_slot;
   typename G::State* req_state;
-  float* resp_policy;             // [n_games][A], indexed by request
+  float* resp_policy;             // [n_games][A], indexed by request (tick mode) or by slot (streaming mode)
   float* resp_value;
+  // streaming mode (q != nullptr): request ring + per-slot answer sequence numbers
+  StreamCtl* q;
+  unsigned* q_seq;                // [q_mask + 1]
+  int* q_slot;                    // [q_mask + 1]
+  typename G::State* q_state;     // [q_mask + 1]
+  unsigned* resp_seq;             // [n_games]
+  unsigned q_mask;
   // self-play
   int autoplay;                   // 1: choose / move root / end games on the device
   int refill;                     // 1: a finished game's slot starts the next game (steady-state stepping)

@@ -154,6 +154,11 @@ class Engine(object):
         self.evaluator = evaluator
         self.lanes = lib.bb_engine_lanes(self._h)
 
+    @property
+    def streaming(self):
+        """True when searches run as the persistent search + network kernel pair (needs a loaded bf16 network)."""
+        return bool(lib.bb_engine_streaming(self._h))
+
     def close(self):
         if getattr(self, '_h', None):
             lib.bb_engine_destroy(self._h)

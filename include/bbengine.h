@@ -177,6 +177,10 @@ typedef struct bb_counters {
 } bb_counters;
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset);
 int bb_engine_lanes(bb_engine* e);   /* lanes the engine runs with */
+/* 1 when searches run in streaming mode: a persistent search kernel and a persistent network kernel side by side,
+ * talking through a request ring (built-in tensor-core network only; BB_STREAM=0 forces tick mode).  Results do not
+ * depend on the mode.  bb_profile_read then returns the two kernels' durations and the batches served. */
+int bb_engine_streaming(bb_engine* e);
 
 #ifdef __cplusplus
 }

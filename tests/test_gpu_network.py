@@ -100,13 +100,18 @@ class Replay(object):
         return self._eval(planes)[1]
 
 
-@pytest.mark.parametrize('kind,P', [('dynamic', 64), ('fixed', 24)])
-def test_selfplay_with_network_replay(mods, kind, P):
+@pytest.mark.parametrize('kind,P,precision', [('dynamic', 64, 'fp32'), ('fixed', 24, 'fp32'),
+                                              ('dynamic', 64, 'bf16'), ('fixed', 24, 'bf16')])
+def test_selfplay_with_network_replay(mods, kind, P, precision):
+    """Self-play driven by the built-in network vs the oracle search fed with the SAME kernel's outputs
+    (replayed per position): visit counts, moves and record bytes must agree exactly.  fp32 runs in tick
+    mode, bf16 in streaming mode (persistent search + network kernels, request ring)."""
     engine, records = mods
     game, G = 'Connect4', 6
     w = network_np.init_weights(3, 7, seed=2, jitter=0.1)
     eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P)
-    eng.load_network(network_np.flatten_weights(w), 4, 16, 16)
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, precision=precision)
+    assert eng.streaming == (precision == 'bf16')
     u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
     eng.selfplay(P, 1.0, u)
     got = records.build_records(eng)
@@ -117,6 +122,28 @@ def test_selfplay_with_network_replay(mods, kind, P):
         want, winner, _ = selfplay_np.play_game(s, GAMES[game], 1)
         assert got[g][0] == want, (kind, g)
     eng.close()
+
+
+@pytest.mark.parametrize('game,kind,P,G', [('Connect4', 'fixed', 48, 300), ('TicTacToe', 'dynamic', 40, 200), ('DragonChess', 'dynamic', 10, 24)])
+def test_streaming_equals_tick_mode(mods, game, kind, P, G, monkeypatch):
+    """The persistent kernel pair and the tick loop produce byte-identical records and counters."""
+    engine, records = mods
+    from blackbird_b200 import netinit
+    cin = engine.plane_shape(game)[2]
+    w = netinit.random_weights(cin, engine.n_actions(game), seed=5)
+    out = {}
+    for mode in ('1', '0'):
+        monkeypatch.setenv('BB_STREAM', mode)
+        eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P, max_plies=40 if game == 'DragonChess' else None)
+        eng.load_network(w, 4, 16, 16, precision='bf16')
+        assert eng.streaming == (mode == '1')
+        u = np.stack([np.random.RandomState(7000 + g).random_sample(eng.max_plies) for g in range(G)])
+        eng.selfplay(P, 1.0, u)
+        c = eng.counters()
+        out[mode] = (records.build_records(eng), c['sims'], c['evals'], c['nodes'], c['moves'])
+        eng.close()
+    assert out['1'][1:] == out['0'][1:]
+    assert out['1'][0] == out['0'][0]
 
 
 def test_noise_statistics(mods):
