@@ -239,10 +239,13 @@ def run_ours(args):
     value = sims / (ms * 1e-3)
 
     # kernel shares: one profiled step (CUDA events around every advance / network launch)
+    streaming = eng.streaming
+    st0 = eng.stream_stats()
     eng.profile(True, 16384)
     eng.stream_moves(G, P)
     prof = eng.profile_read()
     eng.profile(False)
+    st1 = eng.stream_stats()
     cp = eng.counters(reset=True)
     flops = netinit.flops_per_eval(h, w, cin, 7, **NET)
     peaks = {}
@@ -262,19 +265,41 @@ def run_ours(args):
     # mailbox: state out/in + policy/value out/in; backup: 8-byte read-modify-write per path node
     b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * 16 + 2 * 4 * 8) + 16 * (d_bar + 1)
     tree_gbs = cp['sims'] * b_sim / (prof['advance_ms'] * 1e-3) / 1e9 if prof['advance_ms'] > 0 else 0.0
-    roofline = {'bound': 'tensor', 'kernel': ('k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' if args.precision == 'bf16' else 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)') % (cp['evals'] / max(1, prof['ticks'])),
+    launches_prof = max(1, cp['kernel_launches'] // 3) if streaming else max(1, prof['ticks'])
+    if streaming:
+        kname = 'k_net_forward_tc<Connect4> serve mode (bf16 tcgen05 tower, persistent: %d evals/launch, batches of %.2f)' % (
+            cp['evals'] / launches_prof, cp['evals'] / max(1, prof['ticks']))
+    elif args.precision == 'bf16':
+        kname = 'k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks']))
+    else:
+        kname = 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks']))
+    roofline = {'bound': 'tensor', 'kernel': kname,
                 'achieved': net_tflops, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / tensor_peak,
                 'traffic': None, 'peak_source': peak_src, 'flops_per_eval': flops,
-                'launch_ms_avg': prof['eval_ms'] / max(1, prof['ticks']),
+                'launch_ms_avg': prof['eval_ms'] / launches_prof,
                 'step_share': prof['eval_ms'] / max(1e-9, prof['eval_ms'] + prof['advance_ms'])}
-    roofline_tree = {'bound': 'hbm', 'kernel': 'k_advance<Connect4> (select/expand/backup)', 'achieved': tree_gbs, 'peak': hbm_peak,
+    roofline_tree = {'bound': 'hbm', 'kernel': ('k_search_stream<Connect4> (persistent select/expand/backup)' if streaming
+                                                else 'k_advance<Connect4> (select/expand/backup)'), 'achieved': tree_gbs, 'peak': hbm_peak,
                      'unit': 'GB/s', 'frac': tree_gbs / hbm_peak, 'bytes_per_sim_model': b_sim, 'mean_depth': d_bar,
                      'expansions_per_sim': nexp, 'children_per_expansion': k_bar, 'evals_per_sim': cp['evals'] / max(1, cp['sims']),
-                     'launch_ms_avg': prof['advance_ms'] / max(1, prof['ticks'])}
+                     'launch_ms_avg': prof['advance_ms'] / launches_prof}
 
     # the kernel with the larger share of the step is the one `roofline` reports; the other rides along
     roofline_tree['step_share'] = 1.0 - roofline['step_share']
-    dominant, other = (roofline, roofline_tree) if roofline['step_share'] >= 0.5 else (roofline_tree, roofline)
+    if streaming:
+        # the two persistent kernels share every SM for the whole step: each one's launch spans the step, so its
+        # share is 1 by construction; what tells them apart is how busy the network pipelines were (cycle
+        # counters kept by the kernel itself: wait for tickets / convolution tower / heads + publish)
+        dw, dt, dh = [st1[k] - st0[k] for k in ('cyc_wait', 'cyc_tower', 'cyc_heads')]
+        nb = max(1, st1['batches'] - st0['batches'])
+        roofline['step_share'] = roofline_tree['step_share'] = 1.0
+        roofline['concurrent'] = roofline_tree['concurrent'] = 'both persistent kernels are resident on every SM for the whole step'
+        roofline['pipeline_busy_frac'] = (dt + dh) / max(1, dw + dt + dh)
+        roofline['cycles_per_batch'] = {'wait': dw / nb, 'tower': dt / nb, 'heads_publish': dh / nb}
+        roofline['batches'] = nb
+        dominant, other = roofline, roofline_tree           # the search warps wait on the network (busy_frac ~ 0.9)
+    else:
+        dominant, other = (roofline, roofline_tree) if roofline['step_share'] >= 0.5 else (roofline_tree, roofline)
 
     # e2e: whole games through the C-ABI call with host buffers (H2D uniforms, D2H records inside)
     e2e = None
@@ -283,7 +308,11 @@ def run_ours(args):
         pinned = torch.from_numpy(uniforms).pin_memory()
         t0 = time.perf_counter()
         eng.selfplay(P, 1.0, pinned.numpy())
-        raw = eng.records_raw()
+        if world > 1:                                        # every rank ends up with every game's records
+            from blackbird_b200.parallel import allgather_raw, _records_device_views
+            raw = allgather_raw(_records_device_views(eng))
+        else:
+            raw = eng.records_raw()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         ce = eng.counters(reset=True)
@@ -295,7 +324,8 @@ def run_ours(args):
         d2h = sum(v.nbytes for v in raw.values())
         e2e = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'h2d_bytes_per_step': int(uniforms.nbytes),
                'd2h_bytes_per_step': int(d2h), 'games_per_sec': float(ss[1].item()) / float(tt.item()),
-               'seconds': float(tt.item()), 'what': 'bb_selfplay_run + bb_records_export: %d whole games/GPU to completion' % G,
+               'seconds': float(tt.item()), 'what': 'bb_selfplay_run + %s: %d whole games/GPU to completion' % (
+                   'one NCCL all-gather of the record buffers + D2H' if world > 1 else 'bb_records_export', G),
                'mean_moves_per_game': float(raw['n_moves'].mean())}
 
     cpu = None
@@ -311,7 +341,7 @@ def run_ours(args):
             'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
             'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
             'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
-            'roofline': dominant, 'roofline_other': other, 'lanes': eng.lanes, 'cpu_baseline': cpu, 'e2e': e2e,
+            'roofline': dominant, 'roofline_other': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e,
             'gpu_launches': int(launches), 'clocks': clocks}))
     if world > 1:
         dist.barrier()

@@ -78,6 +78,7 @@ SIGNATURES = {
     'bb_counters_read': (I, [VP, C.POINTER(bb_counters), I]),
     'bb_engine_lanes': (I, [VP]),
     'bb_engine_streaming': (I, [VP]),
+    'bb_stream_stats': (I, [VP, C.POINTER(C.c_uint64)]),
 }
 
 

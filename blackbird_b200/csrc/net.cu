@@ -120,19 +120,30 @@ __device__ __forceinline__ void conv3x3(const float* __restrict__ in, float* __r
   }
 }
 
-__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
+// A team = the threads that work on one batch together: the whole CTA in the fp32 kernel, one of the two
+// pipelines of a CTA in the tensor-core kernel (named barrier `bar`, threads numbered tid = 0 .. n-1).
+struct Team {
+  int tid, n, bar;
+  __device__ __forceinline__ void sync() const {           // literal barrier ids: a register id makes ptxas reserve all 16 barriers
+    if (bar == 1) asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory");
+    else if (bar == 2) asm volatile("bar.sync 2, %0;" ::"r"(n) : "memory");
+    else asm volatile("bar.sync 0, %0;" ::"r"(n) : "memory");
+  }
+};
+
+__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max, const Team& tm) {
   // fixed-order tree: deterministic
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int lane = tm.tid & 31, wid = tm.tid >> 5;
 #pragma unroll
   for (int o = 16; o; o >>= 1) {
     float t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
     v = is_max ? fmaxf(v, t) : v + t;
   }
-  __syncthreads();
+  tm.sync();
   if (lane == 0) red[wid] = v;
-  __syncthreads();
+  tm.sync();
   float r = red[0];
-  for (int i = 1; i < (int)(blockDim.x >> 5); ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  for (int i = 1; i < (tm.n >> 5); ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
   return r;
 }
 
@@ -171,9 +182,9 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 template <class G>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
-                             float* __restrict__ value, const int* out_idx = nullptr) {
+                             float* __restrict__ value, const Team& tm, const int* out_idx = nullptr) {
   constexpr int HW = G::H * G::W;
-  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int tid = tm.tid, nthreads = tm.n;
   const int D = np.dense;                               // hd / pol_w / pol_b: np.head / np.pol_w / np.pol_b or copies in shared memory
   const float* d1w = hd + 17 + 34;
   const float* d1b = d1w + D;
@@ -222,10 +233,10 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
         out[a] = z;
         m = fmaxf(m, z);
       }
-      m = block_reduce(m, red, true);
+      m = block_reduce(m, red, true, tm);
       float sum = 0.f;
       for (int a = tid; a < G::A; a += nthreads) { float e = expf(out[a] - m); out[a] = e; sum += e; }
-      sum = block_reduce(sum, red, false);
+      sum = block_reduce(sum, red, false, tm);
       float tot = 0.f;
       for (int a = tid; a < G::A; a += nthreads) {
         float pa = out[a] / sum;
@@ -234,7 +245,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
         out[a] = pa;
         tot += pa;
       }
-      tot = block_reduce(tot, red, false);
+      tot = block_reduce(tot, red, false, tm);
       for (int a = tid; a < G::A; a += nthreads) out[a] = out[a] / tot;
     }
   }
@@ -344,7 +355,7 @@ k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_
       hsum[p * 4 + k] = s;
     }
     __syncthreads();
-    heads_finish<G>(np, np.head, np.pol_w, np.pol_b, hsum, red, base, n, Ge::P, call, policy, value);
+    heads_finish<G>(np, np.head, np.pol_w, np.pol_b, hsum, red, base, n, Ge::P, call, policy, value, Team{(int)threadIdx.x, (int)blockDim.x, 0});
   }
 }
 
@@ -401,7 +412,8 @@ static int net_launch_tc(NetDev* net, const void* states, int n, const int* coun
   }
   // the kernel spreads the (device-side) request count evenly over the grid, so launch one full wave
   const int cap = net->sm_count * ctas_per_sm[G::ID];
-  const int grid = n < cap ? n : cap;
+  const int want = (n + Ge::PIPES - 1) / Ge::PIPES;             // every CTA runs PIPES batches side by side
+  const int grid = want < cap ? want : cap;
   k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value, NetServe{});
   BB_CUDA(cudaGetLastError());
   if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
@@ -413,6 +425,7 @@ static int net_serve_tc(NetDev* net, const NetServe& sv, float* policy, float* v
   using Ge = TcGeom<G>;
   const TcSmem<G> L(net->tc.w_blocks, net->p.layers);
   BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+  BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
   // one CTA per SM (a kernel that allocates TMEM never gets more), all resident for the whole launch
   k_net_forward_tc<G><<<net->sm_count, Ge::THREADS, L.total, stream>>>(net->p, net->tc, nullptr, 0, nullptr, policy, value, sv);
   BB_CUDA(cudaGetLastError());

@@ -35,13 +35,16 @@ constexpr int TC_HEAD_FLOATS = 384;      // head parameters staged in shared mem
 constexpr int TC_MARGIN = 16;            // zero rows in front of / behind the raster (|tap offset| <= W+2)
 
 template <class G> struct TcBatch;
-// Largest batch of one CTA: seven 128-row tiles.  A kernel that allocates TMEM runs ONE CTA per SM
-// (cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for any kernel with tcgen05.alloc, and the
-// measured two-wave step agrees), so a launch is one wave of 148 CTAs and the CTA must be able to take
-// its share of a lane's requests (2048 slots / 148 SMs = 14 Connect4 positions) in a single batch.
+// A kernel that allocates TMEM runs ONE CTA per SM (cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for
+// any kernel with tcgen05.alloc, two different TMEM kernels do not share an SM either, and the measured two-wave
+// step agrees).  A single batch is a chain of dependent steps per layer (MMA -> commit -> epilogue -> arrive)
+// that leaves the tensor pipe idle most of the time, so the CTA runs TWO independent pipelines: each has its
+// own MMA-issuing warp, eight epilogue warps, activation buffers, TMEM columns, mbarriers and named barrier,
+// and works on its own batch; they share the resident weights and interleave on the tensor pipe.
+// Largest batch of one pipeline (positions): up to seven 128-row tiles.
 template <> struct TcBatch<TicTacToe> { static constexpr int NP = 56; };     // 56 * 16 rows = 896
 template <> struct TcBatch<Connect4> { static constexpr int NP = 14; };      // 14 * 56 rows = 784
-template <> struct TcBatch<DragonChess> { static constexpr int NP = 11; };   // 11 * 81 rows = 891
+template <> struct TcBatch<DragonChess> { static constexpr int NP = 6; };    //  6 * 81 rows = 486 (17 input planes need a separate input buffer)
 
 template <class G>
 struct TcGeom {
@@ -54,13 +57,16 @@ struct TcGeom {
   static constexpr int PLANE = ROWS * 16;                   // bytes per k-half plane
   static constexpr int BUF = 2 * PLANE;                     // one 16-channel activation buffer
   static constexpr int KB_IN = (G::C + 15) / 16;            // 16-channel blocks of the input planes
-  static constexpr int TMEM_COLS = TILES * 16 <= 32 ? 32 : (TILES * 16 <= 64 ? 64 : (TILES * 16 <= 128 ? 128 : 256));
+  static constexpr int TMEM_COLS = 256;                     // 128 per pipeline
   static_assert(LW + 1 <= TC_MARGIN, "tap offsets must stay inside the margin");
   static_assert(TILES * 16 <= 256, "too many tiles for TMEM");
-  static_assert(TILES <= 8, "two tiles per epilogue warp group");
-  static constexpr int EPI_GROUPS = 4;                      // groups of four warps (one per TMEM lane quarter); group g drains tiles g, g+4
-  static constexpr int EPI_THREADS = EPI_GROUPS * 128;
-  static constexpr int THREADS = EPI_THREADS + 32;
+  static_assert(TILES <= 8, "one mbarrier pair and 16 TMEM columns per tile, 128 columns per pipeline");
+  static constexpr int PIPES = 2;                           // independent pipelines per CTA
+  static constexpr int EPI_GROUPS = 2;                      // per pipeline: groups of four warps (one per TMEM lane quarter); group g drains tiles g, g+2, ...
+  static constexpr int EPI_THREADS = EPI_GROUPS * 128;      // epilogue threads of one pipeline
+  static constexpr int PIPE_THREADS = EPI_THREADS + 32;     // + its MMA-issuing warp
+  static constexpr int THREADS = PIPES * PIPE_THREADS;
+  static constexpr int TMEM_PIPE_COLS = 128;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -203,29 +209,35 @@ __device__ __forceinline__ void umma_taps9(uint32_t tmem_d, uint32_t a_lo, uint3
 template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
-  int w, bias, head, x, y, in, hsum, red, idx, claim, mbar, tmem, total;
+  int w, bias, head, wbar, tmem, pipe0, pipe_stride, total;          // shared by both pipelines, then one block per pipeline
+  int x, y, in, hsum, red, idx, claim, mbar;                         // offsets inside a pipeline's block
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
     bias = o; o += layers * 16 * 4;
     head = o; o += TC_HEAD_FLOATS * 4;
-    o = (o + 127) & ~127;
-    x = o; o += Ge::BUF;
-    y = o; o += Ge::BUF;
-    if (Ge::KB_IN == 1) in = y; else { in = o; o += Ge::KB_IN * Ge::BUF; }
-    hsum = o; o += Ge::NP * 4 * 4;
-    red = o; o += 32 * 4;
-    idx = o; o += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
-    claim = o; o += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     o = (o + 7) & ~7;
-    mbar = o; o += (2 * Ge::TILES + 1) * 8;      // full[TILES], ready[TILES], weights
-    tmem = o; o += 16;
-    total = o;
+    wbar = o; o += 8;
+    tmem = o; o += 8;
+    o = (o + 127) & ~127;
+    pipe0 = o;
+    int q = 0;
+    x = q; q += Ge::BUF;
+    y = q; q += Ge::BUF;
+    if (Ge::KB_IN == 1) in = y; else { in = q; q += Ge::KB_IN * Ge::BUF; }
+    hsum = q; q += Ge::NP * 4 * 4;
+    red = q; q += 32 * 4;
+    idx = q; q += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
+    claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
+    q = (q + 7) & ~7;
+    mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
+    pipe_stride = (q + 127) & ~127;
+    total = pipe0 + Ge::PIPES * pipe_stride;
   }
 };
 
 template <class G>
-__global__ void __launch_bounds__(TcGeom<G>::THREADS + 96, 2)   // 48 registers: the CTA must share its SM's register file with a search CTA
+__global__ void __launch_bounds__(TcGeom<G>::THREADS + 64, 2)   // 48 registers: the CTA shares its SM's register file with a search CTA
 k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict__ states, int n_max,
                  const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value, NetServe sv) {
   using Ge = TcGeom<G>;
@@ -234,51 +246,49 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   extern __shared__ __align__(128) uint8_t tc_smem[];
   const bool serve = sv.q != nullptr;                       // streaming mode: batches are claimed from the request ring
   const int n = serve ? 0x7FFFFFFF : (count_dev ? min(n_max, *count_dev) : n_max);
-  // positions per CTA: spread the requests of this launch evenly over the grid (a tick of the engine is
-  // latency-bound, one wave of equally loaded CTAs is what matters), at most NP (= TILES tiles) per batch
-  const int ppc = min(Ge::NP, max(1, (n + (int)gridDim.x - 1) / (int)gridDim.x));
+  // launch mode: spread the requests evenly over all pipelines of the grid (a tick of the engine is latency-bound,
+  // one wave of equally loaded pipelines is what matters), at most NP positions per batch
+  const int n_pipes = (int)gridDim.x * Ge::PIPES;
+  const int ppc = min(Ge::NP, max(1, (n + n_pipes - 1) / n_pipes));
   const int n_batches = (n + ppc - 1) / ppc;
-  if (!serve && (int)blockIdx.x >= n_batches) return;       // before any allocation
+  if (!serve && (int)blockIdx.x * Ge::PIPES >= n_batches) return;     // before any allocation
   const TcSmem<G> L(tp.w_blocks, np.layers);
+  const int tid_cta = threadIdx.x, lane = tid_cta & 31, warp = tid_cta >> 5;
+  const int pipe = tid_cta / Ge::PIPE_THREADS;              // which pipeline this thread belongs to
+  const int tid = tid_cta - pipe * Ge::PIPE_THREADS;        // thread index inside the pipeline
+  const int pwarp = tid >> 5;                               // warp index inside the pipeline: 0..7 epilogue, 8 MMA issuer
+  const bool is_mma = pwarp == 4 * Ge::EPI_GROUPS;
+  const Team team{tid, Ge::PIPE_THREADS, 1 + pipe};         // named barrier 1 / 2: the pipelines never wait for each other
   uint8_t* sW = tc_smem + L.w;
   float* sBias = reinterpret_cast<float*>(tc_smem + L.bias);
   float* sHead = reinterpret_cast<float*>(tc_smem + L.head);
-  uint8_t* bufX = tc_smem + L.x;
-  uint8_t* bufY = tc_smem + L.y;
-  uint8_t* bufIn = tc_smem + L.in;
-  float* hsum = reinterpret_cast<float*>(tc_smem + L.hsum);
-  float* red = reinterpret_cast<float*>(tc_smem + L.red);
-  int* sIdx = reinterpret_cast<int*>(tc_smem + L.idx);
-  volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(tc_smem + L.claim);
-  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + L.mbar);     // MMA -> epilogue, per tile
-  uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
-  uint64_t* wbar = ready + TILES;                                     // weights landed
+  uint64_t* wbar = reinterpret_cast<uint64_t*>(tc_smem + L.wbar);     // weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tc_smem + L.tmem);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const bool is_mma = warp == 4 * Ge::EPI_GROUPS;
+  uint8_t* pb = tc_smem + L.pipe0 + pipe * L.pipe_stride;             // this pipeline's block
+  uint8_t* bufX = pb + L.x;
+  uint8_t* bufY = pb + L.y;
+  uint8_t* bufIn = pb + L.in;
+  float* hsum = reinterpret_cast<float*>(pb + L.hsum);
+  float* red = reinterpret_cast<float*>(pb + L.red);
+  int* sIdx = reinterpret_cast<int*>(pb + L.idx);
+  volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(pb + L.claim);
+  uint64_t* full = reinterpret_cast<uint64_t*>(pb + L.mbar);          // MMA -> epilogue, per tile
+  uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
   const int layers = np.layers;
-#ifdef BB_TC_TIMING
-  long long tq[64];
-  int tqn = 0;
-#define TQ() do { if (tqn < 64) tq[tqn++] = clock64(); } while (0)
-#else
-#define TQ() ((void)0)
-#endif
-  TQ();
 
-  // ---- one-time setup ---------------------------------------------------------------------------
+  // ---- one-time setup (whole CTA) --------------------------------------------------------------------
   if (is_mma) {
     if (lane == 0) {
       for (int t = 0; t < TILES; ++t) { mbar_init(&full[t], 1); mbar_init(&ready[t], 4); }
-      mbar_init(wbar, 1);
+      if (pipe == 0) mbar_init(wbar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      bulk_g2s(sW, tp.w, (uint32_t)tp.w_blocks * 512u, wbar);
+      if (pipe == 0) bulk_g2s(sW, tp.w, (uint32_t)tp.w_blocks * 512u, wbar);
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, Ge::TMEM_COLS);
+    if (pipe == 0) tmem_alloc(tmem_slot, Ge::TMEM_COLS);
   } else {
-    for (int i = tid; i < layers * 16; i += Ge::EPI_THREADS) sBias[i] = np.tower_b[i];
-    {
+    if (pipe == 0) {
+      for (int i = tid; i < layers * 16; i += Ge::EPI_THREADS) sBias[i] = np.tower_b[i];
       const int nh = 51 + 3 * np.dense + 1;                 // value conv, policy conv, d1 w/b, d2 w/b
       for (int i = tid; i < nh; i += Ge::EPI_THREADS) sHead[i] = np.head[i];
       if (G::A <= 32) {
@@ -293,8 +303,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   fence_async_smem();
   __syncthreads();
   tc_fence_after();
-  TQ();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = *tmem_slot + (uint32_t)(pipe * Ge::TMEM_PIPE_COLS);
   constexpr uint32_t IDESC = umma_idesc_bf16(128, 16);
   unsigned long long call = 0;
   if (np.eps > 0.f) call = *np.call_counter;
@@ -303,7 +312,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   uint32_t full_par = 0, ready_par = 0;
   bool weights_in = false;
 
-  int batch = blockIdx.x;
+  int batch = (int)blockIdx.x * Ge::PIPES + pipe;
   for (;;) {
     int base, cnt;
     unsigned ticket0 = 0;
@@ -311,8 +320,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
     if (serve && tid == 0) tm0 = clock64();
     if (serve) {
       if (tid == 0) {
-        // Claim tickets with ONE atomicAdd (a compare-and-swap loop serialises the 148 CTAs: ~55 us of waiting per
-        // batch was measured).  The size is open / servers (at least 1, at most NP) from a possibly stale view, so a
+        // Claim tickets with ONE atomicAdd (a compare-and-swap loop serialises the claimers: ~55 us of waiting per
+        // batch was measured).  The size is open / divisor (at least 1, at most NP) from a possibly stale view, so a
         // claim can run past the tail; those tickets are waited for, or dropped when the search has already left.
         unsigned c = 0, hh = 0, idle = 0;
         volatile unsigned* vt = reinterpret_cast<volatile unsigned*>(&sv.q->tail);
@@ -354,7 +363,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         sClaim[0] = hh;
         sClaim[1] = c;
       }
-      __syncthreads();
+      team.sync();
       ticket0 = sClaim[0];
       cnt = (int)sClaim[1];
       base = 0;
@@ -364,7 +373,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       if (batch >= n_batches) break;
       base = batch * ppc;
       cnt = min(ppc, n - base);                             // positions of this batch
-      batch += gridDim.x;
+      batch += n_pipes;
     }
     const int tiles = (cnt * Ge::RPP + 127) >> 7;           // 128-row tiles in use
     if (is_mma) {
@@ -397,8 +406,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       }
       __syncwarp();
     } else {
-      // ---- epilogue warps: group wg = warp / 4 drains tiles wg, wg + 4; TMEM lane quarter q = warp % 4 -----
-      const int wg = warp >> 2, q = warp & 3;
+      // ---- epilogue warps: group wg drains tiles wg, wg + 2, ...; TMEM lane quarter q = warp % 4 -----------
+      const int wg = pwarp >> 2, q = warp & 3;               // q follows the CTA-wide warp id: a warp reaches TMEM lanes 32 * (warp % 4) ...
       // input planes (AsInputArray) decoded straight from the packed states into the raster rows
       for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
         const int row = t * 128 + q * 32 + lane;
@@ -438,7 +447,6 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         __syncwarp();
         if (lane == 0) mbar_arrive(&ready[t]);
       }
-      TQ();
 
       for (int layer = 0; layer < layers; ++layer) {
         const bool odd = layer & 1;
@@ -452,7 +460,6 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           const bool cell_ok = row < cnt * Ge::RPP && line >= 1 && col < G::W;
           mbar_wait(&full[t], (full_par >> t) & 1u);
           full_par ^= 1u << t;
-          TQ();
           tc_fence_after();
           float acc[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + t * 16, acc);
@@ -496,15 +503,14 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready[t]);
           }
-          TQ();
         }
       }
     }
-    // ---- heads: the whole CTA (MMA warp included) meets here once per batch --------------------------
-    __syncthreads();
+    // ---- heads: the whole pipeline (MMA warp included) meets here once per batch -----------------------
+    team.sync();
     if (serve && tid == 0) tm2 = clock64();
     // per-position sums over H,W of the three head maps: one warp per (position, map), fixed-order tree
-    for (int pk = warp; pk < cnt * 3; pk += Ge::THREADS / 32) {
+    for (int pk = pwarp; pk < cnt * 3; pk += Ge::PIPE_THREADS / 32) {
       const int p = pk / 3, k = pk % 3;
       float s = 0.f;
       for (int c = lane; c < G::H * G::W; c += 32)
@@ -513,17 +519,16 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
       if (lane == 0) hsum[p * 4 + k] = s;
     }
-    __syncthreads();
-    TQ();
+    team.sync();
     {
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
-      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, serve ? sIdx : nullptr);
+      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr);
     }
     if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
       __threadfence();
-      __syncthreads();
+      team.sync();
       if (tid < cnt) *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
       if (tid == 0) {
         const long long tm3 = clock64();
@@ -533,19 +538,11 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         atomicAdd(&sv.q->cyc_heads, (unsigned long long)(tm3 - tm2));
       }
     }
-    __syncthreads();                                          // X / hsum are rewritten by the next batch
-    TQ();
-#ifdef BB_TC_TIMING
-    if (blockIdx.x == 0 && tid == 0 && batch == (int)gridDim.x) {
-      printf("TCT");
-      for (int i = 1; i < tqn; ++i) printf(" %lld", tq[i] - tq[0]);
-      printf("\n");
-    }
-#endif
+    team.sync();                                          // X / hsum are rewritten by the next batch
   }
   tc_fence_before();
   __syncthreads();
-  if (is_mma) tmem_dealloc(tmem_base, Ge::TMEM_COLS);
+  if (is_mma && pipe == 0) tmem_dealloc(*tmem_slot, Ge::TMEM_COLS);
 }
 
 }  // namespace bb

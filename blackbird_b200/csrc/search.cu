@@ -105,6 +105,7 @@ struct bb_engine {
   virtual int counters(bb_counters*, int) = 0;
   virtual int n_lanes() = 0;
   virtual int streaming() = 0;
+  virtual int stream_stats(uint64_t*) = 0;
 };
 
 template <class G>
@@ -473,8 +474,8 @@ struct EngineT : bb_engine {
     if (grid > sms) grid = sms;
     if ((long long)grid * per_cta < d.n_games) grid = (d.n_games + per_cta - 1) / per_cta;
     if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
-    int div = sms;                                              // a claim takes open / div tickets (1 .. NP)
-    if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : sms;
+    int div = 2 * sms;                                          // a claim takes open / div tickets (1 .. NP); two pipelines per CTA
+    if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : div;
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));
@@ -710,6 +711,15 @@ struct EngineT : bb_engine {
   }
   int n_lanes() override { return (int)lanes.size(); }
   int streaming() override { return use_stream() ? 1 : 0; }
+  int stream_stats(uint64_t* out) override {
+    for (int i = 0; i < 5; ++i) out[i] = 0;
+    if (!use_stream() || !q_dev) return BB_OK;
+    StreamCtl h{};
+    BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
+    out[0] = h.batches; out[1] = h.cyc_claim; out[2] = h.cyc_tower; out[3] = h.cyc_heads;
+    out[4] = 2ull * (unsigned long long)net_sm_count(net);
+    return BB_OK;
+  }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -786,5 +796,6 @@ int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
 int bb_engine_streaming(bb_engine* e) { BB_NEED(e); return e->streaming(); }
+int bb_stream_stats(bb_engine* e, uint64_t out[5]) { BB_NEED(e); if (!out) return BB_EINVAL; return e->stream_stats(out); }
 
 }  // extern "C"

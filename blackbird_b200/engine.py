@@ -159,6 +159,12 @@ class Engine(object):
         """True when searches run as the persistent search + network kernel pair (needs a loaded bf16 network)."""
         return bool(lib.bb_engine_streaming(self._h))
 
+    def stream_stats(self):
+        """Cumulative busy accounting of the streaming network kernel (batches, wait / tower / heads cycles, pipelines)."""
+        out = (C.c_uint64 * 5)()
+        check(lib.bb_stream_stats(self._h, out))
+        return dict(zip(('batches', 'cyc_wait', 'cyc_tower', 'cyc_heads', 'pipelines'), [int(x) for x in out]))
+
     def close(self):
         if getattr(self, '_h', None):
             lib.bb_engine_destroy(self._h)

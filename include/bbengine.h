@@ -181,6 +181,10 @@ int bb_engine_lanes(bb_engine* e);   /* lanes the engine runs with */
  * talking through a request ring (built-in tensor-core network only; BB_STREAM=0 forces tick mode).  Results do not
  * depend on the mode.  bb_profile_read then returns the two kernels' durations and the batches served. */
 int bb_engine_streaming(bb_engine* e);
+/* Streaming-mode busy accounting since engine creation: out[0] batches served by the network kernel, out[1..3]
+ * SM cycles its pipelines spent waiting for tickets, in the convolution tower, and in heads + publish (summed over
+ * pipelines); out[4] pipelines x SMs serving.  Zeros in tick mode.  bench.py turns them into busy fractions. */
+int bb_stream_stats(bb_engine* e, uint64_t out[5]);
 
 #ifdef __cplusplus
 }

@@ -134,7 +134,8 @@ def test_streaming_equals_tick_mode(mods, game, kind, P, G, monkeypatch):
     out = {}
     for mode in ('1', '0'):
         monkeypatch.setenv('BB_STREAM', mode)
-        eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P, max_plies=40 if game == 'DragonChess' else None)
+        eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P, max_plies=40 if game == 'DragonChess' else None,
+                            node_cap=16384 if game == 'DragonChess' else None)
         eng.load_network(w, 4, 16, 16, precision='bf16')
         assert eng.streaming == (mode == '1')
         u = np.stack([np.random.RandomState(7000 + g).random_sample(eng.max_plies) for g in range(G)])
