@@ -297,6 +297,8 @@ def run_ours(args):
         roofline['pipeline_busy_frac'] = (dt + dh) / max(1, dw + dt + dh)
         roofline['cycles_per_batch'] = {'wait': dw / nb, 'tower': dt / nb, 'heads_publish': dh / nb}
         roofline['batches'] = nb
+        roofline_tree['warp_busy_frac'] = (st1['cyc_search_busy'] - st0['cyc_search_busy']) / max(1, st1['cyc_search_total'] - st0['cyc_search_total'])
+        roofline_tree['cycles_per_advance_call'] = (st1['cyc_search_busy'] - st0['cyc_search_busy']) / max(1, st1['search_calls'] - st0['search_calls'])
         dominant, other = roofline, roofline_tree           # the search warps wait on the network (busy_frac ~ 0.9)
     else:
         dominant, other = (roofline, roofline_tree) if roofline['step_share'] >= 0.5 else (roofline_tree, roofline)

@@ -48,6 +48,8 @@ struct StreamCtl {
   unsigned long long goal_moves;  // stop once the engine-wide move counter reaches this (0 = no goal)
   unsigned long long batches;     // network batches served (measurement)
   unsigned long long cyc_claim, cyc_tower, cyc_heads;   // SM cycles the network CTAs spent waiting for work / in the tower / in the heads (measurement)
+  unsigned long long cyc_search_busy, cyc_search_total; // search warps: cycles inside advance_slot / resident (measurement)
+  unsigned long long search_calls;                      // advance_slot calls (measurement)
 };
 
 // Built-in network (net.cu)

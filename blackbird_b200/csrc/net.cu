@@ -441,10 +441,13 @@ template <class G>
 static void tc_footprint(NetDev* net, int* regs, int* smem) {
   cudaFuncAttributes fa{};
   cudaFuncGetAttributes(&fa, k_net_forward_tc<G>);
-  *regs = ((fa.numRegs * 32 + 511) / 512 * 512) * (TcGeom<G>::THREADS / 32);    // per-warp allocations are rounded up (512 assumed)
+  // an SM's register file is four 16 K files, one per scheduler; a CTA's warps are dealt round-robin, and per-warp
+  // allocations are rounded up to 512 registers: what counts is the fullest quarter (measured: 12 search warps of
+  // 128 registers + 10 network warps of 48 add up to 64.5 K of 64 K and still do not share an SM)
+  *regs = ((fa.numRegs * 32 + 511) / 512 * 512) * ((TcGeom<G>::THREADS / 32 + 3) / 4);
   *smem = TcSmem<G>(net->tc.w_blocks, net->p.layers).total + 1024;
 }
-// registers and shared memory one CTA of the tensor-core kernel holds on its SM
+// registers (in the fullest of the SM's four register files) and shared memory one CTA of the tensor-core kernel holds on its SM
 int net_tc_footprint(NetDev* net, int* regs, int* smem) {
   BB_DISPATCH_GAME(net->game, tc_footprint<G>(net, regs, smem); return BB_OK);
   return BB_EINVAL;

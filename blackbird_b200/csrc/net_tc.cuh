@@ -62,7 +62,14 @@ struct TcGeom {
   static_assert(TILES * 16 <= 256, "too many tiles for TMEM");
   static_assert(TILES <= 8, "one mbarrier pair and 16 TMEM columns per tile, 128 columns per pipeline");
   static constexpr int PIPES = 2;                           // independent pipelines per CTA
-  static constexpr int EPI_GROUPS = 2;                      // per pipeline: groups of four warps (one per TMEM lane quarter); group g drains tiles g, g+2, ...
+  // per pipeline: groups of four warps (one per TMEM lane quarter); group g drains tiles g, g + GROUPS, ...
+  // One group is the default: streaming batches are one to three tiles, and the four warps a second group would
+  // cost are worth more as search warps (register file: DESIGN.md "co-residency").  Splitting a tile's 16 output
+  // channels over two groups instead was tried and lost: the epilogue's cost is per-row overhead, not per channel.
+#ifndef BB_TC_EPI_GROUPS
+#define BB_TC_EPI_GROUPS 1
+#endif
+  static constexpr int EPI_GROUPS = BB_TC_EPI_GROUPS;
   static constexpr int EPI_THREADS = EPI_GROUPS * 128;      // epilogue threads of one pipeline
   static constexpr int PIPE_THREADS = EPI_THREADS + 32;     // + its MMA-issuing warp
   static constexpr int THREADS = PIPES * PIPE_THREADS;
@@ -237,7 +244,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
 };
 
 template <class G>
-__global__ void __launch_bounds__(TcGeom<G>::THREADS + 64, 2)   // 48 registers: the CTA shares its SM's register file with a search CTA
+__global__ void __launch_bounds__(640, 2)   // <= 48 registers whatever the thread count: the CTA shares its SM's register file with a search CTA
 k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict__ states, int n_max,
                  const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value, NetServe sv) {
   using Ge = TcGeom<G>;

@@ -451,17 +451,17 @@ struct EngineT : bb_engine {
       cudaFuncAttributes fa{};
       stream_fits = 0;
       if (net_tc_footprint(net, &nregs, &nsmem) == BB_OK && cudaFuncGetAttributes(&fa, k_search_stream<G>) == cudaSuccess) {
-        const int sregs = ((fa.numRegs * 32 + 511) / 512 * 512) * STREAM_WARPS_PER_CTA;
-        stream_fits = (nregs + sregs <= 65536 && nsmem + (int)fa.sharedSizeBytes + 1024 <= 227 * 1024) ? 1 : 0;
+        const int sregs = ((fa.numRegs * 32 + 511) / 512 * 512) * ((STREAM_WARPS_PER_CTA + 3) / 4);   // per register-file quarter
+        stream_fits = (nregs + sregs <= 16384 && nsmem + (int)fa.sharedSizeBytes + 1024 <= 227 * 1024) ? 1 : 0;
         if (getenv("BB_DEBUG_OCC"))
-          fprintf(stderr, "[bbengine] streaming: network CTA %d regs %d B smem, search CTA %d regs %zu B smem -> %s\n", nregs, nsmem, sregs,
+          fprintf(stderr, "[bbengine] streaming: network CTA %d regs per SM quarter %d B smem, search CTA %d regs per quarter %zu B smem -> %s\n", nregs, nsmem, sregs,
                   fa.sharedSizeBytes, stream_fits ? "co-resident" : "do NOT fit one SM, tick mode");
       }
     }
     return stream_fits == 1;
   }
   // One launch pair: the persistent network kernel (one CTA per SM) and the persistent search kernel
-  // (one 8-warp CTA per SM; both fit an SM's register file together) run until every slot has left the
+  // (one CTA of STREAM_WARPS_PER_CTA warps per SM; both fit an SM's register file together) run until every slot has left the
   // busy phases, or until the engine-wide move counter reaches goal_moves.
   int run_stream(unsigned long long goal_moves) {
     int rc = sync_lanes();
@@ -500,8 +500,9 @@ struct EngineT : bb_engine {
     StreamCtl h{};
     BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
     if (getenv("BB_DEBUG_STREAM") && h.batches)
-      fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles\n", h.batches,
-              (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches);
+      fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles; search warps busy %.3f, %.0f cycles per advance call\n", h.batches,
+              (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches,
+              (double)h.cyc_search_busy / (double)(h.cyc_search_total ? h.cyc_search_total : 1), (double)h.cyc_search_busy / (double)(h.search_calls ? h.search_calls : 1));
     if (h.stop == 2u) { set_error("streaming watchdog fired: a search warp or the network kernel waited for seconds (see stderr)"); return BB_ESTATE; }
     return BB_OK;
   }
@@ -712,12 +713,13 @@ struct EngineT : bb_engine {
   int n_lanes() override { return (int)lanes.size(); }
   int streaming() override { return use_stream() ? 1 : 0; }
   int stream_stats(uint64_t* out) override {
-    for (int i = 0; i < 5; ++i) out[i] = 0;
+    for (int i = 0; i < 8; ++i) out[i] = 0;
     if (!use_stream() || !q_dev) return BB_OK;
     StreamCtl h{};
     BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
     out[0] = h.batches; out[1] = h.cyc_claim; out[2] = h.cyc_tower; out[3] = h.cyc_heads;
     out[4] = 2ull * (unsigned long long)net_sm_count(net);
+    out[5] = h.cyc_search_busy; out[6] = h.cyc_search_total; out[7] = h.search_calls;
     return BB_OK;
   }
 };
@@ -796,6 +798,6 @@ int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
 int bb_engine_streaming(bb_engine* e) { BB_NEED(e); return e->streaming(); }
-int bb_stream_stats(bb_engine* e, uint64_t out[5]) { BB_NEED(e); if (!out) return BB_EINVAL; return e->stream_stats(out); }
+int bb_stream_stats(bb_engine* e, uint64_t out[8]) { BB_NEED(e); if (!out) return BB_EINVAL; return e->stream_stats(out); }
 
 }  // extern "C"

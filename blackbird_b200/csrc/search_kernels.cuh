@@ -139,7 +139,17 @@ __device__ __forceinline__ void run_compaction(const EngineDev<G>& E, Slot<G>& s
 }
 
 
-constexpr int STREAM_WARPS_PER_CTA = 8;
+// Search warps per SM in streaming mode and their register cap.  An SM's register file is four 16 K-register
+// quarters (one per scheduler); a CTA's warps are dealt over them and allocations are per warp, so what must fit is
+// ceil(warps / 4) * registers * 32 of this kernel plus the same figure of the network kernel (3 * 56 * 32) <= 16384.
+// 12 warps of 112 registers beat 8 warps of 128 (the search is latency-bound: more warps, not more registers).
+#ifndef BB_STREAM_WARPS
+#define BB_STREAM_WARPS 12
+#endif
+#ifndef BB_STREAM_MAXREG
+#define BB_STREAM_MAXREG 112
+#endif
+constexpr int STREAM_WARPS_PER_CTA = BB_STREAM_WARPS;
 #ifndef BB_ADV_MIN_CTAS
 #define BB_ADV_MIN_CTAS 1
 #endif
@@ -319,7 +329,7 @@ constexpr int STREAM_MAX_OWN = 32;      // slots per warp
 constexpr unsigned STREAM_WATCHDOG_SPINS = 4u << 20;   // idle polls (~0.5 us each) before a warp gives up
 
 template <class G>
-__global__ void __launch_bounds__(32 * STREAM_WARPS_PER_CTA, 2) k_search_stream(EngineDev<G> E) {   // <= 128 registers: one CTA fits an SM NEXT TO the network CTA
+__global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) {   // <= 128 registers: one CTA fits an SM NEXT TO the network CTA
   __shared__ WarpScratch s_ws[STREAM_WARPS_PER_CTA];
   __shared__ uint32_t s_ticket[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];
   __shared__ uint8_t s_state[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];   // 0 runnable, 1 waiting for an answer, 2 finished
@@ -341,6 +351,9 @@ __global__ void __launch_bounds__(32 * STREAM_WARPS_PER_CTA, 2) k_search_stream(
   const volatile unsigned long long* moves = reinterpret_cast<const volatile unsigned long long*>(&E.counters->moves);
   const unsigned long long goal = E.q->goal_moves;
   unsigned idle = 0;
+  const long long t_in = clock64();
+  long long t_busy = 0;
+  unsigned calls = 0;
   for (;;) {
     bool progressed = false, any_busy = false;
     for (int j = 0; j < n_own; ++j) {
@@ -353,7 +366,10 @@ __global__ void __launch_bounds__(32 * STREAM_WARPS_PER_CTA, 2) k_search_stream(
         __threadfence();                                     // acquire: the answer was written before its sequence number
       }
       uint32_t ticket = 0;
+      const long long t0 = clock64();
       const int ph = advance_slot(E, g, 0u, s_ws[wl], &ticket);
+      t_busy += clock64() - t0;
+      ++calls;
       progressed = true;
       int nst = 2;
       if (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) nst = 1;
@@ -380,6 +396,11 @@ __global__ void __launch_bounds__(32 * STREAM_WARPS_PER_CTA, 2) k_search_stream(
         break;
       }
     }
+  }
+  if (lane == 0) {
+    atomicAdd(&E.q->cyc_search_busy, (unsigned long long)t_busy);
+    atomicAdd(&E.q->cyc_search_total, (unsigned long long)(clock64() - t_in));
+    atomicAdd(&E.q->search_calls, (unsigned long long)calls);
   }
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -161,9 +161,9 @@ class Engine(object):
 
     def stream_stats(self):
         """Cumulative busy accounting of the streaming network kernel (batches, wait / tower / heads cycles, pipelines)."""
-        out = (C.c_uint64 * 5)()
+        out = (C.c_uint64 * 8)()
         check(lib.bb_stream_stats(self._h, out))
-        return dict(zip(('batches', 'cyc_wait', 'cyc_tower', 'cyc_heads', 'pipelines'), [int(x) for x in out]))
+        return dict(zip(('batches', 'cyc_wait', 'cyc_tower', 'cyc_heads', 'pipelines', 'cyc_search_busy', 'cyc_search_total', 'search_calls'), [int(x) for x in out]))
 
     def close(self):
         if getattr(self, '_h', None):

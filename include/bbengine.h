@@ -183,8 +183,9 @@ int bb_engine_lanes(bb_engine* e);   /* lanes the engine runs with */
 int bb_engine_streaming(bb_engine* e);
 /* Streaming-mode busy accounting since engine creation: out[0] batches served by the network kernel, out[1..3]
  * SM cycles its pipelines spent waiting for tickets, in the convolution tower, and in heads + publish (summed over
- * pipelines); out[4] pipelines x SMs serving.  Zeros in tick mode.  bench.py turns them into busy fractions. */
-int bb_stream_stats(bb_engine* e, uint64_t out[5]);
+ * pipelines); out[4] pipelines x SMs serving; out[5..7] search warps: cycles inside the per-slot advance routine, cycles
+ * resident, advance calls.  Zeros in tick mode.  bench.py turns them into busy fractions. */
+int bb_stream_stats(bb_engine* e, uint64_t out[8]);
 
 #ifdef __cplusplus
 }
