@@ -66,6 +66,7 @@ struct NetServe {                 // the request ring as the persistent network 
 // answers go to policy[slot][A] / value[slot]
 int net_serve(NetDev* net, const NetServe& sv, float* policy, float* value, cudaStream_t stream);
 int net_sm_count(NetDev* net);
+int net_pipes(NetDev* net);
 int net_tc_footprint(NetDev* net, int* regs, int* smem);
 bool net_is_tc(NetDev* net);
 int net_create(int game, const bb_net_desc* d, const float* w_host, size_t n_floats, NetDev** out);

@@ -127,6 +127,7 @@ struct Team {
   __device__ __forceinline__ void sync() const {           // literal barrier ids: a register id makes ptxas reserve all 16 barriers
     if (bar == 1) asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory");
     else if (bar == 2) asm volatile("bar.sync 2, %0;" ::"r"(n) : "memory");
+    else if (bar == 3) asm volatile("bar.sync 3, %0;" ::"r"(n) : "memory");
     else asm volatile("bar.sync 0, %0;" ::"r"(n) : "memory");
   }
 };
@@ -442,12 +443,17 @@ static void tc_footprint(NetDev* net, int* regs, int* smem) {
   cudaFuncAttributes fa{};
   cudaFuncGetAttributes(&fa, k_net_forward_tc<G>);
   // an SM's register file is four 16 K files, one per scheduler; a CTA's warps are dealt round-robin, and per-warp
-  // allocations are rounded up to 512 registers: what counts is the fullest quarter (measured: 12 search warps of
-  // 128 registers + 10 network warps of 48 add up to 64.5 K of 64 K and still do not share an SM)
-  *regs = ((fa.numRegs * 32 + 511) / 512 * 512) * ((TcGeom<G>::THREADS / 32 + 3) / 4);
+  // allocations are rounded up to 256 registers: what counts is the fullest quarter (measured: 12 search warps of
+  // 128 registers + 10 network warps of 48 add up to 64.5 K of 64 K and still do not share an SM; 12 x 104 next to
+  // 15 x 48 = 3 * 3328 + 4 * 1536 = 16128 per quarter do)
+  *regs = ((fa.numRegs * 32 + 255) / 256 * 256) * ((TcGeom<G>::THREADS / 32 + 3) / 4);
   *smem = TcSmem<G>(net->tc.w_blocks, net->p.layers).total + 1024;
 }
 // registers (in the fullest of the SM's four register files) and shared memory one CTA of the tensor-core kernel holds on its SM
+int net_pipes(NetDev* net) {                       // pipelines per CTA of the tensor-core kernel: the servers of the request ring
+  BB_DISPATCH_GAME(net->game, return TcGeom<G>::PIPES);
+  return 1;
+}
 int net_tc_footprint(NetDev* net, int* regs, int* smem) {
   BB_DISPATCH_GAME(net->game, tc_footprint<G>(net, regs, smem); return BB_OK);
   return BB_EINVAL;

@@ -41,10 +41,17 @@ template <class G> struct TcBatch;
 // that leaves the tensor pipe idle most of the time, so the CTA runs TWO independent pipelines: each has its
 // own MMA-issuing warp, eight epilogue warps, activation buffers, TMEM columns, mbarriers and named barrier,
 // and works on its own batch; they share the resident weights and interleave on the tensor pipe.
-// Largest batch of one pipeline (positions): up to seven 128-row tiles.
-template <> struct TcBatch<TicTacToe> { static constexpr int NP = 56; };     // 56 * 16 rows = 896
-template <> struct TcBatch<Connect4> { static constexpr int NP = 14; };      // 14 * 56 rows = 784
-template <> struct TcBatch<DragonChess> { static constexpr int NP = 6; };    //  6 * 81 rows = 486 (17 input planes need a separate input buffer)
+// Largest batch of one pipeline (positions): up to seven 128-row tiles.  DragonChess (17 input planes: a separate
+// two-block input buffer) has room for two pipelines only.
+// Two pipelines is the default: a third one (BB_TC_PIPES=3, four-tile batches) was measured and changes nothing in
+// streaming mode -- with three batches in flight the tensor pipe is the shared bottleneck (nine 128x16x16 MMAs per
+// tile and layer at ~47 cycles each, paced by the 4 KB A-operand read from shared memory, not by the math).
+#ifndef BB_TC_PIPES
+#define BB_TC_PIPES 2
+#endif
+template <> struct TcBatch<TicTacToe> { static constexpr int NP = BB_TC_PIPES == 3 ? 32 : 56, PIPES = BB_TC_PIPES; };   // 56 * 16 rows = 896
+template <> struct TcBatch<Connect4> { static constexpr int NP = BB_TC_PIPES == 3 ? 9 : 14, PIPES = BB_TC_PIPES; };     // 14 * 56 rows = 784
+template <> struct TcBatch<DragonChess> { static constexpr int NP = 6, PIPES = 2; };                                    //  6 * 81 rows = 486
 
 template <class G>
 struct TcGeom {
@@ -57,11 +64,10 @@ struct TcGeom {
   static constexpr int PLANE = ROWS * 16;                   // bytes per k-half plane
   static constexpr int BUF = 2 * PLANE;                     // one 16-channel activation buffer
   static constexpr int KB_IN = (G::C + 15) / 16;            // 16-channel blocks of the input planes
-  static constexpr int TMEM_COLS = 256;                     // 128 per pipeline
   static_assert(LW + 1 <= TC_MARGIN, "tap offsets must stay inside the margin");
-  static_assert(TILES * 16 <= 256, "too many tiles for TMEM");
-  static_assert(TILES <= 8, "one mbarrier pair and 16 TMEM columns per tile, 128 columns per pipeline");
-  static constexpr int PIPES = 2;                           // independent pipelines per CTA
+  static_assert(TILES <= 8, "one mbarrier pair and 16 TMEM columns per tile, parity bits in one word");
+  static constexpr int PIPES = TcBatch<G>::PIPES;           // independent pipelines per CTA
+  static_assert(PIPES >= 1 && PIPES <= 3, "named barriers 1..3");
   // per pipeline: groups of four warps (one per TMEM lane quarter); group g drains tiles g, g + GROUPS, ...
   // One group is the default: streaming batches are one to three tiles, and the four warps a second group would
   // cost are worth more as search warps (register file: DESIGN.md "co-residency").  Splitting a tile's 16 output
@@ -73,7 +79,10 @@ struct TcGeom {
   static constexpr int EPI_THREADS = EPI_GROUPS * 128;      // epilogue threads of one pipeline
   static constexpr int PIPE_THREADS = EPI_THREADS + 32;     // + its MMA-issuing warp
   static constexpr int THREADS = PIPES * PIPE_THREADS;
-  static constexpr int TMEM_PIPE_COLS = 128;
+  static constexpr int TMEM_PIPE_COLS = TILES * 16;         // one 16-column accumulator per tile
+  static constexpr int TMEM_COLS = PIPES * TMEM_PIPE_COLS <= 32 ? 32 : PIPES * TMEM_PIPE_COLS <= 64 ? 64 : PIPES * TMEM_PIPE_COLS <= 128 ? 128
+                                   : PIPES * TMEM_PIPE_COLS <= 256 ? 256 : 512;   // allocations are powers of two
+  static_assert(PIPES * TMEM_PIPE_COLS <= 512, "TMEM has 512 columns");
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -244,7 +253,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
 };
 
 template <class G>
-__global__ void __launch_bounds__(640, 2)   // <= 48 registers whatever the thread count: the CTA shares its SM's register file with a search CTA
+__global__ void __launch_bounds__(576, 2)   // <= 56 registers whatever the thread count: the CTA shares its SM's register file with a search CTA
 k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict__ states, int n_max,
                  const int* __restrict__ count_dev, float* __restrict__ policy, float* __restrict__ value, NetServe sv) {
   using Ge = TcGeom<G>;
@@ -265,7 +274,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   const int tid = tid_cta - pipe * Ge::PIPE_THREADS;        // thread index inside the pipeline
   const int pwarp = tid >> 5;                               // warp index inside the pipeline: 0..7 epilogue, 8 MMA issuer
   const bool is_mma = pwarp == 4 * Ge::EPI_GROUPS;
-  const Team team{tid, Ge::PIPE_THREADS, 1 + pipe};         // named barrier 1 / 2: the pipelines never wait for each other
+  const Team team{tid, Ge::PIPE_THREADS, 1 + pipe};         // named barrier 1 + pipeline: the pipelines never wait for each other
   uint8_t* sW = tc_smem + L.w;
   float* sBias = reinterpret_cast<float*>(tc_smem + L.bias);
   float* sHead = reinterpret_cast<float*>(tc_smem + L.head);
@@ -339,6 +348,9 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           const int open = (int)(*vt - *vh);
           if (open > 0) {
             c = min((unsigned)Ge::NP, max(1u, ((unsigned)open + srv - 1u) / srv));
+            // the tower's cost is per 128-row tile, not per position: fill the last tile while tickets are open
+            const unsigned fill = (((c * Ge::RPP + 127u) >> 7) << 7) / Ge::RPP;
+            c = max(c, min(min(fill, (unsigned)Ge::NP), (unsigned)open));
             hh = atomicAdd(&sv.q->head, c);
             for (;;) {                                          // the claim may be ahead of the tail
               if ((int)(*vt - (hh + c)) >= 0) break;

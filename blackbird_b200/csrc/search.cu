@@ -451,7 +451,8 @@ struct EngineT : bb_engine {
       cudaFuncAttributes fa{};
       stream_fits = 0;
       if (net_tc_footprint(net, &nregs, &nsmem) == BB_OK && cudaFuncGetAttributes(&fa, k_search_stream<G>) == cudaSuccess) {
-        const int sregs = ((fa.numRegs * 32 + 511) / 512 * 512) * ((STREAM_WARPS_PER_CTA + 3) / 4);   // per register-file quarter
+        int sregs = ((fa.numRegs * 32 + 255) / 256 * 256) * ((STREAM_WARPS_PER_CTA + 3) / 4);   // per register-file quarter
+        if (getenv("BB_STREAM_FORCE")) sregs = 0;                 // experiments only: a wrong guess ends in the watchdog, not a hang
         stream_fits = (nregs + sregs <= 16384 && nsmem + (int)fa.sharedSizeBytes + 1024 <= 227 * 1024) ? 1 : 0;
         if (getenv("BB_DEBUG_OCC"))
           fprintf(stderr, "[bbengine] streaming: network CTA %d regs per SM quarter %d B smem, search CTA %d regs per quarter %zu B smem -> %s\n", nregs, nsmem, sregs,
@@ -474,7 +475,7 @@ struct EngineT : bb_engine {
     if (grid > sms) grid = sms;
     if ((long long)grid * per_cta < d.n_games) grid = (d.n_games + per_cta - 1) / per_cta;
     if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
-    int div = 2 * sms;                                          // a claim takes open / div tickets (1 .. NP); two pipelines per CTA
+    int div = net_pipes(net) * sms;                             // a claim takes open / div tickets (1 .. NP); div = pipelines serving
     if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : div;
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
@@ -718,7 +719,7 @@ struct EngineT : bb_engine {
     StreamCtl h{};
     BB_CUDA(cudaMemcpy(&h, q_dev, sizeof h, cudaMemcpyDeviceToHost));
     out[0] = h.batches; out[1] = h.cyc_claim; out[2] = h.cyc_tower; out[3] = h.cyc_heads;
-    out[4] = 2ull * (unsigned long long)net_sm_count(net);
+    out[4] = (unsigned long long)net_pipes(net) * (unsigned long long)net_sm_count(net);
     out[5] = h.cyc_search_busy; out[6] = h.cyc_search_total; out[7] = h.search_calls;
     return BB_OK;
   }
