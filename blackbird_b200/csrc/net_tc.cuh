@@ -167,6 +167,10 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+__device__ __forceinline__ uint32_t pack_relu_bf16(float a, float b) {
+  __nv_bfloat162 h = __hmax2(__floats2bfloat162_rn(a, b), __floats2bfloat162_rn(0.f, 0.f));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
 __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
   __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&u);
   return __bfloat1622float2(h);
@@ -182,8 +186,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// barrier among the epilogue threads only (the MMA warp never joins barrier 1)
-__device__ __forceinline__ void epi_bar_sync(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
+// barrier among the epilogue threads of one pipeline (ids 4..6; the MMA warp never joins; literal ids, see Team)
+template <int NTHREADS>
+__device__ __forceinline__ void epi_bar_sync(int pipe) {
+  if (pipe == 0) asm volatile("bar.sync 4, %0;" ::"n"(NTHREADS) : "memory");
+  else if (pipe == 1) asm volatile("bar.sync 5, %0;" ::"n"(NTHREADS) : "memory");
+  else asm volatile("bar.sync 6, %0;" ::"n"(NTHREADS) : "memory");
+}
 
 // The nine taps of one 128-row tile in ONE asm block: per tap a 32-bit add on the low descriptor word
 // (start-address field, 16-byte units) for A (shifted rows) and for B (next 512-byte weight block).
@@ -226,7 +235,7 @@ template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
   int w, bias, head, wbar, tmem, pipe0, pipe_stride, total;          // shared by both pipelines, then one block per pipeline
-  int x, y, in, hsum, red, idx, claim, mbar;                         // offsets inside a pipeline's block
+  int x, y, in, hsum, red, idx, st, claim, mbar;                     // offsets inside a pipeline's block
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
@@ -244,6 +253,8 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     hsum = q; q += Ge::NP * 4 * 4;
     red = q; q += 32 * 4;
     idx = q; q += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
+    q = (q + 15) & ~15;
+    st = q; q += Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);   // the batch's packed states, staged once
     claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     q = (q + 7) & ~7;
     mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
@@ -287,6 +298,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   float* hsum = reinterpret_cast<float*>(pb + L.hsum);
   float* red = reinterpret_cast<float*>(pb + L.red);
   int* sIdx = reinterpret_cast<int*>(pb + L.idx);
+  constexpr int ST_STRIDE = (int)((sizeof(State) + 15) & ~15u);
+  uint8_t* sState = pb + L.st;
   volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(pb + L.claim);
   uint64_t* full = reinterpret_cast<uint64_t*>(pb + L.mbar);          // MMA -> epilogue, per tile
   uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
@@ -327,6 +340,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   // advance at their own pace (full: epilogue side, ready: MMA side)
   uint32_t full_par = 0, ready_par = 0;
   bool weights_in = false;
+  unsigned pend_lo = 0, pend_n = 0;                         // serve mode, thread 0 of the pipeline: tickets claimed but not yet served
 
   int batch = (int)blockIdx.x * Ge::PIPES + pipe;
   for (;;) {
@@ -338,39 +352,43 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       if (tid == 0) {
         // Claim tickets with ONE atomicAdd (a compare-and-swap loop serialises the claimers: ~55 us of waiting per
         // batch was measured).  The size is open / divisor (at least 1, at most NP) from a possibly stale view, so a
-        // claim can run past the tail; those tickets are waited for, or dropped when the search has already left.
+        // claim can run past the tail.  Claimed tickets belong to this pipeline for good (pend_lo, pend_n); a batch
+        // is whatever part of them has been issued by now -- never wait for the rest: the slots that would issue
+        // them may all be waiting for answers of this very batch.
         unsigned c = 0, hh = 0, idle = 0;
         volatile unsigned* vt = reinterpret_cast<volatile unsigned*>(&sv.q->tail);
         volatile unsigned* vh = reinterpret_cast<volatile unsigned*>(&sv.q->head);
         volatile unsigned* vdone = reinterpret_cast<volatile unsigned*>(&sv.q->search_done);
         const unsigned srv = sv.q->servers, ctas = sv.q->search_ctas;
         for (;;) {
-          const int open = (int)(*vt - *vh);
-          if (open > 0) {
-            c = min((unsigned)Ge::NP, max(1u, ((unsigned)open + srv - 1u) / srv));
-            // the tower's cost is per 128-row tile, not per position: fill the last tile while tickets are open
-            const unsigned fill = (((c * Ge::RPP + 127u) >> 7) << 7) / Ge::RPP;
-            c = max(c, min(min(fill, (unsigned)Ge::NP), (unsigned)open));
-            hh = atomicAdd(&sv.q->head, c);
-            for (;;) {                                          // the claim may be ahead of the tail
-              if ((int)(*vt - (hh + c)) >= 0) break;
-              if (*vdone >= ctas) {
-                __threadfence();
-                const int have = (int)(*vt - hh);
-                c = have > 0 ? min(c, (unsigned)have) : 0u;
-                break;
-              }
-              __nanosleep(100);
+          if (pend_n == 0) {
+            const int open = (int)(*vt - *vh);
+            if (open > 0) {
+              unsigned want = min((unsigned)Ge::NP, max(1u, ((unsigned)open + srv - 1u) / srv));
+              // the tower's cost is per 128-row tile, not per position: fill the last tile while tickets are open
+              const unsigned fill = (((want * Ge::RPP + 127u) >> 7) << 7) / Ge::RPP;
+              want = max(want, min(min(fill, (unsigned)Ge::NP), (unsigned)open));
+              pend_lo = atomicAdd(&sv.q->head, want);
+              pend_n = want;
             }
-            if (c) break;
-            continue;
           }
-          if (*vdone >= ctas) {
+          if (pend_n) {
+            const int have = (int)(*vt - pend_lo);
+            if (have > 0) {
+              c = min(pend_n, (unsigned)have);
+              hh = pend_lo;
+              pend_lo += c;
+              pend_n -= c;
+              break;
+            }
+          }
+          if (*vdone >= ctas) {                                 // the search has left: nothing more will be issued
             __threadfence();
+            if (pend_n) { if ((int)(*vt - pend_lo) > 0) continue; pend_n = 0; }
             if ((int)(*vt - *vh) <= 0) { c = 0; break; }        // nobody left to ask
             continue;
           }
-          __nanosleep(200);
+          __nanosleep(pend_n ? 100 : 200);
           if (++idle > (16u << 20)) {                           // seconds without a request or a finished search: give up, never hang
             if (blockIdx.x == 0) printf("[bbengine] streaming watchdog: network kernel idle (head %u tail %u, search CTAs done %u of %u)\n", *vh, *vt,
                                         *vdone, ctas);
@@ -427,25 +445,35 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
     } else {
       // ---- epilogue warps: group wg drains tiles wg, wg + 2, ...; TMEM lane quarter q = warp % 4 -----------
       const int wg = pwarp >> 2, q = warp & 3;               // q follows the CTA-wide warp id: a warp reaches TMEM lanes 32 * (warp % 4) ...
-      // input planes (AsInputArray) decoded straight from the packed states into the raster rows
+      // stage the batch's packed states once (one thread per position: in streaming mode it waits for the ticket's
+      // entry to be published and reads it through L2), so the global-memory latency is paid once per batch and
+      // not once per tile
+      if (tid < cnt) {
+        const State* src;
+        if (serve) {
+          const unsigned tk = ticket0 + (unsigned)tid, e = tk & sv.q_mask;
+          for (unsigned spin = 0; *reinterpret_cast<volatile unsigned*>(&sv.q_seq[e]) != tk + 1u && spin < (64u << 20); ++spin) {}
+          __threadfence();
+          src = reinterpret_cast<const State*>(sv.q_state) + e;
+          sIdx[tid] = __ldcg(sv.q_slot + e);                // where the answer goes
+        } else {
+          src = states + base + tid;
+        }
+        uint32_t* dst = reinterpret_cast<uint32_t*>(sState + tid * ST_STRIDE);
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(State) / 4); ++i) dst[i] = __ldcg(reinterpret_cast<const uint32_t*>(src) + i);
+      }
+      epi_bar_sync<Ge::EPI_THREADS>(pipe);
+      // input planes (AsInputArray) decoded from the staged states into the raster rows; okmask: this thread's row
+      // is a board cell of the batch, per tile
+      uint32_t okmask = 0;
       for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
         const int row = t * 128 + q * 32 + lane;
         const int pos = row / Ge::RPP, l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
         if (row < cnt * Ge::RPP && line >= 1 && col < G::W) {
+          okmask |= 1u << t;
           const int cell = (line - 1) * G::W + col;
-          State s;
-          if (serve) {                                      // wait for the ticket's entry to be published, read it through L2
-            const unsigned tk = ticket0 + (unsigned)pos, e = tk & sv.q_mask;
-            for (unsigned spin = 0; *reinterpret_cast<volatile unsigned*>(&sv.q_seq[e]) != tk + 1u && spin < (64u << 20); ++spin) {}
-            __threadfence();
-            const uint32_t* src = reinterpret_cast<const uint32_t*>(reinterpret_cast<const State*>(sv.q_state) + e);
-            uint32_t* dst = reinterpret_cast<uint32_t*>(&s);
-#pragma unroll
-            for (int i = 0; i < (int)(sizeof(State) / 4); ++i) dst[i] = __ldcg(src + i);
-            if (l == Ge::LW) sIdx[pos] = __ldcg(sv.q_slot + e);   // the position's first cell records where the answer goes
-          } else {
-            s = states[base + pos];
-          }
+          const State s = *reinterpret_cast<const State*>(sState + pos * ST_STRIDE);
 #pragma unroll
           for (int kb = 0; kb < Ge::KB_IN; ++kb)
 #pragma unroll
@@ -475,8 +503,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         const float* bias = sBias + layer * 16;
         for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
           const int row = t * 128 + q * 32 + lane;
-          const int l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
-          const bool cell_ok = row < cnt * Ge::RPP && line >= 1 && col < G::W;
+          const bool cell_ok = (okmask >> t) & 1u;
           mbar_wait(&full[t], (full_par >> t) & 1u);
           full_par ^= 1u << t;
           tc_fence_after();
@@ -496,14 +523,14 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
                 acc[2 * i + 1] += f.y;
               }
             }
-#pragma unroll
-            for (int c = 0; c < 16; ++c) acc[c] = fmaxf(acc[c], 0.f);
-            if (!last) {
-              *reinterpret_cast<uint4*>(slot) = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
-                                                           pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-              *reinterpret_cast<uint4*>(slot + Ge::PLANE) = make_uint4(pack_bf16(acc[8], acc[9]), pack_bf16(acc[10], acc[11]),
-                                                                       pack_bf16(acc[12], acc[13]), pack_bf16(acc[14], acc[15]));
+            if (!last) {                                    // ReLU on the packed pairs: rounding is monotonic, so the order does not matter
+              *reinterpret_cast<uint4*>(slot) = make_uint4(pack_relu_bf16(acc[0], acc[1]), pack_relu_bf16(acc[2], acc[3]),
+                                                           pack_relu_bf16(acc[4], acc[5]), pack_relu_bf16(acc[6], acc[7]));
+              *reinterpret_cast<uint4*>(slot + Ge::PLANE) = make_uint4(pack_relu_bf16(acc[8], acc[9]), pack_relu_bf16(acc[10], acc[11]),
+                                                                       pack_relu_bf16(acc[12], acc[13]), pack_relu_bf16(acc[14], acc[15]));
             } else {
+#pragma unroll
+              for (int c = 0; c < 16; ++c) acc[c] = fmaxf(acc[c], 0.f);
               // heads from the fp32 registers: 1x1 convs (1 value + 2 policy filters) + BN + ReLU; the three
               // per-cell values replace this row's (now dead) slot in X
               float v = sHead[16], p0 = sHead[17 + 32], p1 = sHead[17 + 33];
