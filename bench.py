@@ -115,7 +115,7 @@ def run_reference(args):
         tot_t += wall
     value = sum(vals) / len(vals)
     sample = '%d worker processes x %.0f s of Connect4 FixedMCTS self-play per step (oracle port, numpy fp32 network at batch 1)' % (cores, seconds)
-    print(json.dumps({
+    print_line(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': 1e3 * tot_t / max(1, args.steps), 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(args, args.gpus),
@@ -337,7 +337,7 @@ def run_ours(args):
                'sample': '%d worker processes x %.0f s of the same workload (oracle port of the reference, numpy fp32 network at batch 1)' % (cores, wall)}
 
     if rank == 0:
-        print(json.dumps({
+        print_line(json.dumps({
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': ms / max(1, args.steps), 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
@@ -351,7 +351,21 @@ def run_ours(args):
     eng.close()
 
 
+_STDOUT = None
+
+
+def print_line(text):
+    """The bench line goes to the process's REAL stdout; everything else that writes to fd 1 (NCCL's version
+    banner, build logs of child processes) was redirected to stderr in main(), so stdout is ONE JSON line."""
+    _STDOUT.write(text + '\n')
+    _STDOUT.flush()
+
+
 def main():
+    global _STDOUT
+    sys.stdout.flush()
+    _STDOUT = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
     args = parse()
     if args.impl == 'reference':
         run_reference(args)
