@@ -475,7 +475,7 @@ struct EngineT : bb_engine {
     if (grid > sms) grid = sms;
     if ((long long)grid * per_cta < d.n_games) grid = (d.n_games + per_cta - 1) / per_cta;
     if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
-    int div = net_pipes(net) * sms;                             // a claim takes open / div tickets (1 .. NP); div = pipelines serving
+    int div = sms;                                                                          // a claim takes open / div tickets (1 .. NP); div = pipelines serving
     if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : div;
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());

@@ -147,6 +147,48 @@ def test_streaming_equals_tick_mode(mods, game, kind, P, G, monkeypatch):
     assert out['1'][0] == out['0'][0]
 
 
+def test_full_size_streaming(mods):
+    """BASELINE configs[1] at full size through the benchmarked path: 4096 Connect4 games, FixedMCTS, 800
+    simulations per move, bf16 network, streaming mode.  Size-independent properties over all games (every game
+    ends, the simulations spent equal 800 per recorded move, records replay legally to the recorded winner) and,
+    for two slots, the first three moves' visit counts and chosen actions against the oracle search replaying the
+    same kernel's outputs."""
+    engine, records = mods
+    from blackbird_b200 import netinit
+    game, G, P = 'Connect4', 4096, 800
+    eng = engine.Engine(game, 'fixed', n_games=G, evaluator='net', play_limit_hint=P)
+    eng.load_network(netinit.random_weights(3, 7, seed=0), 4, 16, 16, precision='bf16')
+    assert eng.streaming
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
+    eng.selfplay(P, 1.0, u)
+    raw = eng.records_raw()
+    c = eng.counters()
+    assert (raw['winner'] >= 0).all() and (raw['n_moves'] >= 7).all() and (raw['n_moves'] <= 42).all()
+    assert c['games_done'] == G and c['sims'] == int(raw['n_moves'].sum()) * P
+    for g in range(0, G, 131):
+        st = engine.init_states(game, 1)
+        for r in range(int(raw['n_moves'][g])):
+            lo, hi = raw['rec_off'][g, r], raw['rec_off'][g, r + 1]
+            assert int(raw['pool_plays'][g, lo:hi].sum()) >= P           # a carried subtree adds to the 800
+            a = int(raw['chosen'][g, r])
+            assert raw['pool_plays'][g, lo:hi][raw['pool_actions'][g, lo:hi] == a][0] > 0
+            assert np.array_equal(st.cpu().numpy()[0], raw['states'][g, r])
+            assert int(engine.apply(game, st, torch.tensor([a])).item()) == 1
+        assert int(engine.winner(game, st).item()) == int(raw['winner'][g])
+    replay = Replay(engine, eng, game)
+    for g in (0, G - 1):
+        s = search_np.NetSearch(replay, 'fixed', maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        _, _, trace = selfplay_np.play_game(s, GAMES[game], 1, max_plies=3)
+        for r, (plays, action, _, _) in enumerate(trace):
+            lo, hi = raw['rec_off'][g, r], raw['rec_off'][g, r + 1]
+            got = np.zeros(7)
+            got[raw['pool_actions'][g, lo:hi]] = raw['pool_plays'][g, lo:hi]
+            assert np.array_equal(got, plays), (g, r, got, plays)
+            assert int(raw['chosen'][g, r]) == action
+    eng.close()
+
+
 def test_noise_statistics(mods):
     """epsilon > 0: policy = (1-eps)*softmax + eps*Beta(alpha, 1-alpha) draws, renormalised (A.17).
     TF's RNG cannot be matched; check moments: E[Beta(a,1-a)] = a, Var = a(1-a)/2."""
