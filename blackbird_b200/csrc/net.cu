@@ -183,7 +183,7 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 template <class G>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
-                             float* __restrict__ value, const Team& tm, const int* out_idx = nullptr) {
+                             float* __restrict__ value, const Team& tm, const int* out_idx = nullptr, float* zbuf = nullptr) {
   constexpr int HW = G::H * G::W;
   const int tid = tm.tid, nthreads = tm.n;
   const int D = np.dense;                               // hd / pol_w / pol_b: np.head / np.pol_w / np.pol_b or copies in shared memory
@@ -228,26 +228,30 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
     for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
       const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
       float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
+      // intermediate values live in shared memory when the caller has room for A floats (every thread touches
+      // only its own actions, so no barrier beyond the reductions'); otherwise in the output row itself.
+      // Same operations in the same order either way: the results are bit-identical.
+      float* z_ = zbuf ? zbuf : out;
       float m = -INFINITY;
       for (int a = tid; a < G::A; a += nthreads) {
         float z = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
-        out[a] = z;
+        z_[a] = z;
         m = fmaxf(m, z);
       }
       m = block_reduce(m, red, true, tm);
       float sum = 0.f;
-      for (int a = tid; a < G::A; a += nthreads) { float e = expf(out[a] - m); out[a] = e; sum += e; }
+      for (int a = tid; a < G::A; a += nthreads) { float e = expf(z_[a] - m); z_[a] = e; sum += e; }
       sum = block_reduce(sum, red, false, tm);
       float tot = 0.f;
       for (int a = tid; a < G::A; a += nthreads) {
-        float pa = out[a] / sum;
+        float pa = z_[a] / sum;
         if (np.eps > 0.f)
           pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + p) * G::A + a);
-        out[a] = pa;
+        z_[a] = pa;
         tot += pa;
       }
       tot = block_reduce(tot, red, false, tm);
-      for (int a = tid; a < G::A; a += nthreads) out[a] = out[a] / tot;
+      for (int a = tid; a < G::A; a += nthreads) out[a] = z_[a] / tot;
     }
   }
 }

@@ -51,7 +51,7 @@ template <class G> struct TcBatch;
 #endif
 template <> struct TcBatch<TicTacToe> { static constexpr int NP = BB_TC_PIPES == 3 ? 32 : 56, PIPES = BB_TC_PIPES; };   // 56 * 16 rows = 896
 template <> struct TcBatch<Connect4> { static constexpr int NP = BB_TC_PIPES == 3 ? 9 : 14, PIPES = BB_TC_PIPES; };     // 14 * 56 rows = 784
-template <> struct TcBatch<DragonChess> { static constexpr int NP = 6, PIPES = 2; };                                    //  6 * 81 rows = 486
+template <> struct TcBatch<DragonChess> { static constexpr int NP = 4, PIPES = 2; };                                    //  4 * 81 rows = 324 (+ a 4032-float policy scratch row per pipeline)
 
 template <class G>
 struct TcGeom {
@@ -235,7 +235,7 @@ template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
   int w, bias, head, wbar, tmem, pipe0, pipe_stride, total;          // shared by both pipelines, then one block per pipeline
-  int x, y, in, hsum, red, idx, st, claim, mbar;                     // offsets inside a pipeline's block
+  int x, y, in, hsum, red, idx, st, zb, claim, mbar;                 // offsets inside a pipeline's block
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
@@ -255,6 +255,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     idx = q; q += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
     q = (q + 15) & ~15;
     st = q; q += Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);   // the batch's packed states, staged once
+    zb = q; if (G::A > 32) q += G::A * 4;          // wide policy heads: one row of logits / probabilities (heads_finish)
     claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     q = (q + 7) & ~7;
     mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
@@ -292,6 +293,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   uint64_t* wbar = reinterpret_cast<uint64_t*>(tc_smem + L.wbar);     // weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tc_smem + L.tmem);
   uint8_t* pb = tc_smem + L.pipe0 + pipe * L.pipe_stride;             // this pipeline's block
+  uint8_t* const pb_ = pb;
   uint8_t* bufX = pb + L.x;
   uint8_t* bufY = pb + L.y;
   uint8_t* bufIn = pb + L.in;
@@ -570,7 +572,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
-      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr);
+      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
+                      G::A > 32 ? reinterpret_cast<float*>(pb_ + L.zb) : nullptr);
     }
     if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
       __threadfence();
