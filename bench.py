@@ -33,7 +33,7 @@ METRIC, UNIT = 'connect4_mcts_simulations_per_sec', 'sims/s'
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=6)
+    ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--games', type=int, default=4096, help='concurrent games per GPU')
@@ -159,14 +159,14 @@ class ClockSampler(threading.Thread):
                 self.rows.append((sm, [k for k, b in bits.items() if mask & b]))
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05)
 
     def summary(self):
         self.stop_flag = True
         sm = sorted(r[0] for r in self.rows)
         reasons = sorted({k for r in self.rows for k in r[1]})
         return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': getattr(self, 'max_sm', None), 'reasons': reasons,
-                'samples': len(self.rows), 'how': 'NVML in-process, 200 ms period'}
+                'samples': len(self.rows), 'how': 'NVML in-process, 50 ms period'}
 
 
 def run_ours(args):
