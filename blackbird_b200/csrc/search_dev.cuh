@@ -61,8 +61,7 @@ __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, do
     }
   }
   for (int j = CHUNKS * 32 + lane; j < k; j += 32) tot += kids[j].s.plays;
-#pragma unroll
-  for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+  tot = __reduce_add_sync(0xFFFFFFFFu, tot);                 // one REDUX instead of five shuffle rounds
   const double t = __dsqrt_rn(__dadd_rn(1.0, (double)tot));   // exact integer sum (builtin sum of f64 ints)
   double bu = -1.0;
   int bj = 0x7FFFFFFF;
@@ -77,11 +76,19 @@ __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, do
     if (j < k) score(r[ci].s, j);
   }
   for (int j = CHUNKS * 32 + lane; j < k; j += 32) score(kids[j].s, j);
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    double ou = __shfl_xor_sync(0xFFFFFFFFu, bu, o);
-    int oj = __shfl_xor_sync(0xFFFFFFFFu, bj, o);
-    if (ou > bu || (ou == bu && oj < bj)) { bu = ou; bj = oj; }
+  // Warp argmax by (value, then smallest index) with three REDUX instructions instead of five rounds of 64-bit
+  // shuffles and compares: map the double to an unsigned key of the same order (-0.0 folded into +0.0 first, so
+  // equal values get equal keys), take the maximum of the high words, then of the low words among the lanes that
+  // hold it, then the smallest index among the lanes that hold both.  The winning value is rebuilt from the key.
+  {
+    const long long b = __double_as_longlong(__dadd_rn(bu, 0.0));
+    const unsigned long long key = (unsigned long long)(b ^ ((b >> 63) | (long long)0x8000000000000000ull));
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_max_sync(0xFFFFFFFFu, hi);
+    const unsigned mlo = __reduce_max_sync(0xFFFFFFFFu, hi == mhi ? lo : 0u);
+    bj = (int)__reduce_min_sync(0xFFFFFFFFu, (hi == mhi && lo == mlo) ? (unsigned)bj : 0x7FFFFFFFu);
+    const unsigned long long wk = ((unsigned long long)mhi << 32) | mlo;
+    bu = __longlong_as_double((long long)((wk >> 63) ? (wk ^ 0x8000000000000000ull) : ~wk));
   }
   *best_u = bu;
   if (bj != 0x7FFFFFFF) {
