@@ -67,6 +67,8 @@ SIGNATURES = {
     'bb_eval_fetch': (I, [VP, VP, VP]),
     'bb_eval_submit': (I, [VP, VP, VP]),
     'bb_selfplay_run': (I, [VP, I, C.c_double, VP]),
+    'bb_selfplay_games': (I, [VP, I, I, C.c_double, VP]),
+    'bb_records_rows': (I, [VP]),
     'bb_selfplay_step': (I, [VP, I, I, C.c_double, VP]),
     'bb_selfplay_stream': (I, [VP, C.c_longlong, I, C.c_double, VP]),
     'bb_engine_stream': (VP, [VP]),

@@ -94,6 +94,8 @@ struct bb_engine {
   virtual int eval_fetch(void*, int32_t*) = 0;
   virtual int eval_submit(const float*, const float*) = 0;
   virtual int selfplay(int, double, const double*) = 0;
+  virtual int selfplay_games(int, int, double, const double*) = 0;
+  virtual int records_rows() = 0;
   virtual int step(int, int, double, const double*) = 0;
   virtual int stream_moves(long long, int, double, const double*) = 0;
   virtual void* stream_handle() = 0;
@@ -116,6 +118,8 @@ struct EngineT : bb_engine {
   cudaStream_t stream = nullptr;    // lane 0's stream; whole-engine kernels and copies run here while the lanes idle
   std::vector<void*> allocs;
   double* uniforms_dev = nullptr;
+  unsigned* next_row_dev = nullptr;
+  size_t rec_cap_rows = 0, rows_last = 0;      // record / uniform rows allocated; rows of the last self-play call
   struct Snap { TickCtl ctl; unsigned long long moves; unsigned par; };
   // A lane is a contiguous range of game slots with its own stream, tick control block, evaluator
   // mailbox and counters.  Lanes tick independently, so one lane's advance kernel (a latency-bound
@@ -214,6 +218,10 @@ struct EngineT : bb_engine {
     A_(d.winners, n);
     A_(counters_dev, lanes.size());
     A_(uniforms_dev, n * c.max_plies);
+    A_(next_row_dev, 1);
+    rec_cap_rows = rows_last = n;
+    d.n_rows = 0;
+    d.next_row = next_row_dev;
     {
       size_t qn = 1;
       while (qn < n) qn <<= 1;
@@ -625,22 +633,64 @@ struct EngineT : bb_engine {
     return BB_OK;
   }
 
-  int selfplay(int play_limit, double temp, const double* u_host) override {
+  int selfplay(int play_limit, double temp, const double* u_host) override { return selfplay_games(d.n_games, play_limit, temp, u_host); }
+  // record and uniform buffers for `rows` games (they grow, never shrink; the old ones are freed with the engine)
+  int ensure_rows(size_t rows) {
+    if (rows <= rec_cap_rows) return BB_OK;
+    int rc = sync_lanes();
+    if (rc) return rc;
+    const size_t mp = d.max_plies;
+#define A_(p, cnt) if ((rc = alloc(&p, cnt)) != BB_OK) return rc
+    A_(d.rec_states, rows * (mp + 1));
+    A_(d.rec_off, rows * (mp + 2));
+    A_(d.pool_actions, rows * d.pool_cap);
+    A_(d.pool_plays, rows * d.pool_cap);
+    A_(d.chosen, rows * mp);
+    A_(d.n_moves, rows);
+    A_(d.winners, rows);
+    A_(uniforms_dev, rows * mp);
+#undef A_
+    BB_CUDA(cudaMemset(d.rec_off, 0, rows * (mp + 2) * sizeof(uint32_t)));
+    d.uniforms = uniforms_dev;
+    for (Lane& L : lanes) {
+      L.d.rec_states = d.rec_states; L.d.rec_off = d.rec_off; L.d.pool_actions = d.pool_actions; L.d.pool_plays = d.pool_plays;
+      L.d.chosen = d.chosen; L.d.n_moves = d.n_moves; L.d.winners = d.winners; L.d.uniforms = uniforms_dev;
+    }
+    rec_cap_rows = rows;
+    return BB_OK;
+  }
+  // n_rows whole games on the engine's n_games slots (n_rows >= n_games): a slot that ends a game takes the next
+  // unplayed row, so the GPU stays full until the last games run out.  Game r draws its moves from uniforms row r
+  // and its records land in row r, whichever slot plays it.
+  int selfplay_games(int n_rows, int play_limit, double temp, const double* u_host) override {
     if (temp != 1.0 && temp != 0.0) { set_error("bb_selfplay_run supports temp 1 and 0 on the device; got %g", temp); return BB_EINVAL; }
     if (cfg.evaluator == BB_EVAL_EXTERNAL) { set_error("bb_selfplay_run needs a device evaluator"); return BB_EINVAL; }
+    if (n_rows < d.n_games) { set_error("bb_selfplay_games: n_rows %d < n_games %d (create a smaller engine)", n_rows, d.n_games); return BB_EINVAL; }
     BB_CUDA(cudaSetDevice(cfg.device));
-    if (temp == 1.0) {
-      if (!u_host) { set_error("temp 1 needs uniforms[n_games][max_plies]"); return BB_EINVAL; }
-      BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)d.n_games * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
-    }
-    int rc = reset(nullptr);
+    int rc = ensure_rows((size_t)n_rows);
     if (rc) return rc;
+    if (temp == 1.0) {
+      if (!u_host) { set_error("temp 1 needs uniforms[n_rows][max_plies]"); return BB_EINVAL; }
+      BB_CUDA(cudaMemcpyAsync(uniforms_dev, u_host, (size_t)n_rows * d.max_plies * 8, cudaMemcpyHostToDevice, stream));
+    }
+    rc = reset(nullptr);
+    if (rc) return rc;
+    const int multi = n_rows > d.n_games ? n_rows : 0;
+    const unsigned first_free = (unsigned)d.n_games;
+    BB_CUDA(cudaMemcpyAsync(next_row_dev, &first_free, sizeof first_free, cudaMemcpyHostToDevice, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    d.n_rows = multi;
+    for (Lane& L : lanes) L.d.n_rows = multi;
     set_mode(1, 0, play_limit, temp == 1.0 ? 1 : 0);
     rc = begin_move(play_limit);
     if (!rc) rc = run(nullptr);
     set_mode(0, 0, play_limit, 0);
+    d.n_rows = 0;
+    for (Lane& L : lanes) L.d.n_rows = 0;
+    rows_last = (size_t)n_rows;
     return rc;
   }
+  int records_rows() override { return (int)rows_last; }
   // steady-state stepping: every slot plays n_moves moves (finished games restart in place)
   int step(int n_moves, int play_limit, double temp, const double* u_host) override {
     if (temp != 1.0 && temp != 0.0) { set_error("bb_selfplay_step supports temp 1 and 0; got %g", temp); return BB_EINVAL; }
@@ -679,7 +729,7 @@ struct EngineT : bb_engine {
   void* stream_handle() override { return (void*)stream; }
   int pool_cap() override { return (int)d.pool_cap; }
   int records_export(int32_t* nm, int32_t* win, void* st, uint32_t* off, uint16_t* pa, uint32_t* pp, uint16_t* ch) override {
-    const size_t n = d.n_games, mp = d.max_plies;
+    const size_t n = rows_last, mp = d.max_plies;
     D2H(nm, d.n_moves, n * 4); D2H(win, d.winners, n * 4); D2H(st, d.rec_states, n * (mp + 1) * sizeof(State));
     D2H(off, d.rec_off, n * (mp + 2) * 4); D2H(pa, d.pool_actions, n * d.pool_cap * 2);
     D2H(pp, d.pool_plays, n * d.pool_cap * 4); D2H(ch, d.chosen, n * mp * 2);
@@ -776,6 +826,8 @@ int bb_eval_pending(bb_engine* e, int32_t* n, const int32_t** slots, const void*
 int bb_eval_fetch(bb_engine* e, void* st, int32_t* slots) { BB_NEED(e); return e->eval_fetch(st, slots); }
 int bb_eval_submit(bb_engine* e, const float* pol, const float* val) { BB_NEED(e); return e->eval_submit(pol, val); }
 int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* u) { BB_NEED(e); return e->selfplay(play_limit, temp, u); }
+int bb_selfplay_games(bb_engine* e, int n_rows, int play_limit, double temp, const double* u) { BB_NEED(e); return e->selfplay_games(n_rows, play_limit, temp, u); }
+int bb_records_rows(bb_engine* e) { BB_NEED(e); return e->records_rows(); }
 int bb_selfplay_step(bb_engine* e, int n_moves, int play_limit, double temp, const double* u) {
   BB_NEED(e);
   return e->step(n_moves, play_limit, temp, u);

@@ -81,9 +81,10 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, Node* nodes,
   const int lane = lane_id();
   const NodeHdr rh = nodes[s.root].h;
   const int k = meta_nchild(rh.meta);
-  const size_t rbase = (size_t)g * (E.max_plies + 1);
-  const size_t obase = (size_t)g * (E.max_plies + 2);
-  const size_t pbase = (size_t)g * E.pool_cap;
+  const size_t row = E.n_rows ? (size_t)s.row : (size_t)g;   // records belong to the game, not to the slot that plays it
+  const size_t rbase = row * (E.max_plies + 1);
+  const size_t obase = row * (E.max_plies + 2);
+  const size_t pbase = row * E.pool_cap;
   if (E.rec_states) {
     if (s.pool_used + (uint32_t)k > E.pool_cap) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; return; }
     for (int j = lane; j < k; j += 32) {
@@ -100,7 +101,7 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, Node* nodes,
   }
   const uint32_t child = rh.child_base + (uint32_t)child_j;
   const int action = meta_action(nodes[child].h.meta);
-  if (E.chosen && lane == 0) E.chosen[(size_t)g * E.max_plies + s.ply] = (uint16_t)action;
+  if (E.chosen && lane == 0) E.chosen[row * E.max_plies + s.ply] = (uint16_t)action;
   s.root_parent_player = G::player(s.root_state);
   G::apply(s.root_state, action);
   s.ply += 1;
@@ -111,8 +112,8 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, Node* nodes,
         E.rec_states[rbase + s.ply] = s.root_state;          // terminal record, zero policy (:256-258)
         E.rec_off[obase + s.ply + 1] = s.pool_used;
       }
-      if (E.n_moves) E.n_moves[g] = s.ply;
-      if (E.winners) E.winners[g] = w;
+      if (E.n_moves) E.n_moves[row] = s.ply;
+      if (E.winners) E.winners[row] = w;
       *games_done += 1;
     }
     s.root = child;
@@ -259,7 +260,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
           BB_ASSERT(rh.child_base + (uint32_t)k <= s.n_nodes && s.ply < E.max_plies);
           int j;
           if (E.temp_mode == 1) {
-            const int row = (int)(((unsigned)g + s.game_no) % (unsigned)E.n_total);   // refill: next game, next row
+            const int row = E.n_rows ? (int)s.row : (int)(((unsigned)g + s.game_no) % (unsigned)E.n_total);   // refill: next game, next row
             j = sample_child(nodes + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
           } else {
             double u;
@@ -269,7 +270,18 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
           play_move(E, s, g, nodes, j, &n_done);
           n_moves += 1;
           if (s.moves_budget > 0) s.moves_budget -= 1;
-          if (s.phase == BB_PH_GAME_OVER && E.refill) {         // Model.Game(); DropRoot() for the next game
+          bool again = s.phase == BB_PH_GAME_OVER && E.refill;
+          if (s.phase == BB_PH_GAME_OVER && E.n_rows) {         // whole-game mode with more games than slots: take the next unplayed row
+            unsigned r = 0;
+            if (lane == 0) r = atomicAdd(E.next_row, 1u);
+            r = __shfl_sync(0xFFFFFFFFu, r, 0);
+            again = r < (unsigned)E.n_rows;
+            if (again) {
+              s.row = r;
+              if (lane == 0) E.rec_off[(size_t)r * (E.max_plies + 2)] = 0;
+            }
+          }
+          if (again) {                                          // Model.Game(); DropRoot() for the next game
             s.game_no += 1;
             s.root_state = G::initial();
             s.root = NONE;
@@ -459,6 +471,7 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.game_no = 0;
   s.half = 0;
   s.cp_head = s.cp_n = s.cp_src = 0;
+  s.row = (uint32_t)g;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;
   if (E.winners) E.winners[g] = WIN_NONE;

@@ -67,6 +67,7 @@ struct Slot {
   uint32_t half;                  // which half-arena is live
   uint32_t cp_head, cp_n;         // subtree copy in progress: next node to scan, nodes written
   uint32_t cp_src;                // old id of the new root
+  uint32_t row;                   // record / uniform row of the game this slot is playing (= slot id unless n_rows > n_games)
 };
 
 // numpy pairwise-sum plan for a dense vector of length A, built on the host.
@@ -121,6 +122,8 @@ struct EngineDev {                // passed to kernels by value
   // self-play
   int autoplay;                   // 1: choose / move root / end games on the device
   int refill;                     // 1: a finished game's slot starts the next game (steady-state stepping)
+  int n_rows;                     // > 0: bb_selfplay_games -- n_rows whole games on n_total slots; a slot that ends a game takes the
+  unsigned* next_row;             //      next unplayed row from this counter (records and uniforms are indexed by row)
   int play_limit;
   int temp_mode;                  // 1: temp == 1 (sample), 0: temp == 0 (PUCT argmax)
   const double* uniforms;         // [n_games][max_plies]

@@ -269,13 +269,27 @@ class Engine(object):
         check(lib.bb_eval_submit(self._h, _ptr(policy), _ptr(value)))
 
     # -- whole self-play ------------------------------------------------------------------------
-    def selfplay(self, play_limit, temp=1.0, uniforms=None):
+    def selfplay(self, play_limit, temp=1.0, uniforms=None, n_rows=None):
+        """Whole games to completion.  With n_rows (or a uniforms table of more than n_games rows) the engine plays
+        n_rows games on its n_games slots: a slot that ends a game starts the next unplayed one (bb_selfplay_games)."""
         u = None
+        rows = self.n_games if n_rows is None else int(n_rows)
         if uniforms is not None:
             u = np.ascontiguousarray(uniforms, dtype=np.float64)
-            assert u.shape == (self.n_games, self.max_plies), u.shape
-        check(lib.bb_selfplay_run(self._h, int(play_limit), float(temp), None if u is None else u.ctypes.data_as(C.c_void_p)))
+            if n_rows is None:
+                rows = u.shape[0]
+            assert u.shape == (rows, self.max_plies), u.shape
+        up = None if u is None else u.ctypes.data_as(C.c_void_p)
+        if rows == self.n_games:
+            check(lib.bb_selfplay_run(self._h, int(play_limit), float(temp), up))
+        else:
+            check(lib.bb_selfplay_games(self._h, rows, int(play_limit), float(temp), up))
         self.check_status()
+
+    @property
+    def rec_rows(self):
+        """Games covered by the record buffers (rows of the last selfplay call)."""
+        return int(lib.bb_records_rows(self._h))
 
     def step(self, n_moves, play_limit, temp=1.0, uniforms=None):
         """Steady-state stepping: every slot plays n_moves moves; finished games restart in place."""
@@ -308,7 +322,7 @@ class Engine(object):
         return dict(advance_ms=a.value, eval_ms=b.value, ticks=n.value)
 
     def records_raw(self):
-        n, mp, cap = self.n_games, self.max_plies, lib.bb_records_pool_cap(self._h)
+        n, mp, cap = self.rec_rows, self.max_plies, lib.bb_records_pool_cap(self._h)
         out = dict(n_moves=np.empty(n, np.int32), winner=np.empty(n, np.int32),
                    states=np.empty((n, mp + 1, self.state_bytes), np.uint8), rec_off=np.empty((n, mp + 2), np.uint32),
                    pool_actions=np.empty((n, cap), np.uint16), pool_plays=np.empty((n, cap), np.uint32),

@@ -40,7 +40,7 @@ def _records_device_views(eng):
     from ._lib import lib, check
     ptrs = [C.c_void_p() for _ in range(7)]
     check(lib.bb_records_device(eng._h, *[C.byref(p) for p in ptrs]))
-    n, mp, cap, sb = eng.n_games, eng.max_plies, lib.bb_records_pool_cap(eng._h), eng.state_bytes
+    n, mp, cap, sb = eng.rec_rows, eng.max_plies, lib.bb_records_pool_cap(eng._h), eng.state_bytes
     shapes = {'n_moves': ((n,), torch.int32), 'winner': ((n,), torch.int32), 'states': ((n, mp + 1, sb), torch.uint8),
               'rec_off': ((n, mp + 2), torch.int32), 'pool_actions': ((n, cap), torch.int16),
               'pool_plays': ((n, cap), torch.int32), 'chosen': ((n, mp), torch.int16)}

@@ -144,6 +144,12 @@ int bb_eval_submit(bb_engine* e, const float* policy_dev, const float* value_dev
  * choice at temp 1 from uniforms_host[n_games][max_plies] (one double per move, A.15), root
  * motion, Winner(None) after every move, records kept on the device. */
 int bb_selfplay_run(bb_engine* e, int play_limit, double temp, const double* uniforms_host);
+/* The same loop for nGames > slots (Blackbird.py:238 `for _ in range(nGames)`): n_rows >= n_games whole games on the
+ * engine's n_games slots; a slot that ends a game starts the next unplayed one, so the GPU stays full until the last
+ * games run out.  Game r draws its moves from uniforms_host[r][max_plies] and its records land in row r whichever
+ * slot played it; bb_records_export / bb_records_device then cover bb_records_rows() rows. */
+int bb_selfplay_games(bb_engine* e, int n_rows, int play_limit, double temp, const double* uniforms_host);
+int bb_records_rows(bb_engine* e);   /* rows of the last bb_selfplay_run / bb_selfplay_games call (n_games after create) */
 /* Steady-state stepping for throughput measurement and streaming generation: every slot plays
  * n_moves further moves (play_limit simulations each); a slot whose game ends starts the next
  * game in place (Blackbird.py:238-244 loop).  uniforms_host may be NULL to keep the table. */

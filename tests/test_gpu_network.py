@@ -147,6 +147,28 @@ def test_streaming_equals_tick_mode(mods, game, kind, P, G, monkeypatch):
     assert out['1'][0] == out['0'][0]
 
 
+def test_more_games_than_slots_streaming(mods):
+    """bb_selfplay_games through the persistent kernel pair: 40 games on 12 slots, every game equal to the oracle
+    replay of the same kernel's outputs."""
+    engine, records = mods
+    game, slots, rows, P = 'Connect4', 12, 40, 24
+    w = network_np.init_weights(3, 7, seed=2, jitter=0.1)
+    eng = engine.Engine(game, 'fixed', n_games=slots, evaluator='net', play_limit_hint=P)
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, precision='bf16')
+    assert eng.streaming
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(rows)])
+    eng.selfplay(P, 1.0, u)
+    got = records.build_records(eng)
+    assert len(got) == rows
+    replay = Replay(engine, eng, game)
+    for g in range(rows):
+        s = search_np.NetSearch(replay, 'fixed', maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        want, winner, _ = selfplay_np.play_game(s, GAMES[game], 1)
+        assert got[g][0] == want, g
+    eng.close()
+
+
 def test_full_size_streaming(mods):
     """BASELINE configs[1] at full size through the benchmarked path: 4096 Connect4 games, FixedMCTS, 800
     simulations per move, bf16 network, streaming mode.  Size-independent properties over all games (every game

@@ -104,6 +104,31 @@ def test_selfplay_vs_oracle(mods, game, kind, P, n_games):
     eng.close()
 
 
+@pytest.mark.parametrize('game,kind,P,slots,rows', [('Connect4', 'fixed', 30, 6, 20), ('TicTacToe', 'dynamic', 40, 8, 29),
+                                                   ('Connect4', 'dynamic', 50, 24, 24)])
+def test_more_games_than_slots(mods, game, kind, P, slots, rows):
+    """bb_selfplay_games: `rows` whole games on `slots` slots (a slot that ends a game starts the next unplayed
+    one).  Every game's records must equal the oracle's for that game, whichever slot played it."""
+    engine, records = mods
+    eng = engine.Engine(game, kind, n_games=slots, evaluator='kat', play_limit_hint=P)
+    u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(rows)])
+    eng.selfplay(P, 1.0, u)
+    assert eng.rec_rows == rows
+    got = records.build_records(eng)
+    assert len(got) == rows
+    for g in range(rows):
+        s = search_np.NetSearch(search_np.KatEvaluator(eng.A), kind, maxDepth=10, explorationRate=0.85, playLimit=P,
+                                rng=np.random.RandomState(1000 + g))
+        want, winner, trace = selfplay_np.play_game(s, GAMES[game], 1)
+        assert got[g][0] == want, (game, kind, g)
+        assert got[g][1] == int(winner)
+    assert eng.counters()['games_done'] == rows
+    # the engine is reusable afterwards, with fewer rows again
+    eng.selfplay(P, 1.0, u[:slots])
+    assert eng.rec_rows == slots and records.build_records(eng)[0][0] == got[0][0]
+    eng.close()
+
+
 def test_selfplay_record_goldens(mods, golden):
     """Records of whole games produced by the UNMODIFIED reference (GenerateTrainingSamples)."""
     engine, records = mods
