@@ -43,6 +43,7 @@ def parse():
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
     ap.add_argument('--lanes', type=int, default=0, help='engine lanes (0 = engine default)')
     ap.add_argument('--prelude', type=int, default=45, help='untimed move rounds at 32 sims/move that desynchronise the game slots')
+    ap.add_argument('--e2e-rounds', type=int, default=4, help='e2e plays this many times --games whole games per GPU on the --games slots')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
     return ap.parse_args()
@@ -307,7 +308,11 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e:
         barrier()
-        pinned = torch.from_numpy(uniforms).pin_memory()
+        rows = G * max(1, args.e2e_rounds)
+        # game id = rank * rows + row: one RandomState stream per global game, as in the timed loop
+        u_e2e = np.stack([np.random.RandomState(1000 + rank * rows + g).random_sample(eng.max_plies) for g in range(rows)])
+        pinned = torch.from_numpy(u_e2e).pin_memory()
+        barrier()
         t0 = time.perf_counter()
         eng.selfplay(P, 1.0, pinned.numpy())
         if world > 1:                                        # every rank ends up with every game's records
@@ -324,10 +329,10 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dist.all_reduce(ss, op=dist.ReduceOp.SUM)
         d2h = sum(v.nbytes for v in raw.values())
-        e2e = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'h2d_bytes_per_step': int(uniforms.nbytes),
+        e2e = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'h2d_bytes_per_step': int(u_e2e.nbytes),
                'd2h_bytes_per_step': int(d2h), 'games_per_sec': float(ss[1].item()) / float(tt.item()),
-               'seconds': float(tt.item()), 'what': 'bb_selfplay_run + %s: %d whole games/GPU to completion' % (
-                   'one NCCL all-gather of the record buffers + D2H' if world > 1 else 'bb_records_export', G),
+               'seconds': float(tt.item()), 'what': 'bb_selfplay_games + %s: %d whole games/GPU to completion on %d slots' % (
+                   'one NCCL all-gather of the record buffers + D2H' if world > 1 else 'bb_records_export', rows, G),
                'mean_moves_per_game': float(raw['n_moves'].mean())}
 
     cpu = None
