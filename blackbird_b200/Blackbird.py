@@ -106,15 +106,14 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
     try:
         if evaluator == 'net':
             model._load_network_into(eng, precision=precision, seed=random.getrandbits(48))
-        for lo in range(0, nGames, slots):
-            n = min(slots, nGames - lo)
-            u = np.ones((slots, eng.max_plies))
-            u[:n] = _uniform_table(n, eng.max_plies) if uniforms is None else np.asarray(uniforms)[lo:lo + n]
-            eng.selfplay(play_limit, float(temp), u)
-            games = _records.build_records(eng)[:n]
-            serialized = [rec for recs, _, _ in games for rec in recs]
-            model.Conn.PutGames(model.Name, model.Version, game, serialized)
-            written += len(serialized)
+        # one engine call for all nGames: the slots (as many as fit the memory budget) start the next unplayed game
+        # as soon as they end one (bb_selfplay_games), so the GPU stays full until the last games run out
+        u = _uniform_table(nGames, eng.max_plies) if uniforms is None else np.asarray(uniforms)[:nGames]
+        eng.selfplay(play_limit, float(temp), u)
+        games = _records.build_records(eng)
+        serialized = [rec for recs, _, _ in games for rec in recs]
+        model.Conn.PutGames(model.Name, model.Version, game, serialized)
+        written += len(serialized)
     finally:
         eng.close()
     return written

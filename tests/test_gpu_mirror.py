@@ -126,6 +126,29 @@ def test_generate_training_samples_records(bb, golden, tmp_path, monkeypatch):
     assert os.path.isfile(tmp_path / 'data' / 'blackbird.db')
 
 
+def test_generate_training_samples_more_games_than_slots(bb, tmp_path, monkeypatch):
+    """nGames larger than the slot count the memory budget allows: one engine call, slots restart with the next
+    unplayed game; the stored records are the same as with one slot per game."""
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    cls = type('KatModel', (B.FixedModel,), {'_SELFPLAY_EVALUATOR': 'kat'})
+    cfg = {'maxDepth': 10, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': 20,
+           'temperature': {'exploration': 1, 'exploitation': 0.1}}
+    net = {'blocks': 1, 'filters': 16, 'eval': {'dense': 16}, 'policy': {'dirichlet': {'alpha': 0.2, 'epsilon': 0.0}}}
+    u = np.random.RandomState(7).random_sample((11, 42))
+    out = []
+    for tag, slots in (('wide', None), ('narrow', 3)):
+        if slots:
+            monkeypatch.setattr(B, '_batch_slots', lambda *a, **k: slots)
+        m = cls(bb['games']['Connect4'], 'rows_' + tag, cfg, net, {})
+        n = B.GenerateTrainingSamples(m, 11, 1, uniforms=u)
+        got = [bytes(r) for r in m.Conn.GetGames(m.Name, m.Version)]
+        assert n == len(got)
+        out.append(got)
+        m.Conn.Close()
+    assert out[0] == out[1]
+
+
 def test_model_network_selfplay_and_arena(bb, tmp_path, monkeypatch):
     """main.py's sequence with the template config on TicTacToe (BASELINE configs[0]): Model(...),
     GenerateTrainingSamples with the built-in network, then a TestPrevious-style arena game."""
