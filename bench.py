@@ -315,9 +315,13 @@ def run_ours(args):
         barrier()
         t0 = time.perf_counter()
         eng.selfplay(P, 1.0, pinned.numpy())
-        if world > 1:                                        # every rank ends up with every game's records
+        if world > 1:                                        # every rank ends up with every game's records on its GPU;
             from blackbird_b200.parallel import allgather_raw, _records_device_views
-            raw = allgather_raw(_records_device_views(eng))
+            if rank == 0:                                    # the trainer rank reads all of them, the others their own shard
+                raw = allgather_raw(_records_device_views(eng))
+            else:
+                allgather_raw(_records_device_views(eng), to_host=False)
+                raw = eng.records_raw()
         else:
             raw = eng.records_raw()
         torch.cuda.synchronize()
@@ -328,12 +332,12 @@ def run_ours(args):
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dist.all_reduce(ss, op=dist.ReduceOp.SUM)
-        d2h = sum(v.nbytes for v in raw.values())
+        d2h = sum(v.nbytes for v in raw.values())            # rank 0's bytes (the largest)
         e2e = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'h2d_bytes_per_step': int(u_e2e.nbytes),
                'd2h_bytes_per_step': int(d2h), 'games_per_sec': float(ss[1].item()) / float(tt.item()),
                'seconds': float(tt.item()), 'what': 'bb_selfplay_games + %s: %d whole games/GPU to completion on %d slots' % (
                    'one NCCL all-gather of the record buffers + D2H' if world > 1 else 'bb_records_export', rows, G),
-               'mean_moves_per_game': float(raw['n_moves'].mean())}
+               'mean_moves_per_game': float(raw['n_moves'].mean()) if rank == 0 else None}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

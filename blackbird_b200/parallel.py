@@ -65,13 +65,14 @@ def _from_ptr(ptr, shape, dtype, device):
 _NP_VIEW = {'rec_off': np.uint32, 'pool_actions': np.uint16, 'pool_plays': np.uint32, 'chosen': np.uint16}
 
 
-def allgather_raw(raw, group=None):
+def allgather_raw(raw, group=None, to_host=True):
     """raw: dict of per-rank buffers (torch tensors on this rank's device, or numpy arrays for the
     gloo/CPU tests), identical shapes on every rank.  Returns numpy arrays with a leading
     concatenation over ranks in rank order (= global game order for contiguous shards).
 
     One flat byte buffer per rank and ONE all_gather: the records are small (C4: ~0.9 KB per game),
-    so the collective is latency-bound and a single launch is what matters."""
+    so the collective is latency-bound and a single launch is what matters.
+    to_host=False returns the gathered [world, bytes] uint8 tensor without the device-to-host copy."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     tensors = {k: (torch.as_tensor(raw[k]) if not torch.is_tensor(raw[k]) else raw[k]) for k in RAW_KEYS}
     parts = [tensors[k].contiguous().view(-1).view(torch.uint8) for k in RAW_KEYS]
@@ -82,6 +83,8 @@ def allgather_raw(raw, group=None):
         gathered = gathered.view(world, flat.numel())
     else:
         gathered = flat[None]
+    if not to_host:                      # ranks that do not train keep the gathered buffer on the GPU
+        return gathered
     host = gathered.cpu().numpy()
     out, off = {}, 0
     for k, p in zip(RAW_KEYS, parts):
