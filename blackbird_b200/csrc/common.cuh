@@ -50,6 +50,9 @@ struct StreamCtl {
   unsigned long long cyc_claim, cyc_tower, cyc_heads;   // SM cycles the network CTAs spent waiting for work / in the tower / in the heads (measurement)
   unsigned long long cyc_search_busy, cyc_search_total; // search warps: cycles inside advance_slot / resident (measurement)
   unsigned long long search_calls;                      // advance_slot calls (measurement)
+#ifdef BB_SEARCH_TIMING
+  unsigned long long sdbg[12];
+#endif
 };
 
 // Built-in network (net.cu)

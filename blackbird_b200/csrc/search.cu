@@ -512,6 +512,14 @@ struct EngineT : bb_engine {
       fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles; search warps busy %.3f, %.0f cycles per advance call\n", h.batches,
               (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches,
               (double)h.cyc_search_busy / (double)(h.cyc_search_total ? h.cyc_search_total : 1), (double)h.cyc_search_busy / (double)(h.search_calls ? h.search_calls : 1));
+#ifdef BB_SEARCH_TIMING
+    if (getenv("BB_DEBUG_STREAM") && h.search_calls) {
+      const char* nm[6] = {"load", "post_request", "expand", "select level", "backup", "other"};
+      for (int i = 0; i < 6; ++i)
+        fprintf(stderr, "[bbengine] advance_slot %-13s %8.0f cycles per call (%.2f per call, %.0f cycles each)\n", nm[i], (double)h.sdbg[i] / h.search_calls,
+                (double)h.sdbg[6 + i] / h.search_calls, h.sdbg[6 + i] ? (double)h.sdbg[i] / h.sdbg[6 + i] : 0.0);
+    }
+#endif
     if (h.stop == 2u) { set_error("streaming watchdog fired: a search warp or the network kernel waited for seconds (see stderr)"); return BB_ESTATE; }
     return BB_OK;
   }

@@ -155,9 +155,21 @@ constexpr int STREAM_WARPS_PER_CTA = BB_STREAM_WARPS;
 #define BB_ADV_MIN_CTAS 1
 #endif
 
+#ifdef BB_SEARCH_TIMING
+#define ST_T0() long long st_t = clock64()
+#define ST_ADD(i) do { const long long st_n = clock64(); st_acc[i] += st_n - st_t; st_cnt[i] += 1; st_t = st_n; } while (0)
+#else
+#define ST_T0()
+#define ST_ADD(i)
+#endif
 template <class G>
 __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws, uint32_t* ticket = nullptr) {
   const int lane = lane_id();
+#ifdef BB_SEARCH_TIMING
+  long long st_acc[6] = {0, 0, 0, 0, 0, 0};
+  int st_cnt[6] = {0, 0, 0, 0, 0, 0};
+#endif
+  ST_T0();
   Slot<G> s = E.slots[g];
   if (!phase_busy(s.phase)) return s.phase;
 #ifdef BB_ADV_TIMING
@@ -188,6 +200,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
   }
 
   int budget = E.step_budget;
+  ST_ADD(0);                                                  // slot, path, header, answer loads
   for (;;) {
 #ifdef BB_ADV_TIMING
     dbg_iters++;
@@ -207,14 +220,18 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }     // FixedMCTS.py:23
       if (ch.child_base == NONE) {                              // Children is None
         if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
+        ST_ADD(5);
         post_request(E, s, g, par);                             // GetPriors(state) of this node
+        ST_ADD(1);
         n_evals += 1;
         s.phase = BB_PH_WAIT_EXPAND;
         break;
       }
       step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
+      ST_ADD(5);
       const int k = expand_node(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws);
+      ST_ADD(2);
       if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
       n_exp += 1;
       n_nodes += k;
@@ -222,6 +239,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
     } else if (step == ST_SELECT) {
       double u;
       NodeHdr chosen = ch;
+      ST_ADD(5);
 #ifdef BB_DEBUG
       if (ch.child_base + (uint32_t)meta_nchild(ch.meta) > s.n_nodes && lane == 0)
         printf("DBG g=%d cur=%u depth=%d cb=%u nch=%d meta=%x n_nodes=%u ply=%d half=%u root=%u rp=%u cp_n=%u cp_head=%u\n", g, s.cur, s.depth,
@@ -241,14 +259,19 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       n_sel += 1;
       budget -= 1;
       step = ST_TOP;
+      ST_ADD(3);
     } else {                                                    // ST_LEAF: SampleValue + _backProp
       if (!(ch.meta & META_HAS_VALUE)) {
+        ST_ADD(5);
         post_request(E, s, g, par);                             // getEvaluation(state) of the leaf
+        ST_ADD(1);
         n_evals += 1;
         s.phase = BB_PH_WAIT_LEAF;
         break;
       }
+      ST_ADD(5);
       backup(s, nodes, path, ch.eval);
+      ST_ADD(4);
       s.root_plays += 1;
       n_sims += 1;
       if (s.root_plays >= s.end_plays) {                        // MCTS.py:298-299
@@ -315,6 +338,10 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
   }
 #endif
   if (ticket) *ticket = s.req_idx;
+#ifdef BB_SEARCH_TIMING
+  ST_ADD(5);
+  if (lane == 0 && E.q) for (int i = 0; i < 6; ++i) { atomicAdd(&E.q->sdbg[i], (unsigned long long)st_acc[i]); atomicAdd(&E.q->sdbg[6 + i], (unsigned long long)st_cnt[i]); }
+#endif
   if (lane == 0) {
     E.slots[g] = s;
     if (!E.q && phase_busy(s.phase)) atomicAdd(&E.ctl->active[par], 1);
