@@ -35,9 +35,16 @@ int launch_kat(int game, const void* states, int n, const int* count_dev, float*
 // Streaming (asynchronous) mode: a persistent search kernel and a persistent network kernel run side by
 // side and talk through a request ring in global memory, so a slot that blocks on the evaluator gets its
 // answer one network batch later instead of one whole tick later (DESIGN.md "streaming engine").
-// Ticket i lives in ring entry i & mask; entry_seq[e] == i + 1 publishes the request, resp_seq[slot] == i + 1
-// publishes the answer.  Every slot has at most one open request, so a ring of >= n_games entries never wraps
-// onto a live entry.
+// Ticket i lives in ring entry i & mask: one 64-bit word, low half = i, high half = slot | RING_PUBLISHED, written
+// with one store once the slot's state is in q_state[slot]; resp_seq[slot] == i + 1 publishes the answer.  The
+// network pipeline that serves ticket i clears the PUBLISHED bit as soon as it has read the entry, and a search warp
+// publishes ticket i + ring only after it has seen that bit clear: open tickets need not be contiguous (a pipeline
+// can sit on ticket i for a whole batch while the other slots issue ring-many newer ones), so without that
+// hand-back a late ticket's entry is overwritten and its slot waits for ever (seen with 64 slots on a 64-entry
+// ring).  The ring is also much larger than the slot count (>= 8192 entries), so the wait is never taken in
+// practice.  The state itself lives per slot, where nothing can overwrite it while the request is open.
+constexpr unsigned RING_PUBLISHED = 0x80000000u;
+constexpr unsigned RING_MIN_ENTRIES = 8192u;
 struct StreamCtl {
   unsigned tail;                  // tickets handed out to the search warps
   unsigned head;                  // tickets claimed by the network CTAs
@@ -59,9 +66,8 @@ struct StreamCtl {
 struct NetDev;
 struct NetServe {                 // the request ring as the persistent network kernel sees it
   StreamCtl* q;
-  unsigned* q_seq;
-  const int* q_slot;
-  const void* q_state;
+  unsigned long long* q_ent;      // ticket ring (see StreamCtl)
+  const void* q_state;            // [n_games] request states, by slot
   unsigned* resp_seq;
   unsigned q_mask;
 };

@@ -453,11 +453,15 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       if (tid < cnt) {
         const State* src;
         if (serve) {
-          const unsigned tk = ticket0 + (unsigned)tid, e = tk & sv.q_mask;
-          for (unsigned spin = 0; *reinterpret_cast<volatile unsigned*>(&sv.q_seq[e]) != tk + 1u && spin < (64u << 20); ++spin) {}
-          __threadfence();
-          src = reinterpret_cast<const State*>(sv.q_state) + e;
-          sIdx[tid] = __ldcg(sv.q_slot + e);                // where the answer goes
+          const unsigned tk = ticket0 + (unsigned)tid;
+          volatile unsigned long long* ent = reinterpret_cast<volatile unsigned long long*>(&sv.q_ent[tk & sv.q_mask]);
+          unsigned long long v = *ent;
+          for (unsigned spin = 0; !((unsigned)v == tk && ((unsigned)(v >> 32) & RING_PUBLISHED)) && spin < (64u << 20); ++spin) v = *ent;
+          const int slot = (int)((unsigned)(v >> 32) & ~RING_PUBLISHED);
+          *ent = v & 0x7FFFFFFFFFFFFFFFull;                  // entry read: ticket tk + ring may publish here
+          __threadfence();                                   // acquire: the slot's state was written before the entry
+          src = reinterpret_cast<const State*>(sv.q_state) + slot;
+          sIdx[tid] = slot;                                  // where the answer goes
         } else {
           src = states + base + tid;
         }

@@ -223,16 +223,15 @@ struct EngineT : bb_engine {
     d.n_rows = 0;
     d.next_row = next_row_dev;
     {
-      size_t qn = 1;
-      while (qn < n) qn <<= 1;
+      size_t qn = RING_MIN_ENTRIES;                                // power of two, >= 4 tickets per slot (see StreamCtl)
+      while (qn < 4 * n) qn <<= 1;
       d.q_mask = (unsigned)(qn - 1);
       A_(q_dev, 1);
-      A_(d.q_seq, qn);
-      A_(d.q_slot, qn);
-      A_(d.q_state, qn);
+      A_(d.q_ent, qn);
+      A_(d.q_state, n);
       A_(d.resp_seq, n);
       BB_CUDA(cudaMemset(q_dev, 0, sizeof(StreamCtl)));
-      BB_CUDA(cudaMemset(d.q_seq, 0, qn * sizeof(unsigned)));
+      BB_CUDA(cudaMemset(d.q_ent, 0, qn * sizeof(unsigned long long)));
       BB_CUDA(cudaMemset(d.resp_seq, 0, n * sizeof(unsigned)));
       d.q = nullptr;                                               // set only in the copy handed to the streaming kernels
       BB_CUDA(cudaStreamCreateWithFlags(&net_stream, cudaStreamNonBlocking));
@@ -308,7 +307,7 @@ struct EngineT : bb_engine {
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaMemsetAsync(ctl_dev, 0, lanes.size() * sizeof(TickCtl), stream));
     BB_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(StreamCtl), stream));
-    BB_CUDA(cudaMemsetAsync(d.q_seq, 0, ((size_t)d.q_mask + 1) * sizeof(unsigned), stream));
+    BB_CUDA(cudaMemsetAsync(d.q_ent, 0, ((size_t)d.q_mask + 1) * sizeof(unsigned long long), stream));
     BB_CUDA(cudaMemsetAsync(d.resp_seq, 0, (size_t)d.n_games * sizeof(unsigned), stream));
     for (Lane& L : lanes) L.par = 0;
     BB_CUDA(cudaStreamSynchronize(stream));
@@ -488,7 +487,7 @@ struct EngineT : bb_engine {
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));
-    NetServe sv{q_dev, d.q_seq, d.q_slot, d.q_state, d.resp_seq, d.q_mask};
+    NetServe sv{q_dev, d.q_ent, d.q_state, d.resp_seq, d.q_mask};
     // the network kernel goes first so that its CTAs are resident before the search CTAs spin on it
     BB_CUDA(cudaEventRecord(st_ev[2], net_stream));
     if ((rc = net_serve(net, sv, d.resp_policy, d.resp_value, net_stream))) return rc;

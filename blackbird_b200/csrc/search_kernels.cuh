@@ -14,14 +14,15 @@ __device__ __forceinline__ bool phase_busy(int ph) {
 template <class G>
 __device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, int g, unsigned parity) {
   int idx = 0;
-  if (E.q) {                                                  // streaming mode: take a ticket, fill the ring entry, publish it
+  if (E.q) {                                                  // streaming mode: park the state, take a ticket, publish its ring entry
     if (lane_id() == 0) {
+      E.q_state[g] = s.cur_state;
       idx = (int)atomicAdd(&E.q->tail, 1u);
-      const unsigned e = (unsigned)idx & E.q_mask;
-      E.q_slot[e] = g;
-      E.q_state[e] = s.cur_state;
-      __threadfence();
-      *reinterpret_cast<volatile unsigned*>(&E.q_seq[e]) = (unsigned)idx + 1u;
+      volatile unsigned long long* ent = reinterpret_cast<volatile unsigned long long*>(&E.q_ent[(unsigned)idx & E.q_mask]);
+      unsigned long long was = *ent;                          // the entry's previous ticket (idx - ring) must have been read by its pipeline
+      __threadfence();                                        // state before entry
+      while ((unsigned)(was >> 32) & RING_PUBLISHED) { __nanosleep(100); was = *ent; }
+      *ent = ((unsigned long long)((unsigned)g | RING_PUBLISHED) << 32) | (unsigned)idx;
     }
     s.req_idx = (uint32_t)__shfl_sync(0xFFFFFFFFu, idx, 0);
     return;

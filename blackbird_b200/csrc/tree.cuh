@@ -112,11 +112,10 @@ struct EngineDev {                // passed to kernels by value
   typename G::State* req_state;
   float* resp_policy;             // [n_games][A], indexed by request (tick mode) or by slot (streaming mode)
   float* resp_value;
-  // streaming mode (q != nullptr): request ring + per-slot answer sequence numbers
+  // streaming mode (q != nullptr): ticket ring + per-slot request states + per-slot answer sequence numbers
   StreamCtl* q;
-  unsigned* q_seq;                // [q_mask + 1]
-  int* q_slot;                    // [q_mask + 1]
-  typename G::State* q_state;     // [q_mask + 1]
+  unsigned long long* q_ent;      // [q_mask + 1] ring entry of ticket t (entry t & q_mask): low word t, high word slot | RING_PUBLISHED
+  typename G::State* q_state;     // [n_games] the state a slot asks about (a slot has one open request at a time)
   unsigned* resp_seq;             // [n_games]
   unsigned q_mask;
   // self-play

@@ -147,6 +147,31 @@ def test_streaming_equals_tick_mode(mods, game, kind, P, G, monkeypatch):
     assert out['1'][0] == out['0'][0]
 
 
+@pytest.mark.parametrize('game,kind,P,slots,rows', [('TicTacToe', 'fixed', 10, 64, 4096), ('TicTacToe', 'dynamic', 24, 33, 1500),
+                                                   ('Connect4', 'dynamic', 32, 64, 1024)])
+def test_few_slots_many_tickets_streaming(mods, game, kind, P, slots, rows, monkeypatch):
+    """Ring hand-back regression: with a few dozen slots the open tickets are not contiguous (a pipeline serves a
+    late ticket while the other slots have issued a ring's worth of newer ones).  Thousands of games on few slots
+    must end (no watchdog), every engine run must give the same records, and they must equal tick mode's."""
+    engine, records = mods
+    from blackbird_b200 import netinit
+    w = netinit.random_weights(engine.plane_shape(game)[2], engine.n_actions(game), seed=3)
+    u = np.stack([np.random.RandomState(3000 + g).random_sample(engine._DEFAULT_PLIES[game]) for g in range(rows)])
+    got = []
+    for mode, repeats in (('1', 3), ('0', 1)):
+        monkeypatch.setenv('BB_STREAM', mode)
+        eng = engine.Engine(game, kind, n_games=slots, evaluator='net', play_limit_hint=P)
+        eng.load_network(w, 4, 16, 16, precision='bf16')
+        assert eng.streaming == (mode == '1')
+        for _ in range(repeats):
+            eng.selfplay(P, 1.0, u, n_rows=rows)
+            r = eng.records_raw()
+            played = np.arange(r['chosen'].shape[1])[None, :] < r['n_moves'][:, None]
+            got.append((r['n_moves'].tobytes(), r['winner'].tobytes(), np.where(played, r['chosen'], 0).tobytes()))
+        eng.close()
+    assert all(g == got[0] for g in got[1:])
+
+
 def test_more_games_than_slots_streaming(mods):
     """bb_selfplay_games through the persistent kernel pair: 40 games on 12 slots, every game equal to the oracle
     replay of the same kernel's outputs."""
