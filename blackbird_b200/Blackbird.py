@@ -21,6 +21,7 @@ from .DynamicMCTS import DynamicMCTS as MCTS
 from .FixedMCTS import FixedMCTS
 from .Network import Network
 from .NetworkFactory import NetworkFactory
+from .RandomMCTS import RandomMCTS
 
 np.seterr(divide='ignore', invalid='ignore')          # Blackbird.py:17
 
@@ -161,7 +162,14 @@ def TestPrevious(model, temp, numTests):
 
 
 def TestRandom(model, temp, numTests):
-    raise NotImplementedError('RandomMCTS opponent (Blackbird.py:84-112, RandomMCTS.py) is SURVEY.md 8f-2 ("next")')
+    """Blackbird.py:84-112: numTests arena games against RandomMCTS, one statistics row per game."""
+    resultMap = {1: 'wins', 0: 'draws', -1: 'losses'}
+    stats = defaultdict(int)
+    for _ in range(numTests):
+        result = TestModels(model, RandomMCTS(), temp, numTests=1)
+        stats[resultMap.get(result, 'indeterminant')] += 1
+        model.Conn.PutTrainingStatistic(result, model.Name, model.Version, 'RANDOM')
+    return stats
 
 
 def TestGood(model, temp, numTests):

@@ -259,6 +259,31 @@ def record_games():
     return out
 
 
+# --- 5. arena games against RandomMCTS through the unmodified Blackbird.TestRandom (8f-2) ----
+def arena_games():
+    import random
+    out = []
+    cases = [('TicTacToe', 'dynamic', 30, 0.1, 4, 0), ('TicTacToe', 'fixed', 12, 0.1, 3, 1),
+             ('Connect4', 'dynamic', 40, 0.1, 3, 2), ('Connect4', 'fixed', 20, 1, 2, 3)]
+    for game, kind, P, temp, n, seed in cases:
+        m = make_model(game, kind, P)
+        stats_rows, boards = [], []
+        m.Conn.PutTrainingStatistic = lambda *a: stats_rows.append(list(a))
+        move_root = m.MoveRoot
+
+        def logged(state, _mr=move_root):
+            boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                         + bytes([int(state.Player)])).hexdigest()[:12])
+            return _mr(state)
+        m.MoveRoot = logged
+        random.seed(seed)
+        np.random.seed(seed)
+        stats = Blackbird.TestRandom(m, temp, n)
+        out.append({'game': game, 'kind': kind, 'playLimit': P, 'temp': temp, 'numTests': n, 'seed': seed,
+                    'stats': dict(stats), 'rows': stats_rows, 'boards': boards})
+    return out
+
+
 def main():
     def dump(name, obj):
         with open(os.path.join(HERE, name), 'w') as f:
@@ -270,6 +295,7 @@ def main():
     dump('dragon_positions.json', dragon_positions())
     dump('mcts_kat.json', mcts_kats())
     dump('records.json', record_games())
+    dump('arena.json', arena_games())
 
 
 if __name__ == '__main__':

@@ -177,3 +177,38 @@ def test_model_network_selfplay_and_arena(bb, tmp_path, monkeypatch):
     res = B.TestModels(model, model.LastVersion(), 0.1, 1)
     assert res in (1, 0, -1)
     model.Conn.Close()
+
+
+@pytest.mark.parametrize('index', [0, 1, 2, 3])
+def test_random_arena_vs_reference(bb, golden, index):
+    """Blackbird.TestRandom (Blackbird.py:84-112) against the RandomMCTS mirror: with random.seed / np.random.seed
+    as in tests/golden/make_golden.py:arena_games the games replay position for position (every state both
+    players' MoveRoot saw), and the statistics rows and the win/draw/loss tally match the unmodified reference."""
+    import random
+    case = golden('arena.json')[index]
+    B = bb['Blackbird']
+    base = bb['DynamicMCTS'] if case['kind'] == 'dynamic' else bb['FixedMCTS']
+    cls = type('KatSearch', (base, KatNet), {})
+    m = cls(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=case['playLimit'])
+    m.Game = bb['games'][case['game']]
+    m._nActions = m.Game.LegalMoves
+    m.Name, m.Version = 'gold', 1
+    rows, boards = [], []
+
+    class Conn(object):
+        def PutTrainingStatistic(self, *a):
+            rows.append(list(a))
+    m.Conn = Conn()
+    move_root = m.MoveRoot
+
+    def logged(state):
+        boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                     + bytes([int(state.Player)])).hexdigest()[:12])
+        return move_root(state)
+    m.MoveRoot = logged
+    random.seed(case['seed'])
+    np.random.seed(case['seed'])
+    stats = B.TestRandom(m, case['temp'], case['numTests'])
+    assert boards == case['boards'], (case['game'], case['kind'])
+    assert rows == case['rows']
+    assert dict(stats) == case['stats']
