@@ -124,7 +124,11 @@ def default_node_cap(game, search, play_limit, max_depth=10):
     Appendix E).  Overflow is reported (BB_ENOMEM), never silent."""
     a = min(_ACTIONS[game], 48)
     per_sim = a * ((min(max_depth, 10) if play_limit <= 64 else 4) if search == 'fixed' else 1)
-    return int(min(1 << 22, max(1024, 2.5 * play_limit * per_sim + 64)))
+    # dynamic trees are narrow and deep: when one child keeps most of the visits move after move the carried
+    # subtree approaches growth / (1 - kept fraction); 6 moves' worth of growth covers a kept fraction of 0.8
+    # (2.5 overflowed in 1 of 131072 Connect4 games at 800 simulations per move, profiles/r01e_summary.md)
+    moves_worth = 2.5 if search == 'fixed' else 6.0
+    return int(min(1 << 22, max(1024, moves_worth * play_limit * per_sim + 64)))
 
 
 _DEFAULT_PLIES = {'TicTacToe': 9, 'Connect4': 42, 'DragonChess': 512}
