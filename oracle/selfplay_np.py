@@ -81,3 +81,71 @@ def play_game(search, game_cls, temp, max_plies=None):
         else:
             ex[0] = 1 if ex[3] == winner else -1
     return [serialize_record(e[0], e[1], e[2]) for e in history], winner, trace
+
+
+class RandomSearch(object):
+    """RandomMCTS.py:4-25: the opponent of Blackbird.TestRandom.  Two draws from the global
+    numpy stream per move (the action, then the reported win rate); no tree."""
+
+    def __init__(self, rng=None):
+        self.Rng = rng if rng is not None else np.random
+        self.Root = None
+
+    def DropRoot(self):
+        self.Root = None                              # inherited MCTS.DropRoot (MCTS.py:141-144)
+
+    def FindMove(self, state, *args, **kwargs):
+        legal = state.LegalActions()
+        action = self.Rng.choice([i for i in range(len(legal)) if legal[i] == 1])    # RandomMCTS.py:10-11
+        winRate = self.Rng.random()                                                 # RandomMCTS.py:12
+        childProbability = state.LegalActions()
+        s = sum(childProbability)
+        if s > 0:
+            childProbability /= s
+        nxt = state.Copy()
+        nxt.ApplyAction(action)
+        return nxt, winRate, childProbability
+
+    def MoveRoot(self, *args, **kwargs):
+        return
+
+    def ResetRoot(self, *args, **kwargs):
+        return
+
+
+def arena_game(model1, model2, game_cls, temp, on_state=None):
+    """One iteration of Blackbird.TestModels (Blackbird.py:195-216): +1 / 0 / -1 for model1.
+    ``on_state`` sees every position both players are moved to (test hook, not in the reference)."""
+    import random
+    model1ToMove = random.choice([True, False])       # Blackbird.py:196, the stdlib stream
+    model1Player = 1 if model1ToMove else 2
+    winner = None
+    model1.DropRoot()
+    model2.DropRoot()
+    state = game_cls()
+    while winner is None:
+        mover = model1 if model1ToMove else model2
+        nextState = mover.FindMove(state, temp)[0]
+        state = nextState
+        if on_state is not None:
+            on_state(state)
+        model1.MoveRoot(state)
+        model2.MoveRoot(state)
+        model1ToMove = not model1ToMove
+        winner = state.Winner()
+    if winner == model1Player:
+        return 1
+    elif winner == 0:
+        return 0
+    return -1
+
+
+def arena_random(model, game_cls, temp, numTests, on_state=None):
+    """Blackbird.TestRandom (Blackbird.py:84-112): (tally, per-game results)."""
+    names = {1: 'wins', 0: 'draws', -1: 'losses'}
+    stats, results = {}, []
+    for _ in range(numTests):
+        r = arena_game(model, RandomSearch(), game_cls, temp, on_state)
+        stats[names[r]] = stats.get(names[r], 0) + 1
+        results.append(r)
+    return stats, results

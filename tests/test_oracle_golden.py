@@ -121,3 +121,23 @@ def test_selfplay_records(golden):
         np.random.seed(case['seed'])
         recs, winner, _ = selfplay_np.play_game(m, game, 1)
         assert [r.hex() for r in recs] == case['records'], (case['game'], case['kind'], case['seed'])
+
+
+def test_random_arena(golden):
+    """oracle arena_random == the unmodified Blackbird.TestRandom, position for position (arena.json)."""
+    import random
+    for case in golden('arena.json'):
+        game = GAMES[case['game']]
+        ev = search_np.KatEvaluator(game.LegalMoves)
+        m = search_np.NetSearch(ev, case['kind'], maxDepth=10, explorationRate=0.85, playLimit=case['playLimit'])
+        boards = []
+
+        def seen(state):
+            boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                         + bytes([int(state.Player)])).hexdigest()[:12])
+        random.seed(case['seed'])
+        np.random.seed(case['seed'])
+        stats, results = selfplay_np.arena_random(m, game, case['temp'], case['numTests'], seen)
+        assert boards == case['boards'], (case['game'], case['kind'])
+        assert results == [r[0] for r in case['rows']]
+        assert stats == case['stats']
