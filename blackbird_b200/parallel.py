@@ -97,21 +97,25 @@ def allgather_raw(raw, group=None, to_host=True):
     return out
 
 
-def selfplay_sharded(make_engine, n_games, play_limit, temp=1.0, seed0=1000, group=None, gather=True):
+def selfplay_sharded(make_engine, n_games, play_limit, temp=1.0, seed0=1000, group=None, gather=True, max_slots=None):
     """Play global games [0, n_games) across the ranks of `group` and all-gather the raw records.
 
     make_engine(n_slots) -> Engine on this rank's GPU (every rank must build the same configuration).
-    Every rank runs the same number of slots (the largest shard) so the gathered buffers are
-    fixed-stride; surplus slots play a game that is dropped.  Returns (raw_all, owner_slices):
-    raw_all as allgather_raw, owner_slices[r] = (first row of rank r in raw_all, games it owns)."""
+    Every rank plays the same number of game rows (the largest shard) so the gathered buffers are
+    fixed-stride; surplus rows play a game that is dropped.  With max_slots a rank plays its rows on
+    at most that many concurrent slots (a slot that ends a game takes the rank's next unplayed row,
+    bb_selfplay_games): BASELINE configs[4b], 131072 games on 4096 slots per GPU.  Returns (engine,
+    raw_all, owner_slices): raw_all as allgather_raw, owner_slices[r] = (first row of rank r in
+    raw_all, games it owns)."""
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    slots = shard_range(n_games, 0, world)[1]               # rank 0 holds the largest shard
+    rows = shard_range(n_games, 0, world)[1]                # rank 0 holds the largest shard
+    slots = rows if max_slots is None else max(1, min(rows, int(max_slots)))
     lo, hi = shard_range(n_games, rank, world)
     eng = make_engine(slots)
-    u = np.ones((slots, eng.max_plies))
+    u = np.ones((rows, eng.max_plies))
     u[:hi - lo] = game_uniforms(range(lo, hi), eng.max_plies, seed0)
-    eng.selfplay(play_limit, temp, u)
+    eng.selfplay(play_limit, temp, u, n_rows=rows)
     if gather and world > 1:
         raw_all = allgather_raw(_records_device_views(eng), group)
     else:
@@ -119,5 +123,5 @@ def selfplay_sharded(make_engine, n_games, play_limit, temp=1.0, seed0=1000, gro
     owners = []
     for r in range(world if (gather and world > 1) else 1):
         a, b = shard_range(n_games, r, world) if world > 1 else (0, n_games)
-        owners.append((r * slots, b - a))
+        owners.append((r * rows, b - a))
     return eng, raw_all, owners

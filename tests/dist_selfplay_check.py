@@ -34,6 +34,15 @@ def main():
         flat += got[first:first + count]
     assert len(flat) == N_GAMES, (len(flat), owners)
     eng.close()
+    # the same games on at most 2 slots per rank (more game rows than slots: bb_selfplay_games)
+    eng, raw_all, owners = parallel.selfplay_sharded(make, N_GAMES, P, max_slots=2)
+    assert eng.n_games == 2
+    got = records.build_records(eng, raw_all)
+    narrow = []
+    for first, count in owners:
+        narrow += got[first:first + count]
+    assert narrow == flat, 'records depend on the slot count'
+    eng.close()
     one = make(N_GAMES)
     one.selfplay(P, 1.0, parallel.game_uniforms(range(N_GAMES), one.max_plies))
     want = records.build_records(one)
