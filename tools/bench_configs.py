@@ -10,7 +10,9 @@ profiles/ holds a number for every row of SURVEY.md 8(d)'s table:
   cfg4b  Connect4 DynamicMCTS 800 sims/move, 131072 whole games on the 4096 slots of one GPU (host uniforms in,
          records out: the e2e definition of bench.py)
 
-Usage: python tools/bench_configs.py [cfg0 cfg2 cfg3 cfg4a cfg4b] > lines.jsonl
+  mcts_only  Connect4 FixedMCTS / DynamicMCTS with the integer evaluator (no network): tree cost alone (not in the default set)
+
+Usage: python tools/bench_configs.py [cfg0 cfg2 cfg3 cfg4a cfg4b mcts_only] > lines.jsonl
 Timing: CUDA events / synchronize-bracketed wall clock after an untimed warm-up; synthetic data (random-init
 weights seed 0, per-game uniforms RandomState(1000 + g)).  Nothing here touches oracle/.
 """
@@ -33,8 +35,10 @@ def out(**kw):
     print(json.dumps(kw), flush=True)
 
 
-def make_engine(game, kind, slots, play_limit, **kw):
-    eng = Engine(game, kind, n_games=slots, evaluator='net', play_limit_hint=play_limit, **kw)
+def make_engine(game, kind, slots, play_limit, evaluator='net', **kw):
+    eng = Engine(game, kind, n_games=slots, evaluator=evaluator, play_limit_hint=play_limit, **kw)
+    if evaluator != 'net':
+        return eng
     w = netinit.random_weights(engine.plane_shape(game)[2], engine.n_actions(game), seed=0, blocks=4, filters=16, dense=16)
     eng.load_network(w, 4, 16, 16, precision='bf16')
     return eng
@@ -137,6 +141,13 @@ def main():
     if 'cfg2' in want:
         steady('cfg2 Connect4 DynamicMCTS, one GPU share of 16384 games / 8 GPUs', 'Connect4', 'dynamic', 2048, 800, 3)
         steady('cfg2 Connect4 DynamicMCTS, 4096 slots', 'Connect4', 'dynamic', 4096, 800, 3)
+    if 'mcts_only' in want:
+        # the tree cost alone -- the integer evaluator of Appendix B.2 (a few integer operations per
+        # position, fused into the tick-mode evaluation kernel) instead of the network; one launch pair per tick
+        steady('mcts_only Connect4 FixedMCTS, integer evaluator (no network), tick mode', 'Connect4', 'fixed', 4096, 800, 2,
+               evaluator='kat')
+        steady('mcts_only Connect4 DynamicMCTS, integer evaluator (no network), tick mode', 'Connect4', 'dynamic', 4096, 800, 2,
+               evaluator='kat')
     if 'cfg3' in want:
         steady('cfg3 DragonChess FixedMCTS playLimit 100', 'DragonChess', 'fixed', 1024, 100, 2, prelude=4, max_plies=64)
         steady('cfg3 DragonChess FixedMCTS playLimit 10 (template)', 'DragonChess', 'fixed', 1024, 10, 4, prelude=4, max_plies=64)
