@@ -180,7 +180,10 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 // Value and policy heads from the per-position sums over H,W of the three head feature maps
 // (hsum[p*4 + {0: value, 1,2: policy}]): value = tanh(dense(relu(dense(1->D)+sum))), policy =
 // softmax(dense(2->A)+sum), noise mix, renormalise (NetworkFactory.py:115-182).  Block-wide.
-template <class G>
+// FAST (the bf16 tensor-core kernel only; its tolerance is 2e-2): wide heads without noise take three passes per
+// position (logits + max with batched non-coherent weight loads, ex2.approx + sum, scaled store) instead of four
+// with two IEEE divisions per action.
+template <class G, bool FAST = false>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
                              float* __restrict__ value, const Team& tm, const int* out_idx = nullptr, float* zbuf = nullptr) {
@@ -233,6 +236,25 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
       // Same operations in the same order either way: the results are bit-identical.
       float* z_ = zbuf ? zbuf : out;
       float m = -INFINITY;
+      if (FAST && !(np.eps > 0.f)) {
+        // the head weights sit in L2 (48 KB): non-coherent loads, four actions in flight per thread, so the pass costs
+        // ~7 dependent round trips instead of one per action
+#pragma unroll 4
+        for (int a = tid; a < G::A; a += nthreads) {
+          const float z = fmaf(s0, __ldg(pol_w + a), fmaf(s1, __ldg(pol_w + G::A + a), (float)HW * __ldg(pol_b + a)));
+          z_[a] = z;
+          m = fmaxf(m, z);
+        }
+        m = block_reduce(m, red, true, tm);
+        float sum = 0.f;
+#pragma unroll 4
+        for (int a = tid; a < G::A; a += nthreads) { const float e = __expf(z_[a] - m); z_[a] = e; sum += e; }
+        sum = block_reduce(sum, red, false, tm);
+        const float inv = 1.f / sum;
+#pragma unroll 4
+        for (int a = tid; a < G::A; a += nthreads) out[a] = z_[a] * inv;
+        continue;
+      }
       for (int a = tid; a < G::A; a += nthreads) {
         float z = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
         z_[a] = z;

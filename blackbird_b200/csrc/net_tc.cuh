@@ -576,7 +576,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
-      heads_finish<G>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
+      heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
                       G::A > 32 ? reinterpret_cast<float*>(pb_ + L.zb) : nullptr);
     }
     if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
