@@ -85,3 +85,30 @@ def test_allgather_single_process_is_identity():
     got = allgather_raw(raw)
     for k in raw:
         assert np.array_equal(got[k], raw[k]) and got[k].dtype == raw[k].dtype
+
+
+def test_selfplay_sharded_rows_slots_and_uniforms_with_a_stub_engine():
+    """Host logic of selfplay_sharded without a GPU: game rows per rank, slot cap, per-game uniform rows, owner
+    slices (single process; the engine is a stub that records the call)."""
+    from blackbird_b200.parallel import game_uniforms, selfplay_sharded
+
+    class StubEngine(object):
+        max_plies = 42
+
+        def __init__(self, slots):
+            self.n_games = slots
+            self.calls = []
+
+        def selfplay(self, play_limit, temp, uniforms, n_rows=None):
+            self.calls.append((play_limit, temp, np.array(uniforms), n_rows))
+
+        def records_raw(self):
+            return {'n_moves': np.zeros(self.calls[-1][3], np.int32)}
+
+    for max_slots, want_slots in ((None, 10), (4, 4), (64, 10)):
+        eng, raw, owners = selfplay_sharded(StubEngine, 10, 24, temp=1.0, seed0=1000, max_slots=max_slots)
+        assert eng.n_games == want_slots and owners == [(0, 10)]
+        (play_limit, temp, u, n_rows), = eng.calls
+        assert (play_limit, temp, n_rows) == (24, 1.0, 10) and u.shape == (10, 42)
+        assert np.array_equal(u, game_uniforms(range(10), 42, 1000))
+        assert len(raw['n_moves']) == 10
