@@ -38,8 +38,10 @@ def parse():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--games', type=int, default=4096, help='concurrent games per GPU')
     ap.add_argument('--sims', type=int, default=800, help='simulations per move (playLimit)')
-    ap.add_argument('--epsilon', type=float, default=0.0, help='policy noise weight (template: 0.3)')
-    ap.add_argument('--cpu-seconds', type=float, default=12.0, help='CPU baseline sample length')
+    ap.add_argument('--epsilon', type=float, default=0.3, help='policy noise weight of the headline loop (parameters_template.yaml: 0.3, alpha 0.2)')
+    ap.add_argument('--other-epsilon', type=float, default=0.0, help='second timed loop at this noise weight (0 = the parity setting); <0: skip')
+    ap.add_argument('--cpu-seconds', type=float, default=25.0, help='cpu_baseline sample length (GPU arm)')
+    ap.add_argument('--ref-seconds', type=float, default=150.0, help='--impl reference: total length of warm-up + timed windows')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
     ap.add_argument('--lanes', type=int, default=0, help='engine lanes (0 = engine default)')
     ap.add_argument('--prelude', type=int, default=45, help='untimed move rounds at 32 sims/move that desynchronise the game slots')
@@ -55,15 +57,22 @@ def config_dict(args, n_gpus):
             'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS', 'max_depth': MAX_DEPTH,
             'step': 'one move round: the %d slots together play %d moves (FindMove+MoveRoot each), no barrier between moves, finished games restart in place' % (args.games, args.games),
             'prelude': '%d untimed move rounds at 32 sims/move to desynchronise the slots, then the warm-up steps' % args.prelude,
-            'epsilon': args.epsilon, 'parallelism': 'games sharded over %d GPU(s), no data-path collective' % n_gpus,
+            'epsilon': args.epsilon, 'alpha': 0.2,
+            'noise': ('policy noise ON as in parameters_template.yaml (every evaluation mixes Beta(alpha, 1-alpha) draws into the policy, NetworkFactory.py:176-182)'
+                      if args.epsilon > 0 else 'policy noise off (the parity setting)'),
+            'parallelism': 'games sharded over %d GPU(s), no data-path collective' % n_gpus,
             'l2_policy': 'working set (tree pool, GBs) larger than L2; no flush needed'}
 
 
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference (Blackbird.GenerateTrainingSamples -> FindMove ...)
 # ---------------------------------------------------------------------------------------------
-def _cpu_worker(task):
-    seed, seconds, sims, epsilon = task
+def _cpu_worker(idx, shared, stop, sims, epsilon):
+    """One persistent single-threaded worker (the reference is single-threaded Python): whole games, one after the
+    other, until told to stop.  A sampler thread publishes the worker's cumulative simulation / game / evaluation
+    counts every 50 ms, so the parent can cut time windows anywhere.  The FIRST game starts with idx-dependent cheap
+    moves (32 simulations each), which spreads the workers over all game phases from the first window on -- the same
+    desynchronisation the GPU arm's prelude does for its slots; every later game is a full game from the empty board."""
     try:
         from threadpoolctl import threadpool_limits
         threadpool_limits(1)
@@ -73,53 +82,121 @@ def _cpu_worker(task):
     from oracle import network_np, search_np
     from oracle.rules_np import GAMES
     w = network_np.init_weights(3, 7, seed=0, **NET)
-    ev = network_np.NetEvaluator(w, eps=epsilon)
+    ev = network_np.NetEvaluator(w, eps=epsilon, rng=np.random.RandomState(77 + idx))
     s = search_np.NetSearch(ev, SEARCH, maxDepth=MAX_DEPTH, explorationRate=C_PUCT, playLimit=sims,
-                            rng=np.random.RandomState(seed))
-    t0 = time.time()
-    end = t0 + seconds
-    games = 0
-    while time.time() < end:
+                            rng=np.random.RandomState(1000 + idx))
+    games = [0]
+    ready = [0.0]
+
+    def sampler():
+        while not stop.value:
+            shared[4 * idx + 0] = s.Stats['sims']
+            shared[4 * idx + 1] = games[0]
+            shared[4 * idx + 2] = s.Evals
+            shared[4 * idx + 3] = ready[0]
+            time.sleep(0.05)
+
+    threading.Thread(target=sampler, daemon=True).start()
+    cheap = (idx * 7) % 24                                   # plies of the first game played at 32 simulations
+    first = True
+    while not stop.value:
         state = GAMES[GAME]()
         s.DropRoot()
-        winner = None
-        while winner is None and time.time() < end:
-            state, _, _ = s.FindMove(state, 1, moveTime=max(end - time.time(), 1e-3), playLimit=sims)
+        winner, ply = None, 0
+        while winner is None and not stop.value:
+            lim = 32 if (first and ply < cheap) else sims
+            if first and ply >= cheap:
+                ready[0] = 1.0                               # from here on the worker runs the measured workload
+            state, _, _ = s.FindMove(state, 1, playLimit=lim)
             s.MoveRoot(state)
             winner = state.Winner(None)
-        games += winner is not None
-    return s.Stats['sims'], games, time.time() - t0
+            ply += 1
+        ready[0] = 1.0
+        games[0] += winner is not None
+        first = False
+
+
+class CpuArm(object):
+    """os.cpu_count() persistent worker processes playing the bench workload on the host cores (oracle port of the
+    reference; numpy fp32 network at batch 1, eager child evaluation exactly like MCTS.py:134-139)."""
+
+    def __init__(self, sims, epsilon, cores=None):
+        import multiprocessing as mp
+        self.cores = cores or os.cpu_count() or 1
+        ctx = mp.get_context('fork')
+        self.shared = ctx.Array('d', 4 * self.cores, lock=False)
+        self.stop = ctx.Value('i', 0, lock=False)
+        self.procs = [ctx.Process(target=_cpu_worker, args=(i, self.shared, self.stop, sims, epsilon), daemon=True)
+                      for i in range(self.cores)]
+        for p_ in self.procs:
+            p_.start()
+
+    def wait_ready(self, timeout=40.0):
+        t0 = time.time()
+        while time.time() - t0 < timeout and sum(self.shared[4 * i + 3] for i in range(self.cores)) < self.cores:
+            time.sleep(0.1)
+
+    def read(self):
+        a = list(self.shared)
+        return time.perf_counter(), sum(a[0::4]), sum(a[1::4]), sum(a[2::4])
+
+    def window(self, seconds):
+        t0, s0, g0, e0 = self.read()
+        time.sleep(seconds)
+        t1, s1, g1, e1 = self.read()
+        return (s1 - s0) / (t1 - t0), g1 - g0, (e1 - e0) / (t1 - t0), t1 - t0
+
+    def close(self):
+        self.stop.value = 1
+        for p_ in self.procs:
+            p_.join(timeout=5)
+            if p_.is_alive():
+                p_.terminate()
+
+
+CPU_SAMPLE = ('%d persistent single-threaded worker processes (one per host core) playing whole Connect4 FixedMCTS games back to back '
+              '(oracle port of the reference: numpy fp32 network at batch 1, eager child evaluation), first game of every worker '
+              'fast-forwarded by 0-23 cheap plies so that all game phases are present; %s')
 
 
 def cpu_sample(seconds, sims, epsilon, cores=None):
-    import multiprocessing as mp
-    cores = cores or os.cpu_count() or 1
-    ctx = mp.get_context('fork')
-    with ctx.Pool(cores) as pool:
-        res = pool.map(_cpu_worker, [(1000 + i, seconds, sims, epsilon) for i in range(cores)])
-    total = sum(r[0] for r in res)
-    wall = max(r[2] for r in res)
-    return total / wall, sum(r[1] for r in res), cores, wall
+    arm = CpuArm(sims, epsilon, cores)
+    try:
+        arm.wait_ready()
+        arm.window(min(3.0, seconds / 4))                    # settle
+        v, games, evals, wall = arm.window(seconds)
+    finally:
+        arm.close()
+    return v, games, arm.cores, wall
 
 
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    seconds = max(2.0, min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup)))
-    for _ in range(args.warmup):
-        cpu_sample(min(seconds, 2.0), args.sims, args.epsilon)
-    vals, tot_t = [], 0.0
-    for _ in range(args.steps):
-        v, _, cores, wall = cpu_sample(seconds, args.sims, args.epsilon)
-        vals.append(v)
-        tot_t += wall
-    value = sum(vals) / len(vals)
-    sample = '%d worker processes x %.0f s of Connect4 FixedMCTS self-play per step (oracle port, numpy fp32 network at batch 1)' % (cores, seconds)
+    # one pool for the whole run; steps are consecutive time windows of the same continuously running workload, sized
+    # so that warm-up + timed windows cover >= 120 s (BASELINE.md section 4) and the run ends within a few minutes
+    n_win = max(1, args.steps + args.warmup)
+    seconds = max(1.0, min(30.0, args.ref_seconds / n_win))
+    arm = CpuArm(args.sims, args.epsilon)
+    try:
+        arm.wait_ready()
+        for _ in range(args.warmup):
+            arm.window(seconds)
+        t0, s0, g0, e0 = arm.read()
+        per = [arm.window(seconds) for _ in range(args.steps)]
+        t1, s1, g1, e1 = arm.read()
+    finally:
+        arm.close()
+    cores = arm.cores
+    value = (s1 - s0) / (t1 - t0)
+    sample = CPU_SAMPLE % (cores, '%d warm-up + %d timed windows of %.1f s, %.0f s in all; %d games finished, %.1f network evaluations per simulation'
+                           % (args.warmup, args.steps, seconds, n_win * seconds, g1 - g0, (e1 - e0) / max(1.0, s1 - s0)))
     print_line(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': 1e3 * tot_t / max(1, args.steps), 'higher_is_better': True,
+        'warmup': args.warmup, 'ms_per_step': 1e3 * (t1 - t0) / max(1, args.steps), 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(args, args.gpus),
+        'games_per_sec': (g1 - g0) / (t1 - t0), 'per_window': [round(w_[0], 1) for w_ in per],
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0}))
@@ -194,7 +271,11 @@ def run_ours(args):
     eng = Engine(GAME, SEARCH, n_games=G, max_depth=MAX_DEPTH, exploration_rate=C_PUCT, evaluator='net',
                  play_limit_hint=P, device=local, lanes=args.lanes)
     weights = netinit.random_weights(cin, 7, seed=0, **NET)
-    eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=args.epsilon, alpha=0.2, seed=rank, precision=args.precision)
+
+    def load_net(eps):
+        eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=eps, alpha=0.2, seed=1 + rank, precision=args.precision)
+
+    load_net(args.epsilon)
     # per-game move-sampling uniforms, game id = rank*G + slot (records identical for any GPU count)
     uniforms = np.stack([np.random.RandomState(1000 + rank * G + g).random_sample(eng.max_plies) for g in range(G)])
     stream = eng.stream()
@@ -212,43 +293,54 @@ def run_ours(args):
     eng.stream_moves(1, 32, 1.0, uniforms)           # uploads the uniform table
     if args.prelude > 0:
         eng.stream_moves(args.prelude * G, 32)
-    for _ in range(max(1, args.warmup)):
-        eng.stream_moves(G, P)
-    eng.check_status()
-    c0 = eng.counters(reset=True)
-    sampler = ClockSampler(local)
-    sampler.start()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(args.steps):
-        eng.stream_moves(G, P)
-    e1.record(stream)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    clocks = sampler.summary()
-    eng.check_status()
-    c = eng.counters(reset=True)
-    t = torch.tensor([ms], dtype=torch.float64, device='cuda')
-    cnt = torch.tensor([c['sims'], c['evals'], c['nodes'], c['expansions'], c['select_steps'], c['games_done'],
-                        c['kernel_launches'], c['moves'], c['ticks']], dtype=torch.float64, device='cuda')
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms = float(t.item())
-    sims, evals, nodes, exps, sel, games_done, launches, moves, ticks = [float(x) for x in cnt.tolist()]
-    value = sims / (ms * 1e-3)
-
-    # kernel shares: one profiled step (CUDA events around every advance / network launch)
-    streaming = eng.streaming
-    st0 = eng.stream_stats()
-    eng.profile(True, 16384)
-    eng.stream_moves(G, P)
-    prof = eng.profile_read()
-    eng.profile(False)
-    st1 = eng.stream_stats()
-    cp = eng.counters(reset=True)
     flops = netinit.flops_per_eval(h, w, cin, 7, **NET)
+    names = ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'games_done', 'kernel_launches', 'moves', 'ticks')
+
+    def timed_loop(steps, warmup):
+        """W untimed + K timed steps; CUDA events on the engine's stream, barrier + synchronize on both sides, time =
+        max over ranks, counters summed over ranks.  -> (ms, counters, clocks, stream-stat deltas of this rank)"""
+        for _ in range(max(1, warmup)):
+            eng.stream_moves(G, P)
+        eng.check_status()
+        eng.counters(reset=True)
+        st0 = eng.stream_stats()
+        sampler = ClockSampler(local)
+        sampler.start()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            eng.stream_moves(G, P)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.summary()
+        eng.check_status()
+        c = eng.counters(reset=True)
+        st1 = eng.stream_stats()
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        cnt = torch.tensor([c[k] for k in names], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        return float(t.item()), dict(zip(names, [float(x) for x in cnt.tolist()])), clocks, {k: st1[k] - st0[k] for k in st1}
+
+    ms, cn, clocks, dst = timed_loop(args.steps, args.warmup)
+    sims, evals, games_done, launches, moves, ticks = (cn[k] for k in ('sims', 'evals', 'games_done', 'kernel_launches', 'moves', 'ticks'))
+    value = sims / (ms * 1e-3)
+    streaming = eng.streaming
+
+    # the same loop at the other noise setting (template: epsilon 0.3 = every evaluation draws Beta noise per action,
+    # NetworkFactory.py:176-182; parity runs: epsilon 0), fewer steps
+    other = None
+    if args.other_epsilon >= 0 and args.other_epsilon != args.epsilon:
+        load_net(args.other_epsilon)
+        ms2, cn2, _, _ = timed_loop(max(3, args.steps // 2), max(3, args.warmup))
+        other = {'epsilon': args.other_epsilon, 'value': cn2['sims'] / (ms2 * 1e-3), 'unit': UNIT, 'steps': max(3, args.steps // 2),
+                 'ms_per_step': ms2 / max(3, args.steps // 2), 'evals_per_sec': cn2['evals'] / (ms2 * 1e-3),
+                 'what': 'the same timed loop with the policy noise %s' % ('off (the parity setting)' if args.other_epsilon == 0 else 'on')}
+        load_net(args.epsilon)
+
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
@@ -256,8 +348,27 @@ def run_ours(args):
         pass
     tensor_peak = float(peaks.get('bf16_tflops_sustained', 1400.0))
     hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
-    peak_src = 'measured (MEASURED_PEAKS.json, sustained bf16)' if peaks else 'fallback'
-    net_tflops = cp['evals'] * flops / (prof['eval_ms'] * 1e-3) / 1e12 if prof['eval_ms'] > 0 else 0.0
+    peak_src = 'measured (MEASURED_PEAKS.json, sustained bf16: the kernel runs inside a long step)' if peaks else 'fallback'
+    traffic = {}
+    try:                                             # ncu DRAM bytes of the same kernels in tick mode (profiles/r02_traffic.json)
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')))
+    except Exception:
+        pass
+    if streaming:
+        # the two persistent kernels are resident on every SM for the whole timed region: one launch of each per
+        # step, launch duration = step duration, so the roofline numbers come from the TIMED loop itself
+        adv_ms = eval_ms = ms
+        n_launch = args.steps
+        cp = cn
+        prof_ticks = max(1.0, dst['batches'])
+    else:
+        eng.profile(True, 16384)                     # tick mode: CUDA events around every advance / network launch of one more step
+        eng.stream_moves(G, P)
+        prof = eng.profile_read()
+        eng.profile(False)
+        cp = {k: float(v) for k, v in eng.counters(reset=True).items()}
+        adv_ms, eval_ms, n_launch, prof_ticks = prof['advance_ms'], prof['eval_ms'], max(1, prof['ticks']), max(1, prof['ticks'])
+    net_tflops = cp['evals'] * flops / (eval_ms * 1e-3) / 1e12 if eval_ms > 0 else 0.0
     # tree traffic model of SURVEY.md 8d with measured d, k, n_exp (Connect4: S folded out -- child states are not stored)
     d_bar = cp['select_steps'] / max(1, cp['sims'])
     nexp = cp['expansions'] / max(1, cp['sims'])
@@ -265,44 +376,49 @@ def run_ours(args):
     # select: one 32-byte node per child per level; expand: k 32-byte nodes + the parent's header; evaluator
     # mailbox: state out/in + policy/value out/in; backup: 8-byte read-modify-write per path node
     b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * 16 + 2 * 4 * 8) + 16 * (d_bar + 1)
-    tree_gbs = cp['sims'] * b_sim / (prof['advance_ms'] * 1e-3) / 1e9 if prof['advance_ms'] > 0 else 0.0
-    launches_prof = max(1, cp['kernel_launches'] // 3) if streaming else max(1, prof['ticks'])
+    tree_gbs = cp['sims'] * b_sim / (adv_ms * 1e-3) / 1e9 if adv_ms > 0 else 0.0
+    per_world = max(1, world)
     if streaming:
-        kname = 'k_net_forward_tc<Connect4> serve mode (bf16 tcgen05 tower, persistent: %d evals/launch, batches of %.2f)' % (
-            cp['evals'] / launches_prof, cp['evals'] / max(1, prof['ticks']))
+        kname = 'k_net_forward_tc<Connect4> serve mode (bf16 tcgen05 tower, persistent: %d evals/launch/GPU, batches of %.2f)' % (
+            cp['evals'] / n_launch / per_world, cp['evals'] / per_world / prof_ticks)
     elif args.precision == 'bf16':
-        kname = 'k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks']))
+        kname = 'k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' % (cp['evals'] / prof_ticks)
     else:
-        kname = 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / max(1, prof['ticks']))
+        kname = 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / prof_ticks)
+    net_traffic = None
+    if traffic.get('net_dram_bytes_per_eval') is not None:
+        net_traffic = traffic['net_dram_bytes_per_eval'] * cp['evals'] / per_world / n_launch
     roofline = {'bound': 'tensor', 'kernel': kname,
-                'achieved': net_tflops, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / tensor_peak,
-                'traffic': None, 'peak_source': peak_src, 'flops_per_eval': flops,
-                'launch_ms_avg': prof['eval_ms'] / launches_prof,
-                'step_share': prof['eval_ms'] / max(1e-9, prof['eval_ms'] + prof['advance_ms'])}
+                'achieved': net_tflops / per_world, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / per_world / tensor_peak,
+                'traffic': net_traffic, 'traffic_how': traffic.get('how'), 'peak_source': peak_src, 'flops_per_eval': flops,
+                'algorithmic_bytes_per_eval': 16 + 4 * 8, 'dram_bytes_per_eval_ncu': traffic.get('net_dram_bytes_per_eval'),
+                'launch_ms_avg': eval_ms / n_launch, 'from': 'the timed loop (evals and CUDA-event time of the %d timed steps)' % args.steps if streaming else 'one profiled step',
+                'step_share': eval_ms / max(1e-9, eval_ms + adv_ms)}
     roofline_tree = {'bound': 'hbm', 'kernel': ('k_search_stream<Connect4> (persistent select/expand/backup)' if streaming
-                                                else 'k_advance<Connect4> (select/expand/backup)'), 'achieved': tree_gbs, 'peak': hbm_peak,
-                     'unit': 'GB/s', 'frac': tree_gbs / hbm_peak, 'bytes_per_sim_model': b_sim, 'mean_depth': d_bar,
+                                                else 'k_advance<Connect4> (select/expand/backup)'), 'achieved': tree_gbs / per_world, 'peak': hbm_peak,
+                     'unit': 'GB/s', 'frac': tree_gbs / per_world / hbm_peak, 'bytes_per_sim_model': b_sim, 'mean_depth': d_bar,
+                     'dram_bytes_per_sim_ncu': traffic.get('search_dram_bytes_per_sim'),
+                     'traffic': (traffic['search_dram_bytes_per_sim'] * cp['sims'] / per_world / n_launch) if traffic.get('search_dram_bytes_per_sim') is not None else None,
                      'expansions_per_sim': nexp, 'children_per_expansion': k_bar, 'evals_per_sim': cp['evals'] / max(1, cp['sims']),
-                     'launch_ms_avg': prof['advance_ms'] / launches_prof}
+                     'launch_ms_avg': adv_ms / n_launch}
 
     # the kernel with the larger share of the step is the one `roofline` reports; the other rides along
     roofline_tree['step_share'] = 1.0 - roofline['step_share']
     if streaming:
-        # the two persistent kernels share every SM for the whole step: each one's launch spans the step, so its
-        # share is 1 by construction; what tells them apart is how busy the network pipelines were (cycle
-        # counters kept by the kernel itself: wait for tickets / convolution tower / heads + publish)
-        dw, dt, dh = [st1[k] - st0[k] for k in ('cyc_wait', 'cyc_tower', 'cyc_heads')]
-        nb = max(1, st1['batches'] - st0['batches'])
+        # each persistent launch spans the step, so its share is 1 by construction; what tells the two apart is how
+        # busy the network pipelines were (cycle counters kept by the kernel itself: wait for tickets / tower / heads)
+        dw, dt, dh = dst['cyc_wait'], dst['cyc_tower'], dst['cyc_heads']
+        nb = max(1, dst['batches'])
         roofline['step_share'] = roofline_tree['step_share'] = 1.0
         roofline['concurrent'] = roofline_tree['concurrent'] = 'both persistent kernels are resident on every SM for the whole step'
         roofline['pipeline_busy_frac'] = (dt + dh) / max(1, dw + dt + dh)
         roofline['cycles_per_batch'] = {'wait': dw / nb, 'tower': dt / nb, 'heads_publish': dh / nb}
         roofline['batches'] = nb
-        roofline_tree['warp_busy_frac'] = (st1['cyc_search_busy'] - st0['cyc_search_busy']) / max(1, st1['cyc_search_total'] - st0['cyc_search_total'])
-        roofline_tree['cycles_per_advance_call'] = (st1['cyc_search_busy'] - st0['cyc_search_busy']) / max(1, st1['search_calls'] - st0['search_calls'])
-        dominant, other = roofline, roofline_tree           # the search warps wait on the network (busy_frac ~ 0.9)
+        roofline_tree['warp_busy_frac'] = dst['cyc_search_busy'] / max(1, dst['cyc_search_total'])
+        roofline_tree['cycles_per_advance_call'] = dst['cyc_search_busy'] / max(1, dst['search_calls'])
+        dominant, other_k = roofline, roofline_tree           # the search warps wait on the network (busy_frac ~ 0.9)
     else:
-        dominant, other = (roofline, roofline_tree) if roofline['step_share'] >= 0.5 else (roofline_tree, roofline)
+        dominant, other_k = (roofline, roofline_tree) if roofline['step_share'] >= 0.5 else (roofline_tree, roofline)
 
     # e2e: whole games through the C-ABI call with host buffers (H2D uniforms, D2H records inside)
     e2e = None
@@ -342,8 +458,8 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, games, cores, wall = cpu_sample(args.cpu_seconds, P, args.epsilon)
-        cpu = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-               'sample': '%d worker processes x %.0f s of the same workload (oracle port of the reference, numpy fp32 network at batch 1)' % (cores, wall)}
+        cpu = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'games_finished': games,
+               'sample': CPU_SAMPLE % (cores, 'one %.0f s window after a 3 s settle' % wall)}
 
     if rank == 0:
         print_line(json.dumps({
@@ -352,7 +468,7 @@ def run_ours(args):
             'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
             'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
             'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
-            'roofline': dominant, 'roofline_other': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e,
+            'roofline': dominant, 'roofline_other': other_k, 'other_noise_setting': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e,
             'gpu_launches': int(launches), 'clocks': clocks}))
     if world > 1:
         dist.barrier()

@@ -54,6 +54,7 @@ SIGNATURES = {
     'bb_net_load': (I, [VP, C.POINTER(bb_net_desc), VP, C.c_size_t]),
     'bb_net_forward': (I, [VP, VP, I, VP, VP, VP]),
     'bb_kat_forward': (I, [I, VP, I, VP, VP, VP]),
+    'bb_debug_beta_noise': (I, [C.c_float, C.c_uint64, I, VP, VP]),
     'bb_search_reset': (I, [VP, VP]),
     'bb_search_drop_root': (I, [VP]),
     'bb_search_begin_move': (I, [VP, I]),
@@ -81,6 +82,8 @@ SIGNATURES = {
     'bb_engine_lanes': (I, [VP]),
     'bb_engine_streaming': (I, [VP]),
     'bb_stream_stats': (I, [VP, C.POINTER(C.c_uint64)]),
+    'bb_stream_last_answers': (I, [VP, VP, VP, VP, VP]),
+    'bb_debug_kernels_concurrent': (I, [I]),
 }
 
 

@@ -156,25 +156,21 @@ __device__ __forceinline__ float u01(unsigned long long key, unsigned long long 
   z ^= z >> 31;
   return ((float)(z >> 40) + 0.5f) * (1.0f / 16777216.0f);
 }
-// Gamma(a, 1) for 0 < a < 1: Marsaglia-Tsang on a+1, boosted by U^(1/a)
-__device__ float gamma_small(float a, unsigned long long key, unsigned long long& ctr) {
-  const float d = a + 1.0f - 1.0f / 3.0f, c = rsqrtf(9.0f * d);
-  for (int it = 0; it < 16; ++it) {
-    float u1 = u01(key, ctr++), u2 = u01(key, ctr++);
-    float x = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
-    float v = 1.0f + c * x;
-    if (v <= 0.f) continue;
-    v = v * v * v;
-    float u = u01(key, ctr++);
-    if (logf(u) < 0.5f * x * x + d - d * v + d * logf(v)) return d * v * powf(u01(key, ctr++), 1.0f / a);
-  }
-  return a;
-}
-// dist.sample(...)[..., 0] of Dirichlet([alpha, 1-alpha]) == Beta(alpha, 1-alpha)  (A.17)
+// dist.sample(...)[..., 0] of Dirichlet([alpha, 1-alpha]) == Beta(alpha, 1-alpha)  (A.17), by Joehnk's method: X = U^(1/a),
+// Y = V^(1/b), accept when X + Y <= 1, return X / (X + Y).  For b = 1 - a the acceptance probability is
+// Gamma(1+a) Gamma(2-a) >= 0.785, so a draw costs ~2.4 uniforms and four MUFU operations on average (the first version,
+// two Marsaglia-Tsang gammas with Box-Muller normals, logf and powf, cost ~3 k cycles per action and sat on the network
+// pipelines' critical path: 7.4 k -> 49 k cycles of heads per batch with the template's epsilon 0.3).
 __device__ float beta_noise(float alpha, unsigned long long key, unsigned long long elem) {
-  unsigned long long ctr = elem << 8;
-  float x = gamma_small(alpha, key, ctr), y = gamma_small(1.0f - alpha, key, ctr);
-  return x / (x + y);
+  unsigned long long ctr = elem << 6;
+  const float ia = 1.0f / alpha, ib = 1.0f / (1.0f - alpha);
+  for (int it = 0; it < 32; ++it) {
+    const float u = u01(key, ctr++), v = u01(key, ctr++);
+    const float x = exp2f(ia * __log2f(u)), y = exp2f(ib * __log2f(v));
+    const float t = x + y;
+    if (t <= 1.0f && t > 0.f) return x / t;
+  }
+  return alpha;                                            // unreachable in practice: 0.215^32
 }
 
 // Value and policy heads from the per-position sums over H,W of the three head feature maps
@@ -186,9 +182,12 @@ __device__ float beta_noise(float alpha, unsigned long long key, unsigned long l
 template <class G, bool FAST = false>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
-                             float* __restrict__ value, const Team& tm, const int* out_idx = nullptr, float* zbuf = nullptr) {
+                             float* __restrict__ value, const Team& tm, const int* out_idx = nullptr, float* zbuf = nullptr,
+                             long long noise_base = -1) {
   constexpr int HW = G::H * G::W;
   const int tid = tm.tid, nthreads = tm.n;
+  // noise element index of position p: serve mode keys it on the full 32-bit ticket (noise_base), launch mode on the batch row
+  const unsigned long long nb = noise_base >= 0 ? (unsigned long long)noise_base : (unsigned long long)base;
   const int D = np.dense;                               // hd / pol_w / pol_b: np.head / np.pol_w / np.pol_b or copies in shared memory
   const float* d1w = hd + 17 + 34;
   const float* d1b = d1w + D;
@@ -202,6 +201,15 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
   }
   // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
   if (G::A <= 32) {
+    const bool noisy = np.eps > 0.f;
+    if (noisy) {                                           // one Beta draw per (position, action), spread over the whole team
+      const unsigned long long key = np.seed ^ (call * 0x632BE59BD9B4E019ull);
+      for (int i = tid; i < P * G::A; i += nthreads) {
+        const int p = i / G::A;
+        if (base + p < n) zbuf[i] = beta_noise(np.alpha, key, (nb + p) * G::A + (i - p * G::A));
+      }
+      tm.sync();
+    }
     if (tid < P && base + tid < n) {
       const float s0 = hsum[tid * 4 + 1], s1 = hsum[tid * 4 + 2];
       float z[G::A <= 32 ? G::A : 1];
@@ -218,8 +226,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
 #pragma unroll
       for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
         float pa = z[a] / sum;
-        if (np.eps > 0.f)
-          pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + tid) * G::A + a);
+        if (noisy) pa = (1.f - np.eps) * pa + np.eps * zbuf[tid * G::A + a];
         z[a] = pa;
         tot += pa;
       }
@@ -234,7 +241,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
       // intermediate values live in shared memory when the caller has room for A floats (every thread touches
       // only its own actions, so no barrier beyond the reductions'); otherwise in the output row itself.
       // Same operations in the same order either way: the results are bit-identical.
-      float* z_ = zbuf ? zbuf : out;
+      float* z_ = (zbuf && G::A > 32) ? zbuf : out;
       float m = -INFINITY;
       if (FAST && !(np.eps > 0.f)) {
         // the head weights sit in L2 (48 KB): non-coherent loads, four actions in flight per thread, so the pass costs
@@ -268,7 +275,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
       for (int a = tid; a < G::A; a += nthreads) {
         float pa = z_[a] / sum;
         if (np.eps > 0.f)
-          pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (unsigned long long)(base + p) * G::A + a);
+          pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (nb + p) * G::A + a);
         z_[a] = pa;
         tot += pa;
       }
@@ -382,7 +389,9 @@ k_net_forward(NetParams np, const typename G::State* __restrict__ states, int n_
       hsum[p * 4 + k] = s;
     }
     __syncthreads();
-    heads_finish<G>(np, np.head, np.pol_w, np.pol_b, hsum, red, base, n, Ge::P, call, policy, value, Team{(int)threadIdx.x, (int)blockDim.x, 0});
+    // hcell (consumed by the sums above) doubles as the noise scratch of the narrow heads: P * A <= 3 * ITEMS floats
+    heads_finish<G>(np, np.head, np.pol_w, np.pol_b, hsum, red, base, n, Ge::P, call, policy, value, Team{(int)threadIdx.x, (int)blockDim.x, 0},
+                    nullptr, G::A <= 32 ? hcell : nullptr);
   }
 }
 
@@ -453,6 +462,8 @@ static int net_serve_tc(NetDev* net, const NetServe& sv, float* policy, float* v
   const TcSmem<G> L(net->tc.w_blocks, net->p.layers);
   BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
   BB_CUDA(cudaFuncSetAttribute(k_net_forward_tc<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+  // a new noise epoch per persistent launch: inside a launch the noise is keyed on the 32-bit ticket
+  if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
   // one CTA per SM (a kernel that allocates TMEM never gets more), all resident for the whole launch
   k_net_forward_tc<G><<<net->sm_count, Ge::THREADS, L.total, stream>>>(net->p, net->tc, nullptr, 0, nullptr, policy, value, sv);
   BB_CUDA(cudaGetLastError());
@@ -596,6 +607,11 @@ static int net_build(NetDev* net, const bb_net_desc* d, const float* w, size_t n
   return BB_OK;
 }
 
+__global__ void k_beta_fill(float alpha, unsigned long long key, int n, float* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = beta_noise(alpha, key, (unsigned long long)i);
+}
+
 int net_create(int game, const bb_net_desc* d, const float* w, size_t n_floats, NetDev** out) {
   if (!d || !w || !out) { set_error("bb_net_load: null argument"); return BB_EINVAL; }
   NetDev* net = new NetDev();
@@ -623,3 +639,11 @@ void net_destroy(NetDev* net) {
 }
 
 }  // namespace bb
+
+extern "C" int bb_debug_beta_noise(float alpha, uint64_t seed, int n, float* out_dev, void* stream) {
+  if (!(alpha > 0.f && alpha < 1.f) || n < 0 || !out_dev) { bb::set_error("bb_debug_beta_noise: alpha in (0,1), n >= 0"); return BB_EINVAL; }
+  if (n == 0) return BB_OK;
+  bb::k_beta_fill<<<bb::grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(alpha, seed, n, out_dev);
+  BB_CUDA(cudaGetLastError());
+  return BB_OK;
+}

@@ -255,7 +255,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     idx = q; q += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
     q = (q + 15) & ~15;
     st = q; q += Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);   // the batch's packed states, staged once
-    zb = q; if (G::A > 32) q += G::A * 4;          // wide policy heads: one row of logits / probabilities (heads_finish)
+    zb = q; q += (G::A > 32 ? G::A : Ge::NP * G::A) * 4;   // wide policy heads: one row of logits / probabilities; narrow ones: the batch's noise draws (heads_finish)
     claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     q = (q + 7) & ~7;
     mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
@@ -456,9 +456,16 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           const unsigned tk = ticket0 + (unsigned)tid;
           volatile unsigned long long* ent = reinterpret_cast<volatile unsigned long long*>(&sv.q_ent[tk & sv.q_mask]);
           unsigned long long v = *ent;
-          for (unsigned spin = 0; !((unsigned)v == tk && ((unsigned)(v >> 32) & RING_PUBLISHED)) && spin < (64u << 20); ++spin) v = *ent;
-          const int slot = (int)((unsigned)(v >> 32) & ~RING_PUBLISHED);
-          *ent = v & 0x7FFFFFFFFFFFFFFFull;                  // entry read: ticket tk + ring may publish here
+          unsigned spin = 0;
+          for (; !((unsigned)v == tk && ((unsigned)(v >> 32) & RING_PUBLISHED)) && spin < (64u << 20); ++spin) v = *ent;
+          int slot = (int)((unsigned)(v >> 32) & ~RING_PUBLISHED);
+          if (spin >= (64u << 20)) {                         // the ticket was issued (tail moved past it) but its entry never appeared: report, never serve garbage
+            printf("[bbengine] streaming watchdog: ring entry of ticket %u never published (entry holds ticket %u, word %08x)\n", tk, (unsigned)v, (unsigned)(v >> 32));
+            *reinterpret_cast<volatile unsigned*>(&sv.q->stop) = 2u;
+            slot = 0;                                        // any valid slot: the call returns BB_ESTATE and the results are discarded
+          } else {
+            *ent = v & 0x7FFFFFFFFFFFFFFFull;                // entry read: ticket tk + ring may publish here
+          }
           __threadfence();                                   // acquire: the slot's state was written before the entry
           src = reinterpret_cast<const State*>(sv.q_state) + slot;
           sIdx[tid] = slot;                                  // where the answer goes
@@ -577,7 +584,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
       heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
-                      G::A > 32 ? reinterpret_cast<float*>(pb_ + L.zb) : nullptr);
+                      reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll);
     }
     if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
       __threadfence();

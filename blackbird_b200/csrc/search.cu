@@ -72,6 +72,17 @@ __global__ void k_stream_arm(StreamCtl* q, unsigned search_ctas, unsigned server
   q->goal_moves = goal;
 }
 
+// Do two kernels on two streams really run at the same time?  A waits (up to ~50 ms) for a flag that only B sets.  Under a
+// profiler that serialises kernel launches (ncu kernel replay) B starts after A has given up: the persistent
+// search / network pair cannot work there (each side would wait for the other until its watchdog fires).
+__global__ void k_probe_wait(volatile unsigned* flag, unsigned* seen) {
+  const long long t0 = clock64();
+  unsigned v = 0;
+  while (!(v = *flag) && clock64() - t0 < 100000000ll) __nanosleep(1000);
+  *seen = v;
+}
+__global__ void k_probe_set(volatile unsigned* flag) { *flag = 1u; }
+
 }  // namespace bb
 
 using namespace bb;
@@ -108,6 +119,7 @@ struct bb_engine {
   virtual int n_lanes() = 0;
   virtual int streaming() = 0;
   virtual int stream_stats(uint64_t*) = 0;
+  virtual int stream_answers(void*, float*, float*, uint32_t*) = 0;
 };
 
 template <class G>
@@ -453,6 +465,9 @@ struct EngineT : bb_engine {
     if (cfg.evaluator != BB_EVAL_NET || !net || !net_is_tc(net)) return false;
     const char* e = getenv("BB_STREAM");
     if (e && atoi(e) == 0) return false;
+    // every slot must be owned by a warp of ONE co-resident wave of search CTAs (a second wave would start only
+    // after the first has left, and its slots would sit idle for whole games)
+    if ((long long)d.n_games > (long long)net_sm_count(net) * STREAM_WARPS_PER_CTA * STREAM_MAX_OWN) return false;
     if (stream_fits < 0) {
       int nregs = 0, nsmem = 0;
       cudaFuncAttributes fa{};
@@ -477,10 +492,8 @@ struct EngineT : bb_engine {
     EngineDev<G> e = d;
     e.q = q_dev;
     const int sms = net_sm_count(net);
-    const int per_cta = STREAM_WARPS_PER_CTA * STREAM_MAX_OWN;
     int grid = (d.n_games + STREAM_WARPS_PER_CTA - 1) / STREAM_WARPS_PER_CTA;
     if (grid > sms) grid = sms;
-    if ((long long)grid * per_cta < d.n_games) grid = (d.n_games + per_cta - 1) / per_cta;
     if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
     int div = sms;                                                                          // a claim takes open / div tickets (1 .. NP); div = pipelines serving
     if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : div;
@@ -768,6 +781,18 @@ struct EngineT : bb_engine {
     if (do_reset) { BB_CUDA(cudaMemset(counters_dev, 0, c.size() * sizeof(Counters))); host_ticks = host_launches = 0; }
     return BB_OK;
   }
+  // streaming mode keeps, per slot, the last state it asked about and the network's answer to it
+  int stream_answers(void* st, float* pol, float* val, uint32_t* seq) override {
+    if (!use_stream()) { set_error("bb_stream_last_answers: the engine is not in streaming mode"); return BB_ESTATE; }
+    int rc = sync_lanes();
+    if (rc) return rc;
+    const size_t n = d.n_games;
+    if (st) BB_CUDA(cudaMemcpy(st, d.q_state, n * sizeof(State), cudaMemcpyDeviceToHost));
+    if (pol) BB_CUDA(cudaMemcpy(pol, d.resp_policy, n * G::A * sizeof(float), cudaMemcpyDeviceToHost));
+    if (val) BB_CUDA(cudaMemcpy(val, d.resp_value, n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (seq) BB_CUDA(cudaMemcpy(seq, d.resp_seq, n * sizeof(unsigned), cudaMemcpyDeviceToHost));
+    return BB_OK;
+  }
   int n_lanes() override { return (int)lanes.size(); }
   int streaming() override { return use_stream() ? 1 : 0; }
   int stream_stats(uint64_t* out) override {
@@ -859,5 +884,25 @@ int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); re
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
 int bb_engine_streaming(bb_engine* e) { BB_NEED(e); return e->streaming(); }
 int bb_stream_stats(bb_engine* e, uint64_t out[8]) { BB_NEED(e); if (!out) return BB_EINVAL; return e->stream_stats(out); }
+int bb_stream_last_answers(bb_engine* e, void* st, float* pol, float* val, uint32_t* seq) { BB_NEED(e); return e->stream_answers(st, pol, val, seq); }
+int bb_debug_kernels_concurrent(int device) {
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice(%d) failed", device); return BB_ECUDA; }
+  unsigned* buf = nullptr;
+  cudaStream_t a = nullptr, b = nullptr;
+  BB_CUDA(cudaMalloc(&buf, 2 * sizeof(unsigned)));
+  BB_CUDA(cudaMemset(buf, 0, 2 * sizeof(unsigned)));
+  BB_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+  BB_CUDA(cudaStreamCreateWithFlags(&b, cudaStreamNonBlocking));
+  k_probe_wait<<<1, 1, 0, a>>>(buf, buf + 1);
+  k_probe_set<<<1, 1, 0, b>>>(buf);
+  unsigned seen = 0;
+  cudaError_t e1 = cudaStreamSynchronize(a), e2 = cudaStreamSynchronize(b);
+  if (e1 == cudaSuccess && e2 == cudaSuccess) e1 = cudaMemcpy(&seen, buf + 1, sizeof seen, cudaMemcpyDeviceToHost);
+  cudaStreamDestroy(a);
+  cudaStreamDestroy(b);
+  cudaFree(buf);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) { set_error("concurrency probe failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2)); return BB_ECUDA; }
+  return seen ? 1 : 0;
+}
 
 }  // extern "C"

@@ -289,8 +289,14 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
           } else {
             double u;
             NodeHdr dummy;
+            dummy.meta = 0;
             j = puct_select<SelectChunks<G>::N>(nodes + rh.child_base, k, E.c, &u, &dummy);
+            // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
+            if (j != 0x7FFFFFFF && !(u > 0.0) && j < meta_action(dummy.meta)) j = 0x7FFFFFFF;
           }
+          // a root without children (no legal move and no winner: a stalemated DragonChess position) or without a
+          // candidate (every prior NaN): the reference trips `assert root.LegalActions[choice] == 1` (MCTS.py:341)
+          if (rh.child_base == NONE || k == 0 || j < 0 || j >= k) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
           play_move(E, s, g, nodes, j, &n_done);
           n_moves += 1;
           if (s.moves_budget > 0) s.moves_budget -= 1;
@@ -365,7 +371,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
 // advanced until it blocks again (or its step budget ends).  Nothing here is a barrier between slots, so a
 // slot costs one network batch of latency per evaluation instead of one engine-wide tick.  Results do not
 // depend on the interleaving: each slot's tree is private and the evaluator is a pure function.
-constexpr int STREAM_MAX_OWN = 32;      // slots per warp
+constexpr int STREAM_MAX_OWN = 64;      // slots per warp (65536 slots on 148 SMs x 12 warps need 37)
 constexpr unsigned STREAM_WATCHDOG_SPINS = 4u << 20;   // idle polls (~0.5 us each) before a warp gives up
 
 template <class G>

@@ -116,6 +116,20 @@ def kat_forward(game, states):
     return pol, val
 
 
+def beta_noise(alpha, seed, n, device=0):
+    """n draws of the network kernels' policy-noise sampler, Beta(alpha, 1 - alpha) (NetworkFactory.py:176-180)."""
+    _need_cuda()
+    out = torch.empty((n,), dtype=torch.float32, device=_dev(device))
+    check(lib.bb_debug_beta_noise(float(alpha), int(seed), int(n), _ptr(out), _stream()))
+    return out
+
+
+def kernels_concurrent(device=0):
+    """False when kernel launches are being serialised (a profiler in kernel-replay mode is attached)."""
+    _need_cuda()
+    return bool(check(lib.bb_debug_kernels_concurrent(int(device))))
+
+
 def default_node_cap(game, search, play_limit, max_depth=10):
     """Nodes per half-arena: one move's growth plus the subtree carried over MoveRoot.
 
@@ -168,6 +182,15 @@ class Engine(object):
         out = (C.c_uint64 * 8)()
         check(lib.bb_stream_stats(self._h, out))
         return dict(zip(('batches', 'cyc_wait', 'cyc_tower', 'cyc_heads', 'pipelines', 'cyc_search_busy', 'cyc_search_total', 'search_calls'), [int(x) for x in out]))
+
+    def stream_last_answers(self):
+        """Per slot: the last state asked through the request ring and the serve-mode network's answer to it
+        -> (states uint8[n, S], policy f32[n, A], value f32[n], seq uint32[n]; seq 0 = the slot never asked)."""
+        n = self.n_games
+        st, pol = np.empty((n, self.state_bytes), np.uint8), np.empty((n, self.A), np.float32)
+        val, seq = np.empty(n, np.float32), np.empty(n, np.uint32)
+        check(lib.bb_stream_last_answers(self._h, *(a.ctypes.data_as(C.c_void_p) for a in (st, pol, val, seq))))
+        return st, pol, val, seq
 
     def close(self):
         if getattr(self, '_h', None):

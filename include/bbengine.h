@@ -103,6 +103,10 @@ int bb_net_load(bb_engine* e, const bb_net_desc* d, const float* weights_host, s
 /* Network.getPolicy + getEvaluation for n packed states: policy f32[n][A] (softmax, noise,
  * renormalised), value f32[n] (tanh). */
 int bb_net_forward(bb_engine* e, const void* states_dev, int n, float* policy_dev, float* value_dev, void* stream);
+/* n draws of the policy-noise sampler the network kernels use: dist.sample([1, A])[0][:, 0] of Dirichlet([alpha,
+ * 1 - alpha]) = Beta(alpha, 1 - alpha) per action (NetworkFactory.py:176-180).  TensorFlow's stream cannot
+ * be matched, so the tests check the distribution itself (Kolmogorov-Smirnov against the Beta cdf). */
+int bb_debug_beta_noise(float alpha, uint64_t seed, int n, float* out_dev, void* stream);
 /* Appendix B.2 integer evaluator, same signature (parity vehicle). */
 int bb_kat_forward(int game, const void* states_dev, int n, float* policy_dev, float* value_dev, void* stream);
 
@@ -192,6 +196,18 @@ int bb_engine_streaming(bb_engine* e);
  * pipelines); out[4] pipelines x SMs serving; out[5..7] search warps: cycles inside the per-slot advance routine, cycles
  * resident, advance calls.  Zeros in tick mode.  bench.py turns them into busy fractions. */
 int bb_stream_stats(bb_engine* e, uint64_t out[8]);
+/* Streaming mode keeps, per slot, the last position it asked the network about and the answer it got (the serve-mode
+ * path of Network.getPolicy / getEvaluation, Network.py:48-64).  After a self-play call that ran to completion every
+ * request has been answered, so (state[s], policy[s], value[s]) are evaluator input / output pairs produced through the
+ * request ring: the parity tests compare them with the oracle forward.  Host buffers: states [n_games][state_bytes],
+ * policy [n_games][A], value [n_games], seq [n_games] (ticket + 1 of the last answer; 0 = the slot never asked).
+ * BB_ESTATE when the engine is not in streaming mode. */
+int bb_stream_last_answers(bb_engine* e, void* states_host, float* policy_host, float* value_host, uint32_t* seq_host);
+/* 1 when two kernels on two streams run concurrently on this device, 0 when launches are being serialised (a
+ * profiler in kernel-replay mode): the persistent search / network pair of streaming mode needs real concurrency
+ * (each side waits for the other), so under such a profiler a streaming call ends in the engine's watchdog
+ * (BB_ESTATE) instead of a result.  Diagnostic only; the engine never changes its path on it. */
+int bb_debug_kernels_concurrent(int device);
 
 #ifdef __cplusplus
 }

@@ -119,13 +119,19 @@ class NetEvaluator(object):
     """Network.getPolicy/getEvaluation (Network.py:48-64) served by the restatement at batch 1,
     fp32, eps = 0 (no noise): the evaluator of the CPU baseline and of replay-parity tests."""
 
-    def __init__(self, weights, eps=0.0, dtype=np.float32):
+    def __init__(self, weights, eps=0.0, dtype=np.float32, alpha=0.2, rng=None):
         self.W = weights
         self.Eps = eps
         self.Dtype = dtype
+        self.Alpha = alpha
+        self.Rng = rng                      # eps > 0 and an rng: a fresh Beta(alpha, 1-alpha) draw per action per call (A.17)
 
     def getPolicy(self, planes):
-        return forward(self.W, planes, self.Eps, None, self.Dtype)[0][0].astype(np.float32)
+        noise = None
+        if self.Eps > 0 and self.Rng is not None:
+            A = self.W['policy.d.b'].shape[0]
+            noise = self.Rng.beta(self.Alpha, 1.0 - self.Alpha, size=(planes.shape[0], A))
+        return forward(self.W, planes, self.Eps, noise, self.Dtype)[0][0].astype(np.float32)
 
     def getEvaluation(self, planes):
         return np.float32(forward(self.W, planes, self.Eps, None, self.Dtype)[1][0])
@@ -134,3 +140,98 @@ class NetEvaluator(object):
 def flatten_weights(weights):
     """Flat fp32 vector in dict order: the layout bb_net_load() takes."""
     return np.concatenate([np.asarray(v, dtype=np.float32).ravel() for v in weights.values()])
+
+
+# ---- second implementation: the same graph through torch.nn.functional (CPU, fp64) -------------------
+def forward_torch(weights, planes, dtype=None):
+    """The graph of NetworkFactory.py:22-183 restated with torch's own layer kernels (conv2d with
+    padding='same', batch_norm(training=False, eps=1e-3), linear) instead of the hand-written numpy
+    loops above: an independent implementation of the layer semantics (NHWC/HWIO -> NCHW/OIHW
+    conversion, zero padding, BN inference formula, dense on the last axis) that pins forward()
+    against a layout or padding slip.  Test infrastructure only (tests/test_oracle_network.py)."""
+    import torch
+    import torch.nn.functional as F
+    dt = dtype or torch.float64
+    T = lambda a: torch.as_tensor(np.asarray(a, dtype=np.float64)).to(dt)
+
+    def conv_bn(x, name):
+        k = T(weights[name + '.w']).permute(3, 2, 0, 1).contiguous()          # HWIO -> OIHW
+        y = F.conv2d(x, k, T(weights[name + '.b']), stride=1, padding='same')
+        return F.batch_norm(y, T(weights[name + '.mean']), T(weights[name + '.var']), T(weights[name + '.gamma']),
+                            T(weights[name + '.beta']), training=False, eps=BN_EPS)
+
+    x = T(planes).permute(0, 3, 1, 2).contiguous()                             # NHWC -> NCHW
+    x = F.relu(conv_bn(x, 'stem'))
+    b = 0
+    while 'block%d.c1.w' % b in weights:
+        y = F.relu(conv_bn(x, 'block%d.c1' % b))
+        y = conv_bn(y, 'block%d.c2' % b)
+        x = F.relu(y + x)
+        b += 1
+    v = F.relu(conv_bn(x, 'value.conv')).permute(0, 2, 3, 1)                    # [N,H,W,1]
+    v = F.linear(v, T(weights['value.d1.w']).t(), T(weights['value.d1.b']))     # dense on the last axis, bias per cell
+    v = F.relu(v.sum(dim=(1, 2)))
+    v = F.linear(v, T(weights['value.d2.w']).t(), T(weights['value.d2.b']))
+    value = torch.tanh(v.sum(dim=1))
+    p = F.relu(conv_bn(x, 'policy.conv')).permute(0, 2, 3, 1)                   # [N,H,W,2]
+    p = F.linear(p, T(weights['policy.d.w']).t(), T(weights['policy.d.b'])).sum(dim=(1, 2))
+    return torch.softmax(p, dim=1).numpy(), value.numpy()
+
+
+# ---- the bf16 tensor-core kernel's arithmetic, restated on the CPU ------------------------------------
+def _bf16_rn(a):
+    """fp32 -> bf16 (round to nearest even) -> fp32, elementwise."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32).reshape(np.shape(a))
+
+
+def forward_bf16_emulated(weights, planes):
+    """What blackbird_b200/csrc/net_tc.cuh computes, with its rounding points: BN folded into the
+    convolutions in double and stored as bf16 tower weights / fp32 biases (net.cu net_build), bf16
+    activations between tower layers (fp32 accumulation, + fp32 bias, + bf16 skip, ReLU, round), the last
+    tower layer kept in fp32 for the heads, heads in fp32.  Only the accumulation ORDER differs from the
+    kernel, so the kernel must agree with this far more tightly (~1e-3 of a probability: a rare bf16
+    rounding flip of one activation) than with the fp64 graph (2e-2).  Test infrastructure only."""
+    f32 = np.float32
+    w = {k: np.asarray(v, dtype=np.float64) for k, v in weights.items()}
+
+    def fold(name):
+        s = w[name + '.gamma'] / np.sqrt(w[name + '.var'] + 1e-3)
+        return (w[name + '.w'] * s).astype(f32), ((w[name + '.b'] - w[name + '.mean']) * s + w[name + '.beta']).astype(f32)
+
+    def conv(x, k, b):                      # x bf16-valued fp32 [N,H,W,Ci]; k bf16-valued; fp32 accumulate (products exact)
+        return (_conv_same(x.astype(np.float64), k.astype(np.float64), 0.0)).astype(f32) + b
+
+    relu = lambda t: np.maximum(t, f32(0))
+    names = ['stem']
+    b = 0
+    while 'block%d.c1.w' % b in w:
+        names += ['block%d.c1' % b, 'block%d.c2' % b]
+        b += 1
+    x = planes.astype(f32)                  # -1/0/1: exact in bf16
+    act = None                              # fp32 value of the last layer
+    for li, name in enumerate(names):
+        k, bias = fold(name)
+        y = conv(x, _bf16_rn(k), bias)
+        if li > 0 and li % 2 == 0:          # conv_2 + BN + block input (the bf16 copy in shared memory)
+            y = y + skip
+        act = relu(y)
+        x = _bf16_rn(act)
+        if li % 2 == 0:
+            skip = x
+    x = act                                 # heads read the fp32 registers of the last epilogue
+    kv, bv = fold('value.conv')
+    kp, bp = fold('policy.conv')
+    hv = relu(x @ kv[0, 0] + bv).sum(axis=(1, 2))[:, 0]                        # s = sum_hw relu(bn(conv))
+    hp = relu(x @ kp[0, 0] + bp).sum(axis=(1, 2))                              # [N,2]
+    hw = f32(planes.shape[1] * planes.shape[2])
+    d1w, d1b = w['value.d1.w'].astype(f32)[0], w['value.d1.b'].astype(f32)
+    d2w, d2b = w['value.d2.w'].astype(f32)[:, 0], w['value.d2.b'].astype(f32)[0]
+    h = relu(hv[:, None] * d1w + hw * d1b)
+    value = np.tanh((h * d2w).sum(axis=1) + d2b)
+    pw, pb = w['policy.d.w'].astype(f32), w['policy.d.b'].astype(f32)
+    z = hp[:, 0:1] * pw[0] + hp[:, 1:2] * pw[1] + hw * pb
+    z = z - z.max(axis=1, keepdims=True)
+    e = np.exp(z.astype(np.float64))
+    return (e / e.sum(axis=1, keepdims=True)), value.astype(np.float64)

@@ -75,6 +75,93 @@ def test_forward_vs_fp64(mods, game, n, jitter):
     eng.close()
 
 
+BF16_TOL = 2e-2     # north_star: "2e-2 in bf16" -- absolute, on probabilities (scale [0,1]) and on the value (scale [-1,1])
+BF16_EMU_TOL = 2e-3  # against the CPU restatement of the kernel's own rounding points (accumulation order is the only difference)
+TC_NP = {'TicTacToe': 56, 'Connect4': 14, 'DragonChess': 4}     # positions per batch of one pipeline (net_tc.cuh TcBatch)
+
+
+def _check_bf16(tag, w, planes, got_p, got_v):
+    """bf16 tcgen05 outputs vs (1) the fp64 graph at the stated tolerance and (2) the CPU restatement of the kernel's
+    rounding points, which pins taps, BN folding, skip connections and head wiring an order of magnitude tighter."""
+    got_p, got_v = got_p.astype(np.float64), got_v.astype(np.float64)
+    want_p, want_v = network_np.forward(w, planes, dtype=np.float64)
+    emu_p, emu_v = network_np.forward_bf16_emulated(w, planes)
+    e64p, e64v = np.abs(got_p - want_p).max(), np.abs(got_v - want_v).max()
+    big = want_p > 1e-3
+    rel = (np.abs(got_p - want_p) / np.maximum(want_p, 1e-30))[big].max() if big.any() else 0.0
+    eep, eev = np.abs(got_p - emu_p).max(), np.abs(got_v - emu_v).max()
+    print('[bf16 parity] %s n=%d: vs fp64 oracle policy abs %.3e (rel %.3e where p>1e-3) value abs %.3e; vs bf16 restatement policy abs %.3e value abs %.3e'
+          % (tag, planes.shape[0], e64p, rel, e64v, eep, eev))
+    assert np.abs(got_p.sum(axis=1) - 1).max() < 1e-5
+    assert e64p <= BF16_TOL and e64v <= BF16_TOL, (tag, e64p, e64v)
+    assert eep <= BF16_EMU_TOL and eev <= BF16_EMU_TOL, (tag, eep, eev)
+    return e64p, rel, e64v
+
+
+@pytest.mark.parametrize('game,n_states', [('TicTacToe', 1000), ('Connect4', 1200), ('DragonChess', 1000)])
+@pytest.mark.parametrize('jitter,seed', [(0.0, 0), (0.2, 4)])
+def test_bf16_launch_mode_vs_fp64(mods, game, n_states, jitter, seed):
+    """The benchmarked kernel, k_net_forward_tc, in launch mode (bb_net_forward, precision bf16) against the fp64
+    oracle (NetworkFactory.py:22-183) on >= 1000 playout positions, at batch sizes that exercise a single position,
+    partial last tiles (NP-1, NP+1 positions per pipeline batch) and batches that fill every pipeline of the grid."""
+    engine, _ = mods
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=4, filters=16, dense=16, seed=seed, jitter=jitter)
+    eng = engine.Engine(game, 'dynamic', n_games=1, evaluator='net')
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, precision='bf16')
+    states = playout_states(game, n_states, seed=1)
+    dev_all = pack(engine, game, states)
+    planes_all = np.concatenate([s.AsInputArray() for s in states])
+    NP, pipes = TC_NP[game], 296
+    worst = (0.0, 0.0, 0.0)
+    for n in (1, NP - 1, NP, NP + 1, n_states, (NP - 1) * pipes + 3, NP * pipes, NP * pipes + NP + 1):
+        idx = np.arange(n) % n_states                        # large batches repeat positions at other tile offsets
+        if n > n_states and game == 'DragonChess':
+            idx = idx % 200                                  # 4032-wide rows: keep the oracle's work bounded
+        dev = dev_all[torch.as_tensor(idx, device=dev_all.device)]
+        pol, val = eng.net_forward(dev)
+        uniq = np.unique(idx)
+        gp, gv = pol.cpu().numpy(), val.cpu().numpy()
+        # the same position gives the same bits wherever it sits in a batch
+        first = {int(i): k for k, i in reversed(list(enumerate(idx)))}
+        firsts = np.array([first[int(i)] for i in idx])
+        assert np.array_equal(gp, gp[firsts]) and np.array_equal(gv, gv[firsts])
+        sel = np.array([first[int(i)] for i in uniq])
+        r = _check_bf16('%s launch jitter=%g batch=%d' % (game, jitter, n), w, planes_all[uniq], gp[sel], gv[sel])
+        worst = tuple(max(a, b) for a, b in zip(worst, r))
+        pol2, val2 = eng.net_forward(dev)
+        assert torch.equal(pol, pol2) and torch.equal(val, val2)
+    print('[bf16 parity] %s jitter=%g WORST vs fp64: policy abs %.3e rel %.3e value abs %.3e' % ((game, jitter) + worst))
+    eng.close()
+
+
+@pytest.mark.parametrize('game,kind,P,G', [('Connect4', 'fixed', 64, 2048), ('TicTacToe', 'dynamic', 40, 1024), ('DragonChess', 'dynamic', 8, 96)])
+def test_bf16_serve_mode_vs_fp64(mods, game, kind, P, G):
+    """The same kernel in SERVE mode (persistent, batches claimed from the request ring by k_search_stream's tickets):
+    after a streaming self-play run every slot holds the last position it asked about and the answer it got
+    (bb_stream_last_answers).  Those answers must equal launch mode bit for bit and the fp64 oracle within tolerance."""
+    engine, _ = mods
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, seed=0)
+    eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P, max_plies=24 if game == 'DragonChess' else None,
+                        node_cap=16384 if game == 'DragonChess' else None)
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, precision='bf16')
+    assert eng.streaming
+    u = np.stack([np.random.RandomState(500 + g).random_sample(eng.max_plies) for g in range(G)])
+    eng.selfplay(P, 1.0, u)
+    st, pol, val, seq = eng.stream_last_answers()
+    assert (seq > 0).all()
+    dev = torch.as_tensor(st).cuda()
+    pol_l, val_l = eng.net_forward(dev)
+    assert np.array_equal(pol_l.cpu().numpy(), pol) and np.array_equal(val_l.cpu().numpy(), val)
+    planes = engine.planes(game, dev).cpu().numpy()
+    _, first = np.unique(st, axis=0, return_index=True)
+    first = first[:400] if game == 'DragonChess' else first
+    assert len(first) >= 20
+    _check_bf16('%s serve mode (%d distinct positions of %d slots)' % (game, len(first), G), w, planes[first], pol[first], val[first])
+    eng.close()
+
+
 class Replay(object):
     """Evaluator for the oracle search that replays the GPU network's own outputs (looked up by
     input planes): isolates tree-search parity from network rounding."""
@@ -233,6 +320,51 @@ def test_full_size_streaming(mods):
             got[raw['pool_actions'][g, lo:hi]] = raw['pool_plays'][g, lo:hi]
             assert np.array_equal(got, plays), (g, r, got, plays)
             assert int(raw['chosen'][g, r]) == action
+    eng.close()
+
+
+@pytest.mark.parametrize('alpha', [0.2, 0.5, 0.03, 0.9])
+def test_beta_sampler_distribution(mods, alpha):
+    """The kernels' noise sampler is Beta(alpha, 1 - alpha) (NetworkFactory.py:176-180: Dirichlet([alpha, 1 - alpha])
+    sample, first component): Kolmogorov-Smirnov against the Beta cdf, moments, and independence of the stream from the seed."""
+    engine, _ = mods
+    from scipy import stats
+    n = 200000
+    x = engine.beta_noise(alpha, 1234, n).cpu().numpy().astype(np.float64)
+    assert (x >= 0).all() and (x <= 1).all()
+    d, p = stats.kstest(x, stats.beta(alpha, 1 - alpha).cdf)
+    assert d < 0.005, (alpha, d, p)                           # 1.36 / sqrt(n) = 0.003 at the 5 % level
+    assert abs(x.mean() - alpha) < 0.004 and abs(x.var() - alpha * (1 - alpha) / 2) < 0.004
+    y = engine.beta_noise(alpha, 99, n).cpu().numpy()
+    assert abs(np.corrcoef(x, y)[0, 1]) < 0.01 and not np.array_equal(x, y)
+    assert np.array_equal(x, engine.beta_noise(alpha, 1234, n).cpu().numpy().astype(np.float64))
+
+
+@pytest.mark.parametrize('precision', ['fp32', 'bf16'])
+def test_noise_mix_against_sampler(mods, precision):
+    """policy = ((1 - eps) softmax + eps noise) / sum (NetworkFactory.py:181-182), in both network kernels: with the
+    softmax known, ratios of outputs give back the noise draws up to the common normaliser; their distribution must be
+    the sampler's."""
+    engine, _ = mods
+    from scipy import stats
+    w = network_np.init_weights(3, 7, seed=0)
+    eng = engine.Engine('Connect4', 'dynamic', n_games=1, evaluator='net')
+    eps, alpha = 0.3, 0.2
+    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, epsilon=eps, alpha=alpha, seed=7, precision=precision)
+    n = 30000
+    dev = engine.init_states('Connect4', n)
+    pol, _ = eng.net_forward(dev)
+    p = pol.cpu().numpy().astype(np.float64)
+    assert np.abs(p.sum(axis=1) - 1).max() < 1e-5
+    soft = network_np.forward(w, GAMES['Connect4']().AsInputArray(), dtype=np.float64)[0][0]
+    # the normalisation removes one degree of freedom, so the draws cannot be solved for; compare the distribution of
+    # every output component with the same mix computed on the host from the sampler's own draws (another seed)
+    nz = engine.beta_noise(alpha, 555, n * 7).cpu().numpy().astype(np.float64).reshape(n, 7)
+    m = (1 - eps) * soft + eps * nz
+    want = m / m.sum(axis=1, keepdims=True)
+    for a in range(7):
+        d = stats.ks_2samp(p[:, a], want[:, a]).statistic
+        assert d < (0.02 if precision == 'fp32' else 0.03), (a, d)     # 1.36 * sqrt(2 / n) = 0.011 at the 5 % level
     eng.close()
 
 
