@@ -111,10 +111,11 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
         # as soon as they end one (bb_selfplay_games), so the GPU stays full until the last games run out
         u = _uniform_table(nGames, eng.max_plies) if uniforms is None else np.asarray(uniforms)[:nGames]
         eng.selfplay(play_limit, float(temp), u)
-        games = _records.build_records(eng)
-        serialized = [rec for recs, _, _ in games for rec in recs]
-        model.Conn.PutGames(model.Name, model.Version, game, serialized)
-        written += len(serialized)
+        # ExampleState.SerializeState + the outcome labels run on the device (bb_records_serialize): one compact byte
+        # stream comes back and goes to the sink in ONE transaction
+        buf, off, sz = eng.records_serialized()
+        written += int(((off[1:] - off[:-1]) // sz).sum())
+        model.Conn.PutGames(model.Name, model.Version, game, _records.iter_records(buf, off, sz))
     finally:
         eng.close()
     return written

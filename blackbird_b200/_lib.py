@@ -78,6 +78,7 @@ SIGNATURES = {
     'bb_records_pool_cap': (I, [VP]),
     'bb_records_export': (I, [VP, VP, VP, VP, VP, VP, VP, VP]),
     'bb_records_device': (I, [VP] + [C.POINTER(VP)] * 7),
+    'bb_records_serialize': (I, [VP, VP, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), VP, VP]),
     'bb_counters_read': (I, [VP, C.POINTER(bb_counters), I]),
     'bb_engine_lanes': (I, [VP]),
     'bb_engine_streaming': (I, [VP]),

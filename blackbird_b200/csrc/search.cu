@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "search_kernels.cuh"
+#include "records.cuh"
 
 namespace bb {
 
@@ -120,6 +121,7 @@ struct bb_engine {
   virtual int streaming() = 0;
   virtual int stream_stats(uint64_t*) = 0;
   virtual int stream_answers(void*, float*, float*, uint32_t*) = 0;
+  virtual int records_serialize(void*, uint64_t, uint64_t*, uint64_t*, uint64_t*, uint32_t*) = 0;
 };
 
 template <class G>
@@ -767,6 +769,41 @@ struct EngineT : bb_engine {
     if (ch) *ch = d.chosen;
     return BB_OK;
   }
+  // ExampleState.SerializeState + labels for every record of the last self-play call, on the device (records.cuh)
+  int records_serialize(void* out_dev, uint64_t cap, uint64_t* n_records, uint64_t* n_bytes, uint64_t* game_off_host, uint32_t* rec_bytes_host) override {
+    using F = RecFmt<G>;
+    BB_CUDA(cudaSetDevice(cfg.device));
+    int rc = sync_lanes();
+    if (rc) return rc;
+    const size_t rows = rows_last;
+    std::vector<int32_t> nm(rows), win(rows);
+    BB_CUDA(cudaMemcpy(nm.data(), d.n_moves, rows * 4, cudaMemcpyDeviceToHost));
+    BB_CUDA(cudaMemcpy(win.data(), d.winners, rows * 4, cudaMemcpyDeviceToHost));
+    std::vector<unsigned long long> off(rows + 1);
+    unsigned long long bytes = 0, recs = 0;
+    for (size_t g = 0; g < rows; ++g) {
+      const uint32_t sz = (uint32_t)F::SIZE0 + ((win[g] == WIN_P1 || win[g] == WIN_P2) ? 5u : 0u);
+      off[g] = bytes;
+      bytes += (unsigned long long)(nm[g] + 1) * sz;
+      recs += (unsigned long long)(nm[g] + 1);
+      if (rec_bytes_host) rec_bytes_host[g] = sz;
+    }
+    off[rows] = bytes;
+    if (n_records) *n_records = recs;
+    if (n_bytes) *n_bytes = bytes;
+    if (game_off_host) memcpy(game_off_host, off.data(), (rows + 1) * sizeof(unsigned long long));
+    if (!out_dev) return BB_OK;                                // size query
+    if (cap < bytes) { set_error("bb_records_serialize: buffer of %llu bytes, %llu needed", (unsigned long long)cap, bytes); return BB_EINVAL; }
+    if (rows == 0) return BB_OK;
+    if ((rc = ensure_scratch((rows + 1) * sizeof(unsigned long long)))) return rc;
+    BB_CUDA(cudaMemcpyAsync(scratch, off.data(), (rows + 1) * sizeof(unsigned long long), cudaMemcpyHostToDevice, stream));
+    const size_t smem = pack_records_smem<G>();
+    k_pack_records<G><<<(unsigned)rows, 128, smem, stream>>>(d, (int)rows, (const unsigned long long*)scratch, (uint8_t*)out_dev);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    host_launches++;
+    return BB_OK;
+  }
   int counters(bb_counters* out, int do_reset) override {
     std::vector<Counters> c(lanes.size());
     int rc = sync_lanes();
@@ -879,6 +916,10 @@ int bb_records_export(bb_engine* e, int32_t* nm, int32_t* win, void* st, uint32_
 int bb_records_device(bb_engine* e, void** nm, void** win, void** st, void** off, void** pa, void** pp, void** ch) {
   BB_NEED(e);
   return e->records_device(nm, win, st, off, pa, pp, ch);
+}
+int bb_records_serialize(bb_engine* e, void* out_dev, uint64_t cap, uint64_t* n_records, uint64_t* n_bytes, uint64_t* game_off_host, uint32_t* rec_bytes_host) {
+  BB_NEED(e);
+  return e->records_serialize(out_dev, cap, n_records, n_bytes, game_off_host, rec_bytes_host);
 }
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }

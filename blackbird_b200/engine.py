@@ -359,6 +359,22 @@ class Engine(object):
                                     p('pool_plays'), p('chosen')))
         return out
 
+    def records_serialized(self, to_host=True):
+        """Every record of the last self-play call as final protobuf bytes, packed on the device (bb_records_serialize).
+        -> (bytes: numpy uint8 [n_bytes] (or the device tensor with to_host=False), game_off uint64 [rows+1],
+        rec_bytes uint32 [rows]); record r of game g is bytes[game_off[g] + r * rec_bytes[g] :][: rec_bytes[g]]."""
+        rows = self.rec_rows
+        n_rec, n_bytes = C.c_uint64(), C.c_uint64()
+        off, sz = np.empty(rows + 1, np.uint64), np.empty(rows, np.uint32)
+        check(lib.bb_records_serialize(self._h, None, 0, C.byref(n_rec), C.byref(n_bytes), off.ctypes.data_as(C.c_void_p), sz.ctypes.data_as(C.c_void_p)))
+        buf = torch.empty((int(n_bytes.value),), dtype=torch.uint8, device=_dev(self.device))
+        check(lib.bb_records_serialize(self._h, _ptr(buf), buf.numel(), None, None, None, None))
+        if not to_host:
+            return buf, off, sz
+        host = torch.empty((buf.numel(),), dtype=torch.uint8, pin_memory=True)
+        host.copy_(buf)
+        return host.numpy(), off, sz
+
     def counters(self, reset=False):
         c = _lib.bb_counters()
         check(lib.bb_counters_read(self._h, C.byref(c), int(reset)))

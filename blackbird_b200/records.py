@@ -78,3 +78,22 @@ def build_records(eng, raw=None):
             k += 1
         out.append((recs, winner, int(n_moves[g])))
     return out
+
+
+def split_records(buf, game_off, rec_bytes):
+    """Compact record stream (Engine.records_serialized) -> list over games of list[bytes] (what PutGames takes)."""
+    mv = memoryview(np.ascontiguousarray(buf)).cast('B')
+    out = []
+    for g in range(len(rec_bytes)):
+        lo, hi, sz = int(game_off[g]), int(game_off[g + 1]), int(rec_bytes[g])
+        out.append([bytes(mv[o:o + sz]) for o in range(lo, hi, sz)])
+    return out
+
+
+def iter_records(buf, game_off, rec_bytes):
+    """The same records as one flat generator of bytes objects (sqlite parameter stream), no per-game lists."""
+    mv = memoryview(np.ascontiguousarray(buf)).cast('B')
+    for g in range(len(rec_bytes)):
+        sz = int(rec_bytes[g])
+        for o in range(int(game_off[g]), int(game_off[g + 1]), sz):
+            yield bytes(mv[o:o + sz])

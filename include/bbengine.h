@@ -181,6 +181,17 @@ int bb_records_export(bb_engine* e, int32_t* n_moves_host, int32_t* winner_host,
 int bb_records_device(bb_engine* e, void** n_moves_dev, void** winner_dev, void** states_dev,
                       void** rec_off_dev, void** pool_actions_dev, void** pool_plays_dev, void** chosen_dev);
 
+/* ExampleState.SerializeState (Blackbird.py:68-81, proto/state.proto:3-9) with the outcome labels of
+ * GenerateTrainingSamples (Blackbird.py:260-264), on the device: every record of the last self-play call as its final
+ * protobuf bytes, game after game (row order), record after record, in ONE compact stream -- what Connection.PutGames
+ * stores (DataManager.py:41-50) and what the ranks all-gather for the trainer.  All records of a game have the same
+ * size (Connect4: 200 bytes with a label, 195 for draws), so record r of game g starts at
+ * game_off_host[g] + r * rec_bytes_host[g]; game g has (game_off_host[g+1] - game_off_host[g]) / rec_bytes_host[g]
+ * records.  out_dev == NULL only reports the sizes (n_records, n_bytes, game_off_host [rows+1], rec_bytes_host [rows];
+ * any of them may be NULL). */
+int bb_records_serialize(bb_engine* e, void* out_dev, uint64_t cap_bytes, uint64_t* n_records, uint64_t* n_bytes,
+                         uint64_t* game_off_host, uint32_t* rec_bytes_host);
+
 /* ---- counters (sims, evals, nodes, depth, expansions, launches) ------------- */
 typedef struct bb_counters {
   uint64_t sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;

@@ -88,6 +88,8 @@ def test_selfplay_vs_oracle(mods, game, kind, P, n_games):
     eng.selfplay(P, 1.0, u)
     got = records.build_records(eng)
     raw = eng.records_raw()
+    packed = records.split_records(*eng.records_serialized())       # the same bytes from the device-side packer
+    assert packed == [r[0] for r in got]
     tot_sims = 0
     for g in range(n_games):
         s = search_np.NetSearch(search_np.KatEvaluator(eng.A), kind, maxDepth=10, explorationRate=0.85, playLimit=P,
@@ -122,6 +124,9 @@ def test_more_games_than_slots(mods, game, kind, P, slots, rows):
         want, winner, trace = selfplay_np.play_game(s, GAMES[game], 1)
         assert got[g][0] == want, (game, kind, g)
         assert got[g][1] == int(winner)
+    buf, off, sz = eng.records_serialized()
+    assert records.split_records(buf, off, sz) == [r[0] for r in got]
+    assert list(records.iter_records(buf, off, sz)) == [x for r in got for x in r[0]] and int(off[-1]) == len(buf)
     assert eng.counters()['games_done'] == rows
     # the engine is reusable afterwards, with fewer rows again
     eng.selfplay(P, 1.0, u[:slots])
@@ -138,6 +143,8 @@ def test_selfplay_record_goldens(mods, golden):
         eng.selfplay(case['playLimit'], 1.0, u)
         recs = records.build_records(eng)[0][0]
         assert [r.hex() for r in recs] == case['records'], (case['game'], case['kind'], case['seed'])
+        packed = records.split_records(*eng.records_serialized())[0]      # k_pack_records: SerializeState on the device
+        assert [r.hex() for r in packed] == case['records'], (case['game'], case['kind'], case['seed'])
         eng.close()
 
 
