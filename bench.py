@@ -48,6 +48,7 @@ def parse():
     ap.add_argument('--e2e-rounds', type=int, default=4, help='e2e plays this many times --games whole games per GPU on the --games slots')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-e2e-records', action='store_true')
     return ap.parse_args()
 
 
@@ -455,6 +456,52 @@ def run_ours(args):
                    'one NCCL all-gather of the record buffers + D2H' if world > 1 else 'bb_records_export', rows, G),
                'mean_moves_per_game': float(raw['n_moves'].mean()) if rank == 0 else None}
 
+    # e2e_records: the reference-facing call itself -- the mirror's GenerateTrainingSamples (Blackbird.py:219-268): engine
+    # set-up, uniforms H2D, whole games, SerializeState + labels on the device (bb_records_serialize), compact byte stream
+    # D2H, Connection.PutGames into sqlite (DataManager.py:41-50); at N > 1 one process per GPU, every rank its own
+    # sink, plus the all-gather of the compact streams for the trainer.  Everything inside the timed region.
+    e2e_records = None
+    if not args.no_e2e and not args.no_e2e_records:
+        import shutil
+        import tempfile
+        from blackbird_b200 import Blackbird as BB
+        from blackbird_b200.Connect4 import BoardState
+        from blackbird_b200.parallel import generate_training_samples_sharded
+        rows = G * max(1, args.e2e_rounds)
+        cwd, tmp = os.getcwd(), tempfile.mkdtemp(prefix='bb_bench_rank%d_' % rank)
+        os.chdir(tmp)
+        try:
+            cls = type('BenchModel', (BB.FixedModel,), {'DEVICE': local})
+            mcfg = {'maxDepth': MAX_DEPTH, 'explorationRate': C_PUCT, 'timeLimit': None, 'playLimit': P,
+                    'temperature': {'exploration': 1, 'exploitation': 0.1}}
+            ncfg = {'blocks': NET['blocks'], 'filters': NET['filters'], 'eval': {'dense': NET['dense']},
+                    'policy': {'dirichlet': {'alpha': 0.2, 'epsilon': args.epsilon}}}
+            model = cls(BoardState, 'bench', mcfg, ncfg, {})
+            model.setWeights(weights)
+            np.random.seed(1234 + rank)
+            barrier()
+            t0 = time.perf_counter()
+            written, gathered, lens = generate_training_samples_sharded(model, rows * world, 1, max_slots=G, gather=world > 1)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            lo_hi = rows                                          # games of this rank (contiguous equal blocks)
+            tt = torch.tensor([dt], dtype=torch.float64, device='cuda')
+            ss = torch.tensor([float(written - lo_hi) * P, float(lo_hi), float(written)], dtype=torch.float64, device='cuda')
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+            db_bytes = os.path.getsize(os.path.join(tmp, 'data', 'blackbird.db'))
+            e2e_records = {'value': float(ss[0].item()) / float(tt.item()), 'unit': UNIT, 'games_per_sec': float(ss[1].item()) / float(tt.item()),
+                           'records_per_sec': float(ss[2].item()) / float(tt.item()), 'records': int(ss[2].item()), 'seconds': float(tt.item()),
+                           'sqlite_bytes_rank0': int(db_bytes), 'allgather_bytes_per_rank': int(lens.max()) if lens is not None else 0,
+                           'what': 'blackbird_b200.Blackbird.GenerateTrainingSamples(model, %d games/GPU, temp 1) on %d slots/GPU: engine set-up, self-play, '
+                                   'device-side SerializeState + labels, compact stream D2H, Connection.PutGames (sqlite, one transaction per rank)%s'
+                                   % (rows, G, ', all-gather of the compact record streams' if world > 1 else '')}
+            model.Conn.Close()
+        finally:
+            os.chdir(cwd)
+            shutil.rmtree(tmp, ignore_errors=True)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, games, cores, wall = cpu_sample(args.cpu_seconds, P, args.epsilon)
@@ -468,7 +515,7 @@ def run_ours(args):
             'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
             'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
             'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
-            'roofline': dominant, 'roofline_other': other_k, 'other_noise_setting': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e,
+            'roofline': dominant, 'roofline_other': other_k, 'other_noise_setting': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e, 'e2e_records': e2e_records,
             'gpu_launches': int(launches), 'clocks': clocks}))
     if world > 1:
         dist.barrier()

@@ -82,7 +82,7 @@ def _batch_slots(game, search, play_limit, max_depth, n_games, budget_bytes=48 <
     return int(max(1, min(n_games, budget_bytes // per, 65536)))
 
 
-def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'):
+def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16', max_slots=None, _device_stream=None):
     """Blackbird.py:219-268.  Plays nGames self-play games with model's search settings and network
     and stores every example through model.Conn.PutGames.
 
@@ -100,6 +100,8 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
         raise ValueError('Not enough information to decide a stop time.')     # time-boxed search is per-object only (A.25)
     max_depth = getattr(model, 'MaxDepth', None) or 10
     slots = _batch_slots(game, search, play_limit, max_depth, nGames)
+    if max_slots:
+        slots = max(1, min(slots, int(max_slots)))         # concurrent games on the GPU (default: what the memory budget allows)
     evaluator = getattr(model, '_SELFPLAY_EVALUATOR', 'net')   # 'kat'  only in parity tests
     eng = _engine.Engine(game, search, n_games=slots, max_depth=max_depth, exploration_rate=model.ExplorationRate,
                          evaluator=evaluator, play_limit_hint=play_limit, device=model.DEVICE)
@@ -113,7 +115,12 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
         eng.selfplay(play_limit, float(temp), u)
         # ExampleState.SerializeState + the outcome labels run on the device (bb_records_serialize): one compact byte
         # stream comes back and goes to the sink in ONE transaction
-        buf, off, sz = eng.records_serialized()
+        if _device_stream is not None:                      # parallel.generate_training_samples_sharded: keep the device copy for the all-gather
+            dev, off, sz = eng.records_serialized(to_host=False)
+            _device_stream['buf'] = dev
+            buf = dev.cpu().numpy()
+        else:
+            buf, off, sz = eng.records_serialized()
         written += int(((off[1:] - off[:-1]) // sz).sum())
         model.Conn.PutGames(model.Name, model.Version, game, _records.iter_records(buf, off, sz))
     finally:

@@ -29,6 +29,12 @@ class bb_net_desc(C.Structure):
                 ('epsilon', C.c_float), ('alpha', C.c_float), ('noise_seed', C.c_uint64), ('precision', C.c_int32), ('reserved', C.c_int32 * 3)]
 
 
+class bb_train_desc(C.Structure):
+    _fields_ = [('game', C.c_int32), ('blocks', C.c_int32), ('filters', C.c_int32), ('dense', C.c_int32), ('optimizer', C.c_int32),
+                ('momentum', C.c_float), ('epsilon', C.c_float), ('alpha', C.c_float), ('noise_seed', C.c_uint64),
+                ('device', C.c_int32), ('reserved', C.c_int32 * 5)]
+
+
 class bb_counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'ticks',
                                           'kernel_launches', 'moves', 'games_done')]
@@ -79,6 +85,15 @@ SIGNATURES = {
     'bb_records_export': (I, [VP, VP, VP, VP, VP, VP, VP, VP]),
     'bb_records_device': (I, [VP] + [C.POINTER(VP)] * 7),
     'bb_records_serialize': (I, [VP, VP, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), VP, VP]),
+    'bb_trainer_create': (I, [C.POINTER(bb_train_desc), VP, C.c_size_t, C.POINTER(VP)]),
+    'bb_trainer_destroy': (I, [VP]),
+    'bb_trainer_step': (I, [VP, VP, VP, VP, I, C.c_float, VP]),
+    'bb_trainer_step_stream': (I, [VP, VP, VP, I, C.c_float, VP]),
+    'bb_trainer_losses': (I, [VP, C.POINTER(C.c_float)]),
+    'bb_trainer_weights': (I, [VP, VP, C.c_size_t]),
+    'bb_trainer_set_weights': (I, [VP, VP, C.c_size_t]),
+    'bb_trainer_grads': (I, [VP, VP, C.c_size_t]),
+    'bb_trainer_steps': (C.c_uint64, [VP]),
     'bb_counters_read': (I, [VP, C.POINTER(bb_counters), I]),
     'bb_engine_lanes': (I, [VP]),
     'bb_engine_streaming': (I, [VP]),

@@ -125,3 +125,52 @@ def selfplay_sharded(make_engine, n_games, play_limit, temp=1.0, seed0=1000, gro
         a, b = shard_range(n_games, r, world) if world > 1 else (0, n_games)
         owners.append((r * rows, b - a))
     return eng, raw_all, owners
+
+
+def allgather_serialized(buf, group=None):
+    """All-gather of the per-rank compact record streams (Engine.records_serialized(to_host=False): final protobuf
+    bytes packed on the device).  The streams differ in length, so the ranks first exchange their byte counts (one
+    8-byte all_gather), pad to the longest and gather once: the collective moves live record bytes plus at most the
+    spread between the ranks ("exchange counts first or pad to max").  Returns (gathered uint8
+    [world, max_len] on the device, lengths int64 [world] on the host); rank r's stream is gathered[r, :lengths[r]]."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return buf[None], np.array([buf.numel()], np.int64)
+    n = torch.tensor([buf.numel()], dtype=torch.int64, device=buf.device)
+    lens = torch.empty((world,), dtype=torch.int64, device=buf.device)
+    dist.all_gather_into_tensor(lens, n, group=group)
+    lens_h = lens.cpu().numpy()
+    width = int(lens_h.max())
+    width = (width + 15) // 16 * 16
+    padded = torch.zeros((width,), dtype=torch.uint8, device=buf.device)
+    padded[:buf.numel()] = buf
+    gathered = torch.empty((world * width,), dtype=torch.uint8, device=buf.device)
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    return gathered.view(world, width), lens_h
+
+
+def generate_training_samples_sharded(model, nGames, temp, group=None, seed0=None, max_slots=None, precision='bf16', gather=True):
+    """Blackbird.GenerateTrainingSamples for one process per GPU: the nGames global games are split in contiguous
+    blocks over the ranks (shard_range), every rank plays and serializes its block on its GPU and stores it through
+    ITS OWN model.Conn (one sqlite sink per rank, written in parallel), and -- with gather -- the compact record
+    streams are all-gathered so that every rank (the trainer) holds every example on its device.  seed0 keys the
+    per-game move-sampling streams by global game id (records independent of the GPU count); None draws them from
+    numpy's global stream like the reference.  Returns (records written by this rank, gathered, lengths)."""
+    from . import Blackbird as _bb
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    lo, hi = shard_range(nGames, rank, world)
+    gathered = lengths = None
+    holder = {}
+    u = None
+    if seed0 is not None:
+        from . import engine as _engine
+        u = game_uniforms(range(lo, hi), _engine._DEFAULT_PLIES[model.Game.GameType], seed0)
+    written = _bb.GenerateTrainingSamples(model, hi - lo, temp, uniforms=u, precision=precision, max_slots=max_slots,
+                                          _device_stream=holder if gather else None) if hi > lo else 0
+    if gather:
+        buf = holder.get('buf')
+        if buf is None:
+            buf = torch.empty((0,), dtype=torch.uint8, device=torch.device('cuda', model.DEVICE))
+        gathered, lengths = allgather_serialized(buf, group)
+    return written, gathered, lengths

@@ -192,6 +192,38 @@ int bb_records_device(bb_engine* e, void** n_moves_dev, void** winner_dev, void*
 int bb_records_serialize(bb_engine* e, void* out_dev, uint64_t cap_bytes, uint64_t* n_records, uint64_t* n_bytes,
                          uint64_t* game_off_host, uint32_t* rec_bytes_host);
 
+/* ---- trainer step: Network.train (Network.py:66-84) over the loss / optimizers of
+ *      NetworkFactory.py:185-245, on the GPU ------------------------------------------------------------ */
+typedef struct bb_trainer bb_trainer;
+typedef struct bb_train_desc {
+  int32_t game;                     /* BB_TICTACTOE | BB_CONNECT4 | BB_DRAGONCHESS: input planes and action count    */
+  int32_t blocks, filters, dense;   /* parameters_template.yaml:12-16                                                 */
+  int32_t optimizer;                /* 0 adam, 1 momentum, 2 gradient descent (network.training.optimizer, :229-242) */
+  float momentum;                   /* network.training.momentum (MomentumOptimizer only)                            */
+  float epsilon, alpha;             /* policy noise of the TRAINING forward (the loss sees the noisy policy, :176-194) */
+  uint64_t noise_seed;
+  int32_t device;
+  int32_t reserved[5];
+} bb_train_desc;
+/* weights_host: the flat fp32 vector of bb_net_load (DESIGN.md "weight layout"); BN moving statistics stay frozen. */
+int bb_trainer_create(const bb_train_desc* d, const float* weights_host, size_t n_floats, bb_trainer** out);
+int bb_trainer_destroy(bb_trainer* t);
+/* One sess.run(trainingOp) (Network.py:78): forward, loss as written, gradients, optimizer update.  Device pointers:
+ * planes int8 [B][H][W][C] (np.vstack of ExampleState.Board), eval f32 [B], policy f32 [B][A].  noise_host: the [A]
+ * noise vector the batch shares (tests); NULL draws it on the device when epsilon > 0. */
+int bb_trainer_step(bb_trainer* t, const int8_t* planes_dev, const float* eval_dev, const float* policy_dev, int B,
+                    float learning_rate, const float* noise_host);
+/* The same step with the batch assembled on the device from a compact record stream (bb_records_serialize output, or the
+ * all-gathered streams of every rank): rec_off_host[i] = first byte of example i.  No sqlite round trip, no host parsing. */
+int bb_trainer_step_stream(bb_trainer* t, const void* stream_dev, const uint64_t* rec_off_host, int B, float learning_rate,
+                           const float* noise_host);
+/* loss, lossEvaluation, lossPolicy, lossParam of the last step's forward (NetworkFactory.py:187-204; the summaries of :221-228) */
+int bb_trainer_losses(bb_trainer* t, float out[4]);
+int bb_trainer_weights(bb_trainer* t, float* weights_host, size_t n_floats);
+int bb_trainer_set_weights(bb_trainer* t, const float* weights_host, size_t n_floats);
+int bb_trainer_grads(bb_trainer* t, float* grads_host, size_t n_floats);     /* gradients of the last step (tests) */
+uint64_t bb_trainer_steps(bb_trainer* t);
+
 /* ---- counters (sims, evals, nodes, depth, expansions, launches) ------------- */
 typedef struct bb_counters {
   uint64_t sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
