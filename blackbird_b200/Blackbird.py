@@ -129,7 +129,40 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
 
 
 def TrainWithExamples(model, batchSize, learningRate, epochs=1, teacher=None, model_override=None, version_override=None):
-    raise NotImplementedError('the trainer (Blackbird.py:271-312) is SURVEY.md 8f-1 ("next"), not part of the self-play path')
+    """Blackbird.py:271-312: every stored example of (model, version) in a random order, truncated to a multiple of
+    batchSize, one Network.train call per batch; then Version += 1 and the new version is registered (the weights are
+    not saved, like the reference).  `epochs` is accepted and ignored, like the reference.  The permutation comes from
+    numpy's global stream exactly as np.random.choice(examples, n, replace=False) draws it (permutation(len)[:n])."""
+    states = model.Conn.GetGames(model_override if model_override is not None else model.Name,
+                                 version_override if version_override is not None else model.Version)
+    examples = [ExampleState.FromSerialized(state) for state in states]
+    n = len(examples) - (len(examples) % batchSize)
+    order = np.random.choice(len(examples), n, replace=False) if len(examples) else []
+    for i in range(n // batchSize):
+        batch = [examples[j] for j in order[i * batchSize:(i + 1) * batchSize]]
+        model.train(np.vstack([b.Board for b in batch]), np.hstack([b.MctsEval for b in batch]),
+                    np.vstack([b.MctsPolicy for b in batch]), learningRate, teacher)
+    model.Version += 1
+    model.Conn.PutModel(model.Game.GameType, model.Name, model.Version)
+
+
+def TrainOnStream(model, stream_dev, game_off, rec_bytes, batchSize, learningRate, seed=None):
+    """The same loop fed from a device-resident compact record stream (Engine.records_serialized(to_host=False), or
+    the all-gathered streams of parallel.generate_training_samples_sharded) instead of sqlite: the batches are assembled
+    on the GPU from byte offsets (bb_trainer_step_stream), no example is parsed on the host ("consuming
+    the all-gathered buffer directly").  Returns the number of batches."""
+    rec_off = np.concatenate([np.arange(int(game_off[g]), int(game_off[g + 1]), int(rec_bytes[g]), dtype=np.uint64)
+                              for g in range(len(rec_bytes))]) if len(rec_bytes) else np.zeros(0, np.uint64)
+    n = rec_off.size - (rec_off.size % batchSize)
+    rs = np.random if seed is None else np.random.RandomState(seed)
+    order = rs.choice(rec_off.size, n, replace=False) if n else []
+    if n:
+        model.train_stream(stream_dev, rec_off[order[:batchSize]], learningRate)     # creates the trainer
+        for i in range(1, n // batchSize):
+            model.train_stream(stream_dev, rec_off[order[i * batchSize:(i + 1) * batchSize]], learningRate)
+    model.Version += 1
+    model.Conn.PutModel(model.Game.GameType, model.Name, model.Version)
+    return n // batchSize
 
 
 def TestModels(model1, model2, temp, numTests):

@@ -4,11 +4,12 @@ getPolicy / getEvaluation take the reference's input array (int8 [n, H, W, C] fr
 BoardState.AsInputArray) and return policy f32 [A] / value f32 of the first row, computed by the
 engine's network kernels (bb_net_forward) -- there is no TensorFlow and no CPU path here.  Weights
 are a flat fp32 vector in the layout of netinit.py / DESIGN.md "weight layout"; a fresh Network is
-randomly initialised like tf.global_variables_initializer (Network.py:24).  train() is trainer
-side; saveModel / loadModel keep the reference's directory convention but store
+randomly initialised like tf.global_variables_initializer (Network.py:24).  train() is one GPU
+step of csrc/train.cu; saveModel / loadModel keep the reference's directory convention but store
 the flat vector (TF Saver bundles are SURVEY.md 8f-4).
 """
 import os
+import random
 
 import numpy as np
 import torch
@@ -47,6 +48,9 @@ class Network(object):
         self._net_device = device
         self._net_eng = None
         self._net_loaded_weights = None
+        self._net_trainer = None
+        self._net_dirty = False
+        self.lastLosses = None
         self.batchCount = 0
         if self.loadModel(name):                                      # Network.py:21: a saved network wins
             return
@@ -68,15 +72,18 @@ class Network(object):
             self._load_network_into(eng)
 
     def getWeights(self):
+        self._sync_weights()
         return self._net_loaded_weights
 
     def _load_network_into(self, eng, precision=None, epsilon=None, seed=0):
+        self._sync_weights()
         s = self._net_shape
         eng.load_network(self._net_loaded_weights, s.blocks, s.filters, s.dense,
                          epsilon=s.epsilon if epsilon is None else epsilon, alpha=s.alpha, seed=seed,
                          precision=precision or self.PRECISION)
 
     def _forward(self, planes):
+        self._sync_weights()
         if self._net_eng is None:
             self._net_eng = _engine.Engine(self._net_game, 'dynamic', n_games=1, evaluator='net', node_cap=64,
                                            device=self._net_device, lanes=1)
@@ -94,15 +101,54 @@ class Network(object):
         return self._forward(state)[0][0]
 
     def train(self, state, eval, policy, learningRate=0.01, teacher=None):
-        raise NotImplementedError('training (Network.py:66-84, NetworkFactory.py:185-245) is trainer side: SURVEY.md 8f-1')
+        """Network.py:66-84: one sess.run(trainingOp) on the batch (state int8 [B,H,W,C], eval [B], policy [B,A]) -- forward,
+        the loss of NetworkFactory.py:185-204 as written, gradients and the configured optimizer, all on the GPU
+        (csrc/train.cu).  The TensorBoard summary every 10th batch (:81-84) becomes self.lastLosses."""
+        if teacher is not None:
+            # NetworkFactory.py:206-219 calls tf.log (gone in TF 2) and reduces a rank-1 tensor over axis 1: the teacher term
+            # cannot run in the reference's own environment (hasTeacher is false in parameters_template.yaml)
+            raise NotImplementedError('the teacher cross-entropy term (NetworkFactory.py:206-219) does not run in the reference either')
+        if self._net_trainer is None:
+            from .trainer import Trainer
+            s = self._net_shape
+            self._net_trainer = Trainer(self._net_game, self._net_loaded_weights, s.blocks, s.filters, s.dense,
+                                        optimizer=getattr(s, 'optimizer', 'sgd'), momentum=getattr(s, 'momentum', 0.9),
+                                        epsilon=s.epsilon, alpha=s.alpha, seed=random.getrandbits(48), device=self._net_device)
+        self._net_trainer.step(state, eval, policy, learningRate)
+        self._net_dirty = True
+        self.batchCount += 1
+        if self.batchCount % 10 == 0:
+            self.lastLosses = self._net_trainer.losses()
+
+    def train_stream(self, stream_dev, rec_offsets, learningRate=0.01):
+        """One train() step whose batch is assembled on the GPU from a compact record stream (byte offsets of the examples)."""
+        if self._net_trainer is None:
+            from .trainer import Trainer
+            s = self._net_shape
+            self._net_trainer = Trainer(self._net_game, self._net_loaded_weights, s.blocks, s.filters, s.dense,
+                                        optimizer=getattr(s, 'optimizer', 'sgd'), momentum=getattr(s, 'momentum', 0.9),
+                                        epsilon=s.epsilon, alpha=s.alpha, seed=random.getrandbits(48), device=self._net_device)
+        self._net_trainer.step_stream(stream_dev, rec_offsets, learningRate)
+        self._net_dirty = True
+        self.batchCount += 1
+        if self.batchCount % 10 == 0:
+            self.lastLosses = self._net_trainer.losses()
+
+    def _sync_weights(self):
+        """Pull the trained weights back from the trainer before anything else uses them."""
+        if self._net_dirty:
+            self._net_dirty = False
+            self.setWeights(self._net_trainer.weights())
 
     def saveModel(self, name=None):
         name = name or getattr(self, 'Name', None) or self._net_name   # Network.py:90-91 uses Model.Name
+        self._sync_weights()
         saveDir = os.path.join('blackbird_models', name)
         os.makedirs(saveDir, exist_ok=True)
         s = self._net_shape
         np.savez(os.path.join(saveDir, 'best.npz'), weights=self._net_loaded_weights,
-                 shape=np.array([s.blocks, s.filters, s.dense, s.policyShape]), noise=np.array([s.epsilon, s.alpha]))
+                 shape=np.array([s.blocks, s.filters, s.dense, s.policyShape]), noise=np.array([s.epsilon, s.alpha]),
+                 training=np.array([str(getattr(s, 'optimizer', 'sgd')), str(getattr(s, 'momentum', 0.9))]))
 
     def loadModel(self, name):
         path = os.path.join('blackbird_models', name, 'best.npz')
@@ -111,7 +157,8 @@ class Network(object):
         from .NetworkFactory import NetworkFactory
         z = np.load(path)
         b, f, d, a = (int(x) for x in z['shape'])
-        self._net_shape = NetworkFactory({'blocks': b, 'filters': f, 'eval': {'dense': d},
+        training = {'optimizer': str(z['training'][0]), 'momentum': float(z['training'][1])} if 'training' in z else {}
+        self._net_shape = NetworkFactory({'blocks': b, 'filters': f, 'eval': {'dense': d}, 'training': training,
                                           'policy': {'dirichlet': {'epsilon': float(z['noise'][0]), 'alpha': float(z['noise'][1])}}}, a)
         self.setWeights(z['weights'])
         return True
@@ -120,3 +167,6 @@ class Network(object):
         eng = getattr(self, '_net_eng', None)
         if eng is not None:
             eng.close()
+        tr = getattr(self, '_net_trainer', None)
+        if tr is not None:
+            tr.close()

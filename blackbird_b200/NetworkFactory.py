@@ -1,6 +1,6 @@
 """NetworkFactory mirror: the shape description of the policy-value network
 (NetworkFactory.py:11-19 constructor arguments; the forward graph of :22-183 is the CUDA kernel
-pair in csrc/net.cu / csrc/net_tc.cuh).  The loss / optimizer half (:185-245) is trainer side."""
+pair in csrc/net.cu / csrc/net_tc.cuh; the loss / optimizer half (:185-245) is csrc/train.cu)."""
 
 
 class NetworkFactory(object):
@@ -13,3 +13,7 @@ class NetworkFactory(object):
         noise = networkConfig.get('policy', {}).get('dirichlet', {})
         self.epsilon = float(noise.get('epsilon', 0.0))
         self.alpha = float(noise.get('alpha', 0.2))
+        training = networkConfig.get('training', {}) or {}
+        self.optimizer = str(training.get('optimizer', 'sgd'))                    # NetworkFactory.py:229-242: adam | momentum | anything else = SGD
+        self.momentum = float(training.get('momentum', 0.9) or 0.0)
+        self.hasTeacher = bool(networkConfig.get('hasTeacher'))                   # NetworkFactory.py:18,206

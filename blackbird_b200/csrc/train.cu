@@ -255,6 +255,7 @@ __global__ void k_tr_heads_fwd(const float* __restrict__ a, HeadPtrs P, HeadBufs
     float o = P.d2b[0];
     for (int d = 0; d < dm.D; ++d) o += sh[d];
     B.value[n] = tanhf(o);
+    B.d_o[n] = o;                                               // pre-activation, for an accurate tanh gradient (overwritten by the backward pass)
     B.s[n] = sv;
     B.t[n * 2] = s0;
     B.t[n * 2 + 1] = s1;
@@ -330,8 +331,17 @@ __global__ void k_tr_heads_bwd(const float* __restrict__ a, const float* __restr
                                HeadPtrs P, HeadBufs B, float* __restrict__ dA, TrainDims dm, int N) {
   __shared__ float red[32];
   const int n = blockIdx.x, tid = threadIdx.x;
-  const float value = B.value[n];
-  const float d_o = 2.f * (value - evalLabel[n]) / (float)N * (1.f - value * value);
+  // d/do (tanh(o) - label)^2 / N = 2 (tanh(o) - label) sech^2(o) / N.  Saturated values (|tanh| -> 1, labels are +-1) lose
+  // every digit of 1 - value^2 and of value - label in fp32, so both factors are formed from e = exp(-2|o|) instead:
+  // sech^2 = 4 e / (1 + e)^2, 1 - tanh|o| = 2 e / (1 + e).
+  const float o = B.d_o[n], label = evalLabel[n];
+  __syncthreads();                                              // everyone has read the pre-activation before thread 0 overwrites it
+  const float e = expf(-2.f * fabsf(o)), e1 = 1.f + e;
+  const float sech2 = 4.f * e / (e1 * e1);
+  float diff = B.value[n] - label;
+  if (label == 1.f && o > 0.f) diff = -2.f * e / e1;
+  else if (label == -1.f && o < 0.f) diff = 2.f * e / e1;
+  const float d_o = 2.f * diff / (float)N * sech2;
   if (tid == 0) B.d_o[n] = d_o;
   float ds = 0.f;
   if (tid < dm.D) {

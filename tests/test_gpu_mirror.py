@@ -179,6 +179,59 @@ def test_model_network_selfplay_and_arena(bb, tmp_path, monkeypatch):
     model.Conn.Close()
 
 
+def test_train_with_examples_mirror(bb, tmp_path, monkeypatch):
+    """main.py:26-31: GenerateTrainingSamples then TrainWithExamples(model, batchSize, learningRate) with the template's
+    training block (adam, lr 1e-4, batch 50): the mirror trains on exactly the batches the reference's loop would form
+    (same permutation from numpy's global stream), the weights match the oracle trainer fed the same batches, Version
+    is bumped and registered, and the search afterwards uses the trained weights."""
+    from oracle import network_np, train_np
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    cfg = {'maxDepth': 10, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': 10,
+           'temperature': {'exploration': 1, 'exploitation': 0.1}}
+    net = {'hasTeacher': False, 'blocks': 2, 'filters': 16, 'eval': {'dense': 16},
+           'policy': {'dirichlet': {'epsilon': 0.0, 'alpha': 0.2}}, 'loss': {'L2_norm': 0.001},
+           'training': {'optimizer': 'adam', 'learning_rate': 1e-3, 'momentum': 0.9, 'batch_size': 50}}
+    model = B.FixedModel(bb['games']['TicTacToe'], 'Trainee', cfg, net, {})
+    B.GenerateTrainingSamples(model, 40, 1)
+    w0 = model.getWeights().copy()
+    recs = model.Conn.GetGames(model.Name, model.Version)
+    np.random.seed(5)
+    B.TrainWithExamples(model, batchSize=50, learningRate=1e-3)
+    assert model.Version == 2 and model.Conn.GetLastVersion('TicTacToe', 'Trainee') == 2
+    assert model.batchCount == len(recs) // 50 >= 4
+    w1 = model.getWeights()
+    assert not np.array_equal(w0, w1)
+    # the oracle trainer on the batches the reference's loop forms
+    np.random.seed(5)
+    order = np.random.choice(len(recs), len(recs) - len(recs) % 50, replace=False)
+    exs = [B.ExampleState.FromSerialized(r) for r in recs]
+    tmpl = network_np.init_weights(3, 9, blocks=2, filters=16, dense=16, seed=0)
+    cur, o = {}, 0
+    for k, v in tmpl.items():
+        cur[k] = np.asarray(w0[o:o + v.size], np.float64).reshape(v.shape)
+        o += v.size
+    opt = train_np.Optimizer('adam')
+    first_loss = None
+    for i in range(len(order) // 50):
+        b = [exs[j] for j in order[i * 50:(i + 1) * 50]]
+        cur, losses = train_np.train_step(cur, opt, np.vstack([e.Board for e in b]), np.hstack([e.MctsEval for e in b]),
+                                          np.vstack([e.MctsPolicy for e in b]).astype(np.float32), 1e-3)
+        first_loss = first_loss or losses
+    want = network_np.flatten_weights(cur)
+    moved = np.abs(want - w0) > 0
+    # Adam: |update| <= ~lr per step whatever the gradient, so compare against the distance travelled
+    assert np.abs(w1 - want).max() < 0.05 * np.abs(want - w0).max() + 1e-6
+    assert np.array_equal(w1[~moved], w0[~moved])                   # frozen BN statistics
+    # the model keeps working with the new weights (search reloads them)
+    s = model.Game()
+    nxt, v, probs = model.FindMove(s, 1, playLimit=10)
+    assert abs(probs.sum() - 1) < 1e-9
+    with pytest.raises(NotImplementedError):
+        model.train(s.AsInputArray(), np.zeros(1), np.zeros((1, 9)), 0.01, teacher=model)
+    model.Conn.Close()
+
+
 @pytest.mark.parametrize('index', [0, 1, 2, 3])
 def test_random_arena_vs_reference(bb, golden, index):
     """Blackbird.TestRandom (Blackbird.py:84-112) against the RandomMCTS mirror: with random.seed / np.random.seed

@@ -66,7 +66,10 @@ def test_gradients_and_losses_vs_autograd(mods, game, B, shape, eps):
 @pytest.mark.parametrize('optimizer', ['adam', 'momentum', 'sgd'])
 def test_steps_vs_oracle_optimizers(mods, optimizer):
     """Three consecutive steps from fixed weights on fixed batches: updated weights against the oracle's
-    (tf.compat.v1.train Adam / Momentum / GradientDescent semantics), 1e-5 of the weight scale."""
+    (tf.compat.v1.train Adam / Momentum / GradientDescent semantics).  Momentum and gradient descent are linear in the
+    gradient: 1e-5 of the tensor's scale.  Adam's first steps move every coordinate by ~lr g / (|g| + 3e-7), which is
+    insensitive to the gradient's size where |g| >> 3e-7 and arbitrary in sign where |g| is fp32 noise, so there the
+    normalised update (theta' - theta) / lr is compared on the coordinates whose gradient is above 1e-4 of the tensor max."""
     engine, trainer = mods
     game, B = 'Connect4', 50
     w = network_np.init_weights(3, 7, seed=1, jitter=0.1)
@@ -74,18 +77,34 @@ def test_steps_vs_oracle_optimizers(mods, optimizer):
     tr = trainer.Trainer(game, network_np.flatten_weights(w), 4, 16, 16, optimizer=optimizer, momentum=0.9)
     opt = train_np.Optimizer(optimizer, 0.9)
     cur = {k: np.asarray(v, np.float64) for k, v in w.items()}
+    prev_got = unflatten(w, tr.weights())
     for step in range(3):
         planes, ev, pol = make_batch(game, B, seed=20 + step)
+        pol = pol.astype(np.float32)
         tr.step(planes, ev, pol, lr)
-        cur, losses = train_np.train_step(cur, opt, planes, ev, pol.astype(np.float32), lr)
+        losses, grads = train_np.loss_and_grads_torch(cur, planes, ev, pol)
+        nxt = opt.step(cur, grads, lr)
         assert np.allclose(tr.losses(), losses, rtol=5e-5, atol=1e-6)
         got = unflatten(w, tr.weights())
         for k in w:
-            scale = max(np.abs(cur[k]).max(), 1e-3)
-            err = np.abs(got[k] - cur[k]).max() / scale
-            # Adam divides by |g| + 3e-7 on the first steps: coordinates with |g| near fp32 noise move by up to lr either way
-            tol = 1e-5 if optimizer != 'adam' else 1e-5 + 2.5 * lr / scale * (np.abs(train_np.loss_and_grads_torch(cur, planes, ev, pol)[1].get(k, np.ones(1))) < 1e-6).any()
-            assert err < tol, (optimizer, step, k, err)
+            if k not in grads:
+                assert np.array_equal(got[k], np.asarray(w[k], np.float64)), k          # frozen BN statistics
+                continue
+            if optimizer == 'adam':
+                live = np.abs(grads[k]) > 1e-4 * max(np.abs(grads[k]).max(), 1e-30)
+                du_got, du_want = (got[k] - prev_got[k]) / lr, (nxt[k] - cur[k]) / lr
+                if live.any():
+                    assert np.abs(du_got - du_want)[live].max() < 1e-2, (step, k, np.abs(du_got - du_want)[live].max())
+                assert np.abs(du_got).max() < 1.2 * (1 if step == 0 else 4)
+            else:
+                scale = max(np.abs(nxt[k]).max(), 1e-3)
+                assert np.abs(got[k] - nxt[k]).max() / scale < 1e-5, (optimizer, step, k)
+        # keep the two trajectories together so that step 2 and 3 test one step each, not the accumulated drift
+        if optimizer == 'adam':
+            for k in grads:
+                nxt[k] = got[k].copy()
+            # the oracle's slots stay its own; they differ from the device's by fp32 rounding only
+        cur, prev_got = nxt, got
     assert tr.steps == 3
     tr.close()
 
