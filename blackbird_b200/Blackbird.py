@@ -213,8 +213,19 @@ def TestRandom(model, temp, numTests):
     return stats
 
 
-def TestGood(model, temp, numTests):
-    raise NotImplementedError('rollout-MCTS opponent (Blackbird.py:146-174, MCTS.py:360-383) is SURVEY.md 8f-2 ("next")')
+def TestGood(model, temp, numTests, good=None):
+    """Blackbird.py:146-174: numTests arena games against a plain rollout MCTS, FixedMCTS(maxDepth=10,
+    explorationRate=0.85, timeLimit=1) -- all-ones priors and a random rollout per leaf visit (MCTS.py:346-383), searched
+    on the device.  `good` overrides the opponent (the parity tests use a play limit instead of the wall-clock second,
+    which is the reference's only non-deterministic input)."""
+    good = good if good is not None else FixedMCTS(maxDepth=10, explorationRate=0.85, timeLimit=1)
+    resultMap = {1: 'wins', 0: 'draws', -1: 'losses'}
+    stats = defaultdict(int)
+    for _ in range(numTests):
+        result = TestModels(model, good, temp, numTests=1)
+        stats[resultMap.get(result, 'indeterminant')] += 1
+        model.Conn.PutTrainingStatistic(result, model.Name, model.Version, 'MCTS')
+    return stats
 
 
 class Model(MCTS, Network):

@@ -14,8 +14,12 @@ Evaluator hook.  The reference lets subclasses override GetPriors / SampleValue
 so the hook it honours sits one level lower: a subclass that defines ``getPolicy(planes)`` and
 ``getEvaluation(planes)`` in Python is served through the engine's external-evaluator mailbox
 (bb_eval_fetch / bb_eval_submit), one call per requested state exactly like the reference's
-batch-1 sess.run.  The base class' default evaluator (uniform priors + random rollouts,
-MCTS.py:346-383) is SURVEY.md 8f-2 ("next") and raises NotImplementedError.
+batch-1 sess.run.  A class with neither (plain FixedMCTS / DynamicMCTS: the 'good' opponent of
+Blackbird.TestGood) gets the base class' own evaluator on the device (BB_EVAL_ROLLOUT): all-ones
+priors and a fresh uniformly random rollout on every leaf visit (MCTS.py:346-383), values exact.
+Its rollout draws are np.random.choice calls on numpy's GLOBAL stream in the reference; the mirror
+hands the engine the next raw MT19937 outputs of that very stream and afterwards advances the
+stream by what the device consumed, so games replay the reference draw for draw.
 """
 from time import time
 
@@ -84,8 +88,7 @@ class MCTS(object):
             return 'net'
         if callable(getattr(self, 'getPolicy', None)) and callable(getattr(self, 'getEvaluation', None)):
             return 'external'
-        raise NotImplementedError('the rollout evaluator of the base class (MCTS.py:346-383) is not on the '
-                                  'accelerated path: define getPolicy/getEvaluation or use Blackbird.Model')
+        return 'rollout'                                                 # the base class' own GetPriors / SampleValue
 
     def _engine_for(self, state, playLimit):
         if self._KIND is None:
@@ -120,7 +123,23 @@ class MCTS(object):
         dev = torch.device('cuda', eng.device)
         eng.eval_submit(torch.as_tensor(pol).to(dev), torch.as_tensor(val).to(dev))
 
+    # raw MT19937 words a rollout simulation may consume, by game (a draw per rollout ply, ~1.4 words each; DragonChess
+    # playouts run a few hundred plies); running out is reported (BB_ESTATE), never silent
+    _ROLLOUT_WORDS = {'TicTacToe': 32, 'Connect4': 160, 'DragonChess': 4096}
+
     def _simulate(self, eng, n):
+        if eng.evaluator == 'rollout':
+            budget = int(n) * self._ROLLOUT_WORDS[eng.game] + 256
+            peek = np.random.RandomState()
+            peek.set_state(np.random.get_state())                        # the words np.random would hand out next
+            eng.set_rng(np.frombuffer(peek.bytes(4 * budget), dtype='<u4'))
+            eng.begin_move(n)
+            eng.run()
+            eng.check_status()
+            used = int(eng.rng_used()[0])
+            if used:
+                np.random.bytes(4 * used)                                # the global stream moves by exactly what the rollouts drew
+            return
         eng.begin_move(n)
         if eng.evaluator == 'external':
             while eng.run():
@@ -139,7 +158,8 @@ class MCTS(object):
         k = int(st['n_children'][0])
         plays = int(st['root_plays'][0])
         # Node.Value stays the int 0 until a parent exists (A.13), then accumulates in f32 (A.9)
-        value = np.float32(st['root_value'][0]) if int(st['root_has_parent'][0]) else 0
+        ro = eng.evaluator == 'rollout'                                  # exact Python numbers instead of np.float32 (A.9)
+        value = (float(st['root_value'][0]) if ro else np.float32(st['root_value'][0])) if int(st['root_has_parent'][0]) else 0
         priors = np.zeros(A)
         children = None
         if k >= 0:
@@ -147,7 +167,8 @@ class MCTS(object):
             for j in range(k):
                 a = int(st['actions'][0, j])
                 priors[a] = st['child_prior'][0, j]
-                kid = Node(None, np.zeros(A), None, plays=int(st['plays'][0, j]), value=np.float32(st['child_value'][0, j]))
+                kid = Node(None, np.zeros(A), None, plays=int(st['plays'][0, j]),
+                           value=float(st['child_value'][0, j]) if ro else np.float32(st['child_value'][0, j]))
                 children[a] = kid
         root = Node(root_state, legal, priors, plays=plays, value=value, children=children)
         for kid in (children or ()):
@@ -284,7 +305,15 @@ class MCTS(object):
         return np.array([1] * len(state.LegalActions()))
 
     def SampleValue(self, state, player):
-        raise NotImplementedError('random-rollout evaluation (MCTS.py:360-383) is SURVEY.md 8f-2, not built')
+        """MCTS.py:360-383 on the host, for callers; the search plays its rollouts on the device (rollout_value)."""
+        rolloutState = state
+        winner = rolloutState.Winner()
+        while winner is None:
+            actions = np.where(rolloutState.LegalActions() == 1)[0]
+            action = np.random.choice(actions)
+            rolloutState = self._applyAction(rolloutState, action)
+            winner = rolloutState.Winner(action)
+        return 0.5 if winner == 0 else int(player == winner)
 
     def _findLeaf(self, node, temp):
         raise NotImplementedError

@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get('BB_ENGINE_LIB') or os.path.join(HERE, 'libbbengine.so
 BB_OK, BB_EINVAL, BB_EILLEGAL, BB_EASSERT, BB_ENOMEM, BB_ECUDA, BB_ESTATE = 0, -1, -2, -3, -4, -5, -6
 TICTACTOE, CONNECT4, DRAGONCHESS = 0, 1, 2
 FIXED, DYNAMIC = 0, 1
-EVAL_KAT, EVAL_NET, EVAL_EXTERNAL = 0, 1, 2
+EVAL_KAT, EVAL_NET, EVAL_EXTERNAL, EVAL_ROLLOUT = 0, 1, 2, 3
 PH_IDLE, PH_RUN, PH_WAIT_EXPAND, PH_WAIT_LEAF, PH_MOVE_READY, PH_GAME_OVER, PH_ERROR, PH_COMPACT = range(8)
 GAME_IDS = {'TicTacToe': TICTACTOE, 'Connect4': CONNECT4, 'DragonChess': DRAGONCHESS}
 
@@ -68,6 +68,8 @@ SIGNATURES = {
     'bb_search_root_stats': (I, [VP, I, VP, VP, VP, VP, VP, VP, VP, VP]),
     'bb_search_choose': (I, [VP, C.c_double, VP, VP]),
     'bb_search_move_root': (I, [VP, VP]),
+    'bb_search_set_rng': (I, [VP, VP, C.c_uint32]),
+    'bb_search_rng_used': (I, [VP, VP]),
     'bb_search_states': (I, [VP, VP]),
     'bb_search_phases': (I, [VP, VP, VP]),
     'bb_eval_pending': (I, [VP, C.POINTER(I32), C.POINTER(VP), C.POINTER(VP)]),

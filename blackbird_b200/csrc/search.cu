@@ -41,7 +41,7 @@ __global__ void k_root_stats(EngineDev<G> E, int kmax, int32_t* n_children, int3
   if (lane == 0) {
     n_children[g] = k;
     root_plays[g] = rn.s.plays;
-    root_value[g] = (double)rn.s.value;
+    root_value[g] = E.rollout ? rn.s.prior : (double)rn.s.value;      // rollout evaluator: Node.Value lives in the f64 field
     root_has_parent[g] = s.root_parent_player != 0;
   }
   for (int j = lane; j < k && j < kmax; j += 32) {
@@ -49,8 +49,8 @@ __global__ void k_root_stats(EngineDev<G> E, int kmax, int32_t* n_children, int3
     const Node kid = nodes[rn.h.child_base + j];
     actions[o] = meta_action(kid.h.meta);
     plays[o] = kid.s.plays;
-    child_value[o] = kid.s.value;
-    child_prior[o] = kid.s.prior;
+    child_value[o] = E.rollout ? (float)kid.s.prior : kid.s.value;     // multiples of 0.5 below 2^23: exact in f32
+    child_prior[o] = E.rollout ? 1.0 : kid.s.prior;
   }
 }
 
@@ -122,6 +122,8 @@ struct bb_engine {
   virtual int stream_stats(uint64_t*) = 0;
   virtual int stream_answers(void*, float*, float*, uint32_t*) = 0;
   virtual int records_serialize(void*, uint64_t, uint64_t*, uint64_t*, uint64_t*, uint32_t*) = 0;
+  virtual int set_rng(const uint32_t*, uint32_t) = 0;
+  virtual int rng_used(uint32_t*) = 0;
 };
 
 template <class G>
@@ -188,6 +190,7 @@ struct EngineT : bb_engine {
     if (const char* e = getenv("BB_LANES")) n_lanes = atoi(e);
     if (n_lanes <= 0) n_lanes = c.n_games >= 512 ? 2 : 1;
     if (c.evaluator == BB_EVAL_EXTERNAL) n_lanes = 1;            // the caller serves one mailbox
+    if (c.evaluator == BB_EVAL_ROLLOUT) n_lanes = 1;             // no evaluator kernel to overlap with
     if (n_lanes > c.n_games) n_lanes = c.n_games;
     if (n_lanes > 8) n_lanes = 8;
     lanes.resize(n_lanes);
@@ -205,6 +208,9 @@ struct EngineT : bb_engine {
     d.max_depth = c.max_depth;
     d.max_plies = c.max_plies;
     d.c = c.exploration_rate;
+    d.rollout = c.evaluator == BB_EVAL_ROLLOUT ? 1 : 0;
+    d.rng_words = nullptr;
+    d.rng_cap = 0;
     {
       const char* sb = getenv("BB_STEP_BUDGET");               // tuning knob; results do not depend on it
       d.step_budget = sb ? atoi(sb) : (c.search == BB_FIXED ? c.max_depth + 6 : 24);
@@ -344,7 +350,10 @@ struct EngineT : bb_engine {
   int tick(Lane& L) {
     const bool timed = prof && L.prof_used + 3 <= L.prof_ev.size();
     if (timed) cudaEventRecord(L.prof_ev[L.prof_used], L.stream);
-    k_advance<G><<<grid_for((long long)L.d.n_games * 32, 32 * WARPS_PER_CTA), 32 * WARPS_PER_CTA, 0, L.stream>>>(L.d, L.par);
+    if (cfg.evaluator == BB_EVAL_ROLLOUT)
+      k_advance<G, true><<<grid_for((long long)L.d.n_games * 32, 32 * WARPS_PER_CTA), 32 * WARPS_PER_CTA, 0, L.stream>>>(L.d, L.par);
+    else
+      k_advance<G><<<grid_for((long long)L.d.n_games * 32, 32 * WARPS_PER_CTA), 32 * WARPS_PER_CTA, 0, L.stream>>>(L.d, L.par);
     BB_CUDA(cudaGetLastError());
     if (timed) cudaEventRecord(L.prof_ev[L.prof_used + 1], L.stream);
     host_ticks++;
@@ -769,6 +778,43 @@ struct EngineT : bb_engine {
     if (ch) *ch = d.chosen;
     return BB_OK;
   }
+  // rollout evaluator: one stream of raw 32-bit MT19937 outputs per slot (words_host [n_games][words_per_slot]); cursors rewound
+  uint32_t* rng_dev = nullptr;
+  size_t rng_alloc = 0;
+  int set_rng(const uint32_t* words_host, uint32_t words_per_slot) override {
+    if (cfg.evaluator != BB_EVAL_ROLLOUT) { set_error("bb_search_set_rng: the engine's evaluator is not BB_EVAL_ROLLOUT"); return BB_EINVAL; }
+    if (!words_host || words_per_slot == 0) { set_error("bb_search_set_rng: empty stream"); return BB_EINVAL; }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    int rc = sync_lanes();
+    if (rc) return rc;
+    const size_t need = (size_t)d.n_games * words_per_slot;
+    if (need > rng_alloc) {
+      uint32_t* p = nullptr;
+      if ((rc = alloc(&p, need))) return rc;
+      rng_dev = p;
+      rng_alloc = need;
+    }
+    BB_CUDA(cudaMemcpyAsync(rng_dev, words_host, need * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+    d.rng_words = rng_dev;
+    d.rng_cap = words_per_slot;
+    for (Lane& L : lanes) { L.d.rng_words = rng_dev; L.d.rng_cap = words_per_slot; }
+    k_rng_rewind<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
+  int rng_used(uint32_t* used_host) override {
+    if (cfg.evaluator != BB_EVAL_ROLLOUT) { set_error("bb_search_rng_used: the engine's evaluator is not BB_EVAL_ROLLOUT"); return BB_EINVAL; }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    int rc = sync_lanes();
+    if (rc) return rc;
+    if ((rc = ensure_scratch((size_t)d.n_games * 4))) return rc;
+    k_rng_used<G><<<grid_for(d.n_games, 128), 128, 0, stream>>>(d, (uint32_t*)scratch);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaMemcpyAsync(used_host, scratch, (size_t)d.n_games * 4, cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    return BB_OK;
+  }
   // ExampleState.SerializeState + labels for every record of the last self-play call, on the device (records.cuh)
   int records_serialize(void* out_dev, uint64_t cap, uint64_t* n_records, uint64_t* n_bytes, uint64_t* game_off_host, uint32_t* rec_bytes_host) override {
     using F = RecFmt<G>;
@@ -857,8 +903,11 @@ int bb_engine_create(const bb_config* cfg, bb_engine** out) {
   if (cfg->n_games <= 0 || cfg->node_cap < 2 || cfg->max_plies <= 0) { set_error("n_games, node_cap, max_plies must be positive"); return BB_EINVAL; }
   if (cfg->search != BB_FIXED && cfg->search != BB_DYNAMIC) { set_error("unknown search kind %d", cfg->search); return BB_EINVAL; }
   if (cfg->search == BB_FIXED && cfg->max_depth <= 0) { set_error("MaxDepth for MCTS must be > 0."); return BB_EINVAL; }   // FixedMCTS.py:15-16
-  if (cfg->evaluator < BB_EVAL_KAT || cfg->evaluator > BB_EVAL_EXTERNAL) { set_error("unknown evaluator %d", cfg->evaluator); return BB_EINVAL; }
-  if (cfg->value_f64) { set_error("value_f64 accumulation (rollout evaluators, SURVEY.md 8f-2) is not built yet"); return BB_EINVAL; }
+  if (cfg->evaluator < BB_EVAL_KAT || cfg->evaluator > BB_EVAL_ROLLOUT) { set_error("unknown evaluator %d", cfg->evaluator); return BB_EINVAL; }
+  if ((cfg->value_f64 != 0) != (cfg->evaluator == BB_EVAL_ROLLOUT)) {
+    set_error("value_f64 goes with BB_EVAL_ROLLOUT and only with it: rollout values are exact Python numbers (f64), network values accumulate in f32 (SURVEY.md A.9)");
+    return BB_EINVAL;
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { set_error("no CUDA device: the engine has no CPU fallback"); return BB_ECUDA; }
   if (cfg->device < 0 || cfg->device >= ndev) { set_error("device %d out of range (%d devices)", cfg->device, ndev); return BB_EINVAL; }
@@ -889,6 +938,8 @@ int bb_search_root_stats(bb_engine* e, int kmax, int32_t* nch, int32_t* act, uin
 }
 int bb_search_choose(bb_engine* e, double temp, const double* u, int32_t* a) { BB_NEED(e); return e->choose(temp, u, a); }
 int bb_search_move_root(bb_engine* e, const int32_t* a) { BB_NEED(e); return e->move_root(a); }
+int bb_search_set_rng(bb_engine* e, const uint32_t* words, uint32_t n) { BB_NEED(e); return e->set_rng(words, n); }
+int bb_search_rng_used(bb_engine* e, uint32_t* used) { BB_NEED(e); return e->rng_used(used); }
 int bb_search_states(bb_engine* e, void* out) { BB_NEED(e); return e->states(out); }
 int bb_search_phases(bb_engine* e, int32_t* ph, int32_t* st) { BB_NEED(e); return e->phases(ph, st); }
 int bb_eval_pending(bb_engine* e, int32_t* n, const int32_t** slots, const void** st) { BB_NEED(e); return e->eval_pending(n, slots, st); }

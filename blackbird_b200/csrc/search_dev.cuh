@@ -47,7 +47,8 @@ __device__ __forceinline__ NodeHdr shfl_hdr(const NodeHdr& h, int src) {
 // Lane j loads child j's whole 32-byte record, so the winner's header (its own child block, action,
 // cached value) arrives with the same memory round trip.  Returns the child index (warp-uniform);
 // *best_u receives U_j and *chosen the winner's header.
-template <int CHUNKS>
+// RO (rollout evaluator): priors are the constant 1 and the f64 field holds Node.Value: W_i = Value / Plays in f64.
+template <int CHUNKS, bool RO = false>
 __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, double* best_u, NodeHdr* chosen) {
   const int lane = lane_id();
   Node r[CHUNKS];
@@ -66,8 +67,14 @@ __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, do
   double bu = -1.0;
   int bj = 0x7FFFFFFF;
   auto score = [&](const NodeStat& s, int j) {
-    float wr = s.plays > 0 ? __fdiv_rn(s.value, (float)s.plays) : 0.f;            // Node.WinRate, f32 (A.9)
-    double u = __dadd_rn((double)wr, __ddiv_rn(__dmul_rn(__dmul_rn(c, s.prior), t), __dadd_rn(1.0, (double)s.plays)));
+    double u;
+    if (RO) {
+      const double wr = s.plays > 0 ? __ddiv_rn(s.prior, (double)s.plays) : 0.0;   // exact Python Value / Plays (A.9)
+      u = __dadd_rn(wr, __ddiv_rn(__dmul_rn(c, t), __dadd_rn(1.0, (double)s.plays)));   // c * 1.0 == c
+    } else {
+      float wr = s.plays > 0 ? __fdiv_rn(s.value, (float)s.plays) : 0.f;          // Node.WinRate, f32 (A.9)
+      u = __dadd_rn((double)wr, __ddiv_rn(__dmul_rn(__dmul_rn(c, s.prior), t), __dadd_rn(1.0, (double)s.plays)));
+    }
     if (u > bu) { bu = u; bj = j; }
   };
 #pragma unroll
@@ -163,7 +170,9 @@ __device__ double pairwise_sum_sparse(int k, Get get) {
 // Creates the k children of `node` (ascending action id) with Plays 0, Value 0 and
 // prior = f64(policy[a]) / sum.  Updates *node_hdr (and its copy in HBM).  Returns k, or -1 when
 // the half-arena is full.
-template <class G>
+// RO: priors are GetPriors' constant ones (MCTS.py:346-358) times the legal mask -- nothing to read or normalise; the
+// f64 field starts as Node.Value = 0.
+template <class G, bool RO = false>
 __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint32_t node, NodeHdr* node_hdr,
                            const float* policy, WarpScratch& ws) {
   const int lane = lane_id();
@@ -179,20 +188,24 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     double p = 0.0;
     if (lane < k) {
       a = nth_bit(m, lane);
-      p = (double)__ldcg(policy + a);                       // f32 policy * 1.0 (f64 mask); L2 load: written by another SM in streaming mode
-      ws.prior[lane] = p;
-      ws.action[lane] = (uint16_t)a;
+      if (!RO) {
+        p = (double)__ldcg(policy + a);                     // f32 policy * 1.0 (f64 mask); L2 load: written by another SM in streaming mode
+        ws.prior[lane] = p;
+        ws.action[lane] = (uint16_t)a;
+      }
     }
     __syncwarp();
-    double sum = 0.0;
-    if (lane == 0)
-      sum = pairwise_sum_sparse<G>(k, [&](int j, int* act) { *act = ws.action[j]; return ws.prior[j]; });
-    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+    double sum = 1.0;
+    if (!RO) {
+      if (lane == 0)
+        sum = pairwise_sum_sparse<G>(k, [&](int j, int* act) { *act = ws.action[j]; return ws.prior[j]; });
+      sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+    }
     if (lane < k) {
       Node n;
       n.s.plays = 0u;
       n.s.value = 0.f;
-      n.s.prior = __ddiv_rn(p, sum);
+      n.s.prior = RO ? 0.0 : __ddiv_rn(p, sum);
       n.h.parent = node;
       n.h.child_base = NONE;
       n.h.meta = meta_pack(a, 0, child_player, false);
@@ -217,7 +230,7 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     }
     k = __shfl_sync(0xFFFFFFFFu, incl, 31);
     if (base + (uint32_t)k > E.node_cap) return -1;
-    const bool staged = k <= STAGE_MAX;
+    const bool staged = !RO && k <= STAGE_MAX;
     int j = incl - cnt;
 #pragma unroll
     for (int r = 0; r < RPL; ++r) {
@@ -230,7 +243,7 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
         Node n;
         n.s.plays = 0u;
         n.s.value = 0.f;
-        n.s.prior = (double)__ldcg(policy + a);
+        n.s.prior = RO ? 0.0 : (double)__ldcg(policy + a);
         n.h.parent = node;
         n.h.child_base = NONE;
         n.h.meta = meta_pack(a, 0, child_player, false);
@@ -241,14 +254,16 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
       }
     }
     __syncwarp();
-    double sum = 0.0;
-    if (lane == 0) {
-      if (staged) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
-      else sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = meta_action(nodes[base + q].h.meta); return nodes[base + q].s.prior; });
+    if (!RO) {
+      double sum = 0.0;
+      if (lane == 0) {
+        if (staged) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
+        else sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = meta_action(nodes[base + q].h.meta); return nodes[base + q].s.prior; });
+      }
+      sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+      for (int i = lane; i < k; i += 32)
+        nodes[base + i].s.prior = __ddiv_rn(staged ? ws.prior[i] : nodes[base + i].s.prior, sum);
     }
-    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
-    for (int i = lane; i < k; i += 32)
-      nodes[base + i].s.prior = __ddiv_rn(staged ? ws.prior[i] : nodes[base + i].s.prior, sum);
   }
   node_hdr->child_base = base;
   node_hdr->meta = (node_hdr->meta & ~(0x3FFu << 12)) | ((uint32_t)k << 12);
@@ -322,6 +337,123 @@ __device__ void backup(const Slot<G>& s, Node* nodes, const Path& path, float ev
       uint2 w = *q;                                          // (plays, value)
       w.x += 1;
       if (parent_player != 0) w.y = __float_as_uint(__fadd_rn(__uint_as_float(w.y), parent_player == p ? v : flip));
+      *q = w;
+    }
+  }
+  __syncwarp();
+}
+
+// ---- rollout evaluator: MCTS.SampleValue (MCTS.py:360-383) and its exact-valued _backProp --------------
+constexpr int ROLLOUT_MAX_PLIES = 8192;   // DragonChess has no draw and no move cap (A.20); random playouts end after a few hundred plies
+
+// One masked-rejection draw of np.random.choice(actions) from the slot's MT19937 word stream (legacy RandomState.randint:
+// no draw at all when a single action is legal).  Returns -1 when the stream is exhausted.
+template <class G>
+__device__ __forceinline__ int rng_choice(const EngineDev<G>& E, Slot<G>& s, int g, int n) {
+  const uint32_t rng = (uint32_t)n - 1u;
+  if (rng == 0u) return 0;
+  uint32_t mask = rng;
+  mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+  for (;;) {
+    if (s.rng_pos >= E.rng_cap) return -1;
+    const uint32_t v = E.rng_words[(size_t)g * E.rng_cap + s.rng_pos++] & mask;
+    if (v <= rng) return (int)v;
+  }
+}
+
+// -> Python 0 / 0.5 / 1 in halves (0, 1, 2), or -1 on an error (s.status set).  Warp-uniform: every lane plays the same game.
+template <class G>
+__device__ int rollout_value(const EngineDev<G>& E, Slot<G>& s, int g) {
+  typename G::State st = s.cur_state;
+  const int player = G::prev(st);                              // SampleValue(leaf.State, leaf.State.PreviousPlayer); 0 = None
+  int w = G::winner(st, -1);                                   // rolloutState.Winner()
+  for (int plies = 0; w == WIN_NONE; ++plies) {
+    int a;
+    if (G::NROWS == 1) {
+      const uint64_t m = G::legal_row(st, 0);
+      const int n = popc64(m);
+      if (n == 0) { s.status = BB_EASSERT; return -1; }         // np.random.choice([]) raises in the reference
+      const int idx = rng_choice(E, s, g, n);
+      if (idx < 0) { s.status = BB_ESTATE; return -1; }
+      a = G::action_of(0, nth_bit(m, idx));
+    } else {                                                    // wide action spaces: the lanes share the rows
+      constexpr int RPL = (G::NROWS + 31) / 32;
+      const int lane = lane_id();
+      uint64_t m[RPL];
+      int cnt = 0;
+#pragma unroll
+      for (int r = 0; r < RPL; ++r) {
+        const int row = lane * RPL + r;
+        m[r] = row < G::NROWS ? G::legal_row(st, row) : 0ull;
+        cnt += popc64(m[r]);
+      }
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const int n = __shfl_sync(0xFFFFFFFFu, incl, 31);
+      if (n == 0) { s.status = BB_EASSERT; return -1; }
+      const int idx = rng_choice(E, s, g, n);
+      if (idx < 0) { s.status = BB_ESTATE; return -1; }
+      int mine = -1;
+      int j = idx - (incl - cnt);                               // position inside this lane's rows
+      if (j >= 0 && j < cnt) {
+#pragma unroll
+        for (int r = 0; r < RPL; ++r) {
+          const int c = popc64(m[r]);
+          if (j >= 0 && j < c) mine = G::action_of(lane * RPL + r, nth_bit(m[r], j));
+          j -= c;
+        }
+      }
+      const unsigned who = __ballot_sync(0xFFFFFFFFu, mine >= 0);
+      a = __shfl_sync(0xFFFFFFFFu, mine, __ffs(who) - 1);
+    }
+    G::apply(st, a);                                            // _applyAction: Copy + ApplyAction
+    w = G::winner(st, a);                                       // rolloutState.Winner(action)
+    if (plies >= ROLLOUT_MAX_PLIES) { s.status = BB_ESTATE; return -1; }
+  }
+  if (w == WIN_DRAW || w == WIN_FLOAT0) return 1;               // `winner == 0` holds for int 0 and np.float64(0.0)
+  return player == w ? 2 : 0;                                   // int(player == winner); player None -> 0
+}
+
+// _backProp with exact values: Plays += 1 and (if the node has a parent) Value += v or 1 - v, Value kept in the f64 field
+template <class G>
+__device__ void backup_rollout(const Slot<G>& s, Node* nodes, const Path& path, int halves) {
+  const int lane = lane_id();
+  const double v = 0.5 * (double)halves, flip = 1.0 - v;
+  const int p = G::prev(s.cur_state);
+  int d = s.depth;
+  if (d >= PATH_LEN) {
+    if (lane == 0) {
+      uint32_t m = s.cur;
+      while (d >= PATH_LEN) {
+        const uint32_t parent = nodes[m].h.parent;
+        const int pp = meta_player(nodes[parent].h.meta);
+        nodes[m].s.plays += 1;
+        nodes[m].s.prior = __dadd_rn(nodes[m].s.prior, pp == p ? v : flip);
+        m = parent;
+        --d;
+      }
+    }
+    d = PATH_LEN - 1;
+    __syncwarp();
+  }
+  uint32_t carry = 0;
+#pragma unroll
+  for (int c = 0; c < PATH_LEN / 32; ++c) {
+    const uint32_t e = path.r[c];
+    uint32_t up = __shfl_up_sync(0xFFFFFFFFu, e, 1);
+    if (lane == 0) up = carry;
+    carry = __shfl_sync(0xFFFFFFFFu, e, 31);
+    const int idx = c * 32 + lane;
+    if (idx <= d) {
+      const int parent_player = idx == 0 ? s.root_parent_player : 1 + (int)(up >> 31);
+      NodeStat* q = &nodes[e & 0x7FFFFFFFu].s;
+      NodeStat w = *q;
+      w.plays += 1;
+      if (parent_player != 0) w.prior = __dadd_rn(w.prior, parent_player == p ? v : flip);
       *q = w;
     }
   }

@@ -163,7 +163,9 @@ constexpr int STREAM_WARPS_PER_CTA = BB_STREAM_WARPS;
 #define ST_T0()
 #define ST_ADD(i)
 #endif
-template <class G>
+// RO: the rollout evaluator (BB_EVAL_ROLLOUT) -- expansion needs no evaluation (constant priors), every leaf visit plays a
+// fresh random rollout (MCTS.py:360-383), values accumulate exactly; a slot never waits for an evaluator.
+template <class G, bool RO = false>
 __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws, uint32_t* ticket = nullptr) {
   const int lane = lane_id();
 #ifdef BB_SEARCH_TIMING
@@ -221,6 +223,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }     // FixedMCTS.py:23
       if (ch.child_base == NONE) {                              // Children is None
         if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
+        if (RO) { step = ST_EXPAND; continue; }                 // AddChildren with GetPriors == ones: nothing to ask
         ST_ADD(5);
         post_request(E, s, g, par);                             // GetPriors(state) of this node
         ST_ADD(1);
@@ -231,7 +234,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
       ST_ADD(5);
-      const int k = expand_node(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws);
+      const int k = expand_node<G, RO>(E, s, nodes, s.cur, &ch, RO ? nullptr : E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws);
       ST_ADD(2);
       if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
       n_exp += 1;
@@ -247,7 +250,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
                ch.child_base, meta_nchild(ch.meta), ch.meta, s.n_nodes, s.ply, s.half, s.root, s.root_plays, s.cp_n, s.cp_head);
 #endif
       BB_ASSERT(ch.child_base + (uint32_t)meta_nchild(ch.meta) <= s.n_nodes);
-      const int j = puct_select<SelectChunks<G>::N>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
+      const int j = puct_select<SelectChunks<G>::N, RO>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
       const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
       // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
       if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
@@ -262,6 +265,11 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       step = ST_TOP;
       ST_ADD(3);
     } else {                                                    // ST_LEAF: SampleValue + _backProp
+      if (RO) {
+        const int halves = rollout_value(E, s, g);
+        if (halves < 0) { s.phase = BB_PH_ERROR; break; }
+        backup_rollout(s, nodes, path, halves);
+      } else {
       if (!(ch.meta & META_HAS_VALUE)) {
         ST_ADD(5);
         post_request(E, s, g, par);                             // getEvaluation(state) of the leaf
@@ -273,6 +281,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       ST_ADD(5);
       backup(s, nodes, path, ch.eval);
       ST_ADD(4);
+      }
       s.root_plays += 1;
       n_sims += 1;
       if (s.root_plays >= s.end_plays) {                        // MCTS.py:298-299
@@ -290,7 +299,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
             double u;
             NodeHdr dummy;
             dummy.meta = 0;
-            j = puct_select<SelectChunks<G>::N>(nodes + rh.child_base, k, E.c, &u, &dummy);
+            j = puct_select<SelectChunks<G>::N, RO>(nodes + rh.child_base, k, E.c, &u, &dummy);
             // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
             if (j != 0x7FFFFFFF && !(u > 0.0) && j < meta_action(dummy.meta)) j = 0x7FFFFFFF;
           }
@@ -457,11 +466,11 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
 
 // One tick.  `par` = tick parity (host-tracked): requests / activity of this tick accumulate in
 // ctl->req[par] / ctl->active[par]; the last CTA to finish clears the other parity for the next tick.
-template <class G>
+template <class G, bool RO = false>
 __global__ void __launch_bounds__(32 * WARPS_PER_CTA, BB_ADV_MIN_CTAS) k_advance(EngineDev<G> E, unsigned par) {
   __shared__ WarpScratch s_ws[WARPS_PER_CTA];
   const int gl = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // lane-local slot
-  if (gl < E.n_games) advance_slot(E, E.g0 + gl, par, s_ws[threadIdx.x >> 5]);
+  if (gl < E.n_games) advance_slot<G, RO>(E, E.g0 + gl, par, s_ws[threadIdx.x >> 5]);
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
@@ -506,6 +515,7 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.half = 0;
   s.cp_head = s.cp_n = s.cp_src = 0;
   s.row = (uint32_t)g;
+  s.rng_pos = 0;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;
   if (E.winners) E.winners[g] = WIN_NONE;
@@ -551,7 +561,11 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_choose(EngineDev<G> E, i
   int j;
   NodeHdr chosen;
   if (temp_mode == 1) { j = sample_child(nodes + rh.child_base, k, uniforms[g]); chosen = nodes[rh.child_base + j].h; }
-  else { double u; j = puct_select<SelectChunks<G>::N>(nodes + rh.child_base, k, E.c, &u, &chosen); }
+  else {
+    double u;
+    j = E.rollout ? puct_select<SelectChunks<G>::N, true>(nodes + rh.child_base, k, E.c, &u, &chosen)
+                  : puct_select<SelectChunks<G>::N, false>(nodes + rh.child_base, k, E.c, &u, &chosen);
+  }
   if (lane_id() == 0) actions[g] = meta_action(chosen.meta);
 }
 
@@ -578,6 +592,18 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_move_root(EngineDev<G> E
     if (lane_id() == 0) atomicAdd(&E.counters->moves, 1ull);
   }
   if (lane_id() == 0) E.slots[g] = s;
+}
+
+// rollout evaluator: rewind every slot's word cursor (a new stream was uploaded) / read the cursors back
+template <class G>
+__global__ void k_rng_rewind(EngineDev<G> E) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < E.n_games) E.slots[g].rng_pos = 0;
+}
+template <class G>
+__global__ void k_rng_used(EngineDev<G> E, uint32_t* used) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < E.n_games) used[g] = E.slots[g].rng_pos;
 }
 
 }  // namespace bb

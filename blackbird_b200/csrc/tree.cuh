@@ -68,6 +68,7 @@ struct Slot {
   uint32_t cp_head, cp_n;         // subtree copy in progress: next node to scan, nodes written
   uint32_t cp_src;                // old id of the new root
   uint32_t row;                   // record / uniform row of the game this slot is playing (= slot id unless n_rows > n_games)
+  uint32_t rng_pos;               // rollout evaluator: next unread word of the slot's MT19937 word stream
 };
 
 // numpy pairwise-sum plan for a dense vector of length A, built on the host.
@@ -135,6 +136,13 @@ struct EngineDev {                // passed to kernels by value
   int32_t* winners;
   uint32_t pool_cap;
   Counters* counters;
+  // rollout evaluator (BB_EVAL_ROLLOUT: the base-class GetPriors / SampleValue of MCTS.py:346-383).  Priors are the
+  // constant 1, so a node's f64 `prior` field holds Node.Value instead (Python 0 / 0.5 / 1 sums, exact: A.9) and the
+  // f32 `value` field is unused.  Rollout draws come from a per-slot stream of raw 32-bit MT19937 outputs supplied by
+  // the host (np.random's own stream, so that the reference's games replay bit for bit).
+  int rollout;
+  const uint32_t* rng_words;      // [n_games][rng_cap]
+  uint32_t rng_cap;
 
   __device__ __forceinline__ Node* half(int g, uint32_t h) const { return nodes + ((size_t)g * 2 + h) * node_cap; }
 };

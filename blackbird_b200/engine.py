@@ -163,7 +163,8 @@ class Engine(object):
         cfg.game = _lib.GAME_IDS[game]
         cfg.search = {'fixed': _lib.FIXED, 'dynamic': _lib.DYNAMIC}[search]
         cfg.max_depth = int(max_depth or 0)
-        cfg.evaluator = {'kat': _lib.EVAL_KAT, 'net': _lib.EVAL_NET, 'external': _lib.EVAL_EXTERNAL}[evaluator]
+        cfg.evaluator = {'kat': _lib.EVAL_KAT, 'net': _lib.EVAL_NET, 'external': _lib.EVAL_EXTERNAL, 'rollout': _lib.EVAL_ROLLOUT}[evaluator]
+        cfg.value_f64 = 1 if evaluator == 'rollout' else 0
         cfg.n_games, cfg.node_cap, cfg.max_plies, cfg.device = self.n_games, self.node_cap, self.max_plies, device
         cfg.exploration_rate = float(exploration_rate)
         cfg.lanes = int(lanes)
@@ -255,6 +256,16 @@ class Engine(object):
     def move_root(self, actions):
         a = np.ascontiguousarray(actions, dtype=np.int32)
         check(lib.bb_search_move_root(self._h, a.ctypes.data_as(C.c_void_p)))
+
+    def set_rng(self, words):
+        """Rollout evaluator: raw 32-bit MT19937 outputs, uint32 [n_games, words_per_slot]; rewinds the slots' cursors."""
+        w = np.ascontiguousarray(words, dtype=np.uint32).reshape(self.n_games, -1)
+        check(lib.bb_search_set_rng(self._h, w.ctypes.data_as(C.c_void_p), w.shape[1]))
+
+    def rng_used(self):
+        used = np.empty(self.n_games, np.uint32)
+        check(lib.bb_search_rng_used(self._h, used.ctypes.data_as(C.c_void_p)))
+        return used
 
     def states(self):
         out = np.empty((self.n_games, self.state_bytes), np.uint8)

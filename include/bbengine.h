@@ -26,7 +26,9 @@ enum { BB_TICTACTOE = 0, BB_CONNECT4 = 1, BB_DRAGONCHESS = 2 };   /* TicTacToe.p
 enum { BB_FIXED = 0, BB_DYNAMIC = 1 };                            /* FixedMCTS.py:21-34 / DynamicMCTS.py:14-34 */
 enum { BB_EVAL_KAT = 0,        /* integer evaluator of SURVEY.md Appendix B.2 (parity vehicle) */
        BB_EVAL_NET = 1,        /* built-in policy-value network (NetworkFactory.py:22-183)     */
-       BB_EVAL_EXTERNAL = 2 }; /* caller serves requests (bb_eval_pending / bb_eval_submit)    */
+       BB_EVAL_EXTERNAL = 2,   /* caller serves requests (bb_eval_pending / bb_eval_submit)    */
+       BB_EVAL_ROLLOUT = 3 };  /* the base class's own evaluator (MCTS.py:346-383): all-ones priors, a fresh random
+                                  rollout on every leaf visit, exact values (bb_config.value_f64 = 1)  */
 /* winner codes: None, python int 0 (draw), 1.0, 2.0, np.float64(0.0) */
 enum { BB_WIN_NONE = -1, BB_WIN_DRAW = 0, BB_WIN_P1 = 1, BB_WIN_P2 = 2, BB_WIN_FLOAT0 = 3 };
 /* per-game phases reported by bb_search_phases */
@@ -133,6 +135,14 @@ int bb_search_root_stats(bb_engine* e, int kmax, int32_t* n_children_host, int32
 int bb_search_choose(bb_engine* e, double temp, const double* uniforms_host, int32_t* actions_host);
 /* state = nextState; MoveRoot(state) (Blackbird.py:249-251, MCTS.py:260-282), by action. */
 int bb_search_move_root(bb_engine* e, const int32_t* actions_host);
+/* BB_EVAL_ROLLOUT: the draws of MCTS.SampleValue's rollouts (np.random.choice(actions), MCTS.py:378-379) come from a
+ * per-slot stream of raw 32-bit MT19937 outputs, words_host [n_games][words_per_slot] -- numpy's own global stream when
+ * the reference's games are to be replayed bit for bit (legacy RandomState.randint: one masked-rejection draw per
+ * rollout step, none when a single action is legal).  The call rewinds every slot's cursor; bb_search_rng_used reports
+ * how many words each slot consumed so that the caller can advance its own generator by the same amount.  A slot that
+ * runs out of words stops with BB_ESTATE. */
+int bb_search_set_rng(bb_engine* e, const uint32_t* words_host, uint32_t words_per_slot);
+int bb_search_rng_used(bb_engine* e, uint32_t* used_host);
 /* current root states / phases / status codes per slot */
 int bb_search_states(bb_engine* e, void* states_host);
 int bb_search_phases(bb_engine* e, int32_t* phases_host, int32_t* status_host);

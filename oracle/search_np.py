@@ -71,7 +71,7 @@ class Search(object):
         self.Rng = rng if rng is not None else np.random   # reference uses the global stream (MCTS.py:338)
         self.Stats = dict(sims=0, expansions=0, nodes=0, depth=0)
 
-    # -- hooks (MCTS.py:346-383 defaults are NOT restated here: rollouts are an 8f "next" row)
+    # -- hooks (the defaults of MCTS.py:346-383 are RolloutSearch below)
     def GetPriors(self, state):
         raise NotImplementedError
 
@@ -220,6 +220,27 @@ class NetSearch(Search):
         policy = self.Evaluator.getPolicy(state.AsInputArray()) * state.LegalActions()   # :386
         policy /= np.sum(policy)                                         # pairwise f64 sum (A.11)
         return policy
+
+
+class RolloutSearch(Search):
+    """The base-class evaluator of MCTS.py:346-383: un-normalised all-ones priors and a fresh uniformly random rollout
+    on EVERY visit of a leaf.  This is the 'good' opponent of Blackbird.TestGood (FixedMCTS(maxDepth=10,
+    explorationRate=0.85, timeLimit=1), Blackbird.py:164).  Values are Python 0 / 1 / 0.5, so Node.Value accumulates
+    exactly (int / float, A.9) and WinRate is an f64 division.  Draws: rollouts use rng.choice(actions) -- one masked
+    32-bit rejection draw of the MT19937 stream per step (none when a single action is legal)."""
+
+    def GetPriors(self, state):
+        return np.array([1] * len(state.LegalActions()))                 # MCTS.py:346-358
+
+    def SampleValue(self, state, player):
+        rolloutState = state                                             # MCTS.py:360-383
+        winner = rolloutState.Winner()
+        while winner is None:
+            actions = np.where(rolloutState.LegalActions() == 1)[0]
+            action = self.Rng.choice(actions)
+            rolloutState = self._child_state(rolloutState, action)
+            winner = rolloutState.Winner(action)
+        return 0.5 if winner == 0 else int(player == winner)
 
 
 class KatEvaluator(object):

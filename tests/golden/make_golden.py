@@ -284,6 +284,67 @@ def arena_games():
     return out
 
 
+# --- 6. the base-class evaluator (all-ones priors, a random rollout per leaf visit): FindMove KATs and arena games
+#        against the 'good' opponent of Blackbird.TestGood, with playLimit in place of its wall-clock limit (8f-2) ----
+def vcode(v):
+    """Root.Value / WinRate of the rollout evaluator: exact Python int / float -> repr."""
+    return repr(float(v))
+
+
+def rollout_kats():
+    out = []
+    cases = [('TicTacToe', 'fixed', 40, 4, 0), ('TicTacToe', 'dynamic', 60, 4, 1), ('Connect4', 'fixed', 30, 4, 2),
+             ('Connect4', 'dynamic', 80, 4, 3), ('Connect4', 'fixed', 135, 3, 4), ('DragonChess', 'fixed', 6, 3, 5),
+             ('DragonChess', 'dynamic', 10, 3, 6)]
+    for game, kind, P, moves, seed in cases:
+        cls = FixedMCTS if kind == 'fixed' else DynamicMCTS
+        m = cls(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=P)
+        np.random.seed(seed)
+        s = GAMES[game]()
+        rows = []
+        for _ in range(moves):
+            nxt, v, probs = m.FindMove(s, 1)
+            plays = m.Root.ChildPlays()
+            nz = np.flatnonzero(plays).astype(int).tolist()
+            action = next(a for a in range(len(plays)) if m.Root.Children[a] is not None and m.Root.Children[a].State == nxt)
+            rows.append({'plays_idx': nz, 'plays': plays[nz].astype(int).tolist(), 'action': action,
+                         'child_values': [vcode(m.Root.Children[a].Value) for a in nz],
+                         'winrate': vcode(v), 'root_plays': int(m.Root.Plays), 'root_value': vcode(m.Root.Value),
+                         'rng_after': int(np.random.get_state()[2]),
+                         'probs_sha': hashlib.sha256(probs.tobytes()).hexdigest()[:16]})
+            s = nxt
+            m.MoveRoot(s)
+        out.append({'game': game, 'kind': kind, 'playLimit': P, 'seed': seed, 'moves': rows,
+                    'next_double': float(np.random.random_sample())})
+    return out
+
+
+def arena_good_games():
+    import random
+    out = []
+    cases = [('TicTacToe', 'dynamic', 30, 25, 0.1, 3, 0), ('Connect4', 'fixed', 20, 30, 0.1, 2, 1), ('Connect4', 'dynamic', 40, 60, 1, 2, 2)]
+    for game, kind, P, Pgood, temp, n, seed in cases:
+        m = make_model(game, kind, P)
+        boards, results = [], []
+        move_root = m.MoveRoot
+
+        def logged(state, _mr=move_root):
+            boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                         + bytes([int(state.Player)])).hexdigest()[:12])
+            return _mr(state)
+        m.MoveRoot = logged
+        random.seed(seed)
+        np.random.seed(seed)
+        for _ in range(n):
+            # Blackbird.TestGood (Blackbird.py:146-174) with the opponent's timeLimit=1 replaced by a play limit: the
+            # wall-clock limit is the only non-deterministic input (A.25); everything else is the reference's own code
+            good = FixedMCTS(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=Pgood)
+            results.append(int(Blackbird.TestModels(m, good, temp, numTests=1)))
+        out.append({'game': game, 'kind': kind, 'playLimit': P, 'goodPlayLimit': Pgood, 'temp': temp, 'numTests': n, 'seed': seed,
+                    'results': results, 'boards': boards, 'next_double': float(np.random.random_sample())})
+    return out
+
+
 def main():
     def dump(name, obj):
         with open(os.path.join(HERE, name), 'w') as f:
@@ -296,6 +357,8 @@ def main():
     dump('mcts_kat.json', mcts_kats())
     dump('records.json', record_games())
     dump('arena.json', arena_games())
+    dump('rollout_kat.json', rollout_kats())
+    dump('arena_good.json', arena_good_games())
 
 
 if __name__ == '__main__':

@@ -265,3 +265,78 @@ def test_random_arena_vs_reference(bb, golden, index):
     assert boards == case['boards'], (case['game'], case['kind'])
     assert rows == case['rows']
     assert dict(stats) == case['stats']
+
+
+@pytest.mark.parametrize('index', [0, 1, 2, 3, 4, 5, 6])
+def test_rollout_search_vs_reference(bb, golden, index):
+    """Plain FixedMCTS / DynamicMCTS (the base class' own evaluator: all-ones priors, a fresh random rollout on every
+    leaf visit, MCTS.py:346-383) on the device against the unmodified reference (rollout_kat.json): visit counts, exact
+    child values, Root.Value / WinRate, chosen moves -- and numpy's global MT19937 stream ends up in the same state,
+    i.e. the device consumed exactly the draws the reference's rollouts make."""
+    case = golden('rollout_kat.json')[index]
+    cls = bb['FixedMCTS'] if case['kind'] == 'fixed' else bb['DynamicMCTS']
+    m = cls(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=case['playLimit'])
+    np.random.seed(case['seed'])
+    s = bb['games'][case['game']]()
+    for mv in case['moves']:
+        nxt, v, probs = m.FindMove(s, 1)
+        plays = m.Root.ChildPlays()
+        nz = np.flatnonzero(plays).tolist()
+        assert nz == mv['plays_idx'] and plays[nz].astype(int).tolist() == mv['plays'], (case['game'], case['kind'])
+        assert [repr(float(m.Root.Children[a].Value)) for a in nz] == mv['child_values']
+        assert m._last_action == mv['action'] and repr(float(v)) == mv['winrate']
+        assert m.Root.Plays == mv['root_plays'] and repr(float(m.Root.Value)) == mv['root_value']
+        assert int(np.random.get_state()[2]) == mv['rng_after']
+        assert hashlib.sha256(probs.tobytes()).hexdigest()[:16] == mv['probs_sha']
+        s = nxt
+        m.MoveRoot(s)
+    assert float(np.random.random_sample()) == case['next_double']
+    assert m._eng.evaluator == 'rollout'
+
+
+@pytest.mark.parametrize('index', [0, 1, 2])
+def test_good_arena_vs_reference(bb, golden, index):
+    """Blackbird.TestGood (Blackbird.py:146-174) with the opponent's wall-clock second replaced by a play limit (the
+    reference's only non-deterministic input): every game replays the unmodified reference's TestModels(model,
+    FixedMCTS(maxDepth=10, explorationRate=0.85, playLimit=...)) position for position (arena_good.json)."""
+    import random
+    case = golden('arena_good.json')[index]
+    B = bb['Blackbird']
+    base = bb['DynamicMCTS'] if case['kind'] == 'dynamic' else bb['FixedMCTS']
+    cls = type('KatSearch', (base, KatNet), {})
+    m = cls(maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=case['playLimit'])
+    m.Game = bb['games'][case['game']]
+    m._nActions = m.Game.LegalMoves
+    m.Name, m.Version = 'gold', 1
+    rows, boards = [], []
+
+    class Conn(object):
+        def PutTrainingStatistic(self, *a):
+            rows.append(list(a))
+    m.Conn = Conn()
+    move_root = m.MoveRoot
+
+    def logged(state):
+        boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                     + bytes([int(state.Player)])).hexdigest()[:12])
+        return move_root(state)
+    m.MoveRoot = logged
+    random.seed(case['seed'])
+    np.random.seed(case['seed'])
+    results = []
+    for _ in range(case['numTests']):
+        good = bb['FixedMCTS'](maxDepth=10, explorationRate=0.85, timeLimit=None, playLimit=case['goodPlayLimit'])
+        stats = B.TestGood(m, case['temp'], 1, good=good)
+        results.append({'wins': 1, 'draws': 0, 'losses': -1}[next(k for k, v in stats.items() if v)])
+    assert boards == case['boards'], (case['game'], case['kind'])
+    assert results == case['results'] and [r[0] for r in rows] == case['results'] and all(r[3] == 'MCTS' for r in rows)
+    assert float(np.random.random_sample()) == case['next_double']
+
+
+def test_good_opponent_wall_clock(bb):
+    """The reference's own TestGood opponent: FixedMCTS(maxDepth=10, explorationRate=0.85, timeLimit=1)."""
+    good = bb['FixedMCTS'](maxDepth=10, explorationRate=0.85, timeLimit=0.2)
+    s = bb['games']['Connect4']()
+    nxt, v, probs = good.FindMove(s, 0.1)
+    assert good.Root.Plays >= 8 and abs(probs.sum() - 1) < 1e-12 and 0 <= float(v) <= 1
+    assert float(good.SampleValue(s, 1)) in (0.0, 0.5, 1.0)

@@ -141,3 +141,57 @@ def test_random_arena(golden):
         assert boards == case['boards'], (case['game'], case['kind'])
         assert results == [r[0] for r in case['rows']]
         assert stats == case['stats']
+
+
+def vrepr(v):
+    return repr(float(v))
+
+
+def test_rollout_kats(golden):
+    """oracle RolloutSearch (all-ones priors, a fresh random rollout per leaf visit, MCTS.py:346-383) == the unmodified
+    FixedMCTS / DynamicMCTS base classes: visit counts, exact child values, chosen moves and the state of numpy's
+    global MT19937 stream after every move (rollout_kat.json)."""
+    for case in golden('rollout_kat.json'):
+        if case['game'] == 'DragonChess':
+            continue                      # minutes in pure python; the GPU tests cover these cases
+        game = GAMES[case['game']]
+        np.random.seed(case['seed'])
+        m = search_np.RolloutSearch(case['kind'], maxDepth=10, explorationRate=0.85, playLimit=case['playLimit'])
+        s = game()
+        for mv in case['moves']:
+            nxt, v, probs = m.FindMove(s, 1)
+            plays = m.Root.ChildPlays()
+            nz = np.flatnonzero(plays).tolist()
+            assert nz == mv['plays_idx'] and plays[nz].astype(int).tolist() == mv['plays']
+            assert [vrepr(m.Root.Children[a].Value) for a in nz] == mv['child_values']
+            assert m.LastAction == mv['action'] and vrepr(v) == mv['winrate']
+            assert m.Root.Plays == mv['root_plays'] and vrepr(m.Root.Value) == mv['root_value']
+            assert int(np.random.get_state()[2]) == mv['rng_after']
+            assert hashlib.sha256(probs.tobytes()).hexdigest()[:16] == mv['probs_sha']
+            s = nxt
+            m.MoveRoot(s)
+        assert float(np.random.random_sample()) == case['next_double']
+
+
+def test_good_arena(golden):
+    """oracle arena against the rollout opponent == the unmodified Blackbird.TestModels(model, FixedMCTS(maxDepth=10,
+    explorationRate=0.85, playLimit=...)) -- TestGood with a play limit in place of its wall-clock limit (arena_good.json)."""
+    import random
+    for case in golden('arena_good.json'):
+        game = GAMES[case['game']]
+        ev = search_np.KatEvaluator(game.LegalMoves)
+        m = search_np.NetSearch(ev, case['kind'], maxDepth=10, explorationRate=0.85, playLimit=case['playLimit'])
+        boards = []
+
+        def seen(state):
+            boards.append(hashlib.sha256(np.asarray(state.Board, dtype=np.int8).tobytes()
+                                         + bytes([int(state.Player)])).hexdigest()[:12])
+        random.seed(case['seed'])
+        np.random.seed(case['seed'])
+        results = []
+        for _ in range(case['numTests']):
+            good = search_np.RolloutSearch('fixed', maxDepth=10, explorationRate=0.85, playLimit=case['goodPlayLimit'])
+            results.append(selfplay_np.arena_game(m, good, game, case['temp'], seen))
+        assert boards == case['boards'], (case['game'], case['kind'])
+        assert results == case['results']
+        assert float(np.random.random_sample()) == case['next_double']
