@@ -60,6 +60,9 @@ struct StreamCtl {
 #ifdef BB_SEARCH_TIMING
   unsigned long long sdbg[12];
 #endif
+#ifdef BB_NET_TIMING
+  unsigned long long ndbg[8];     // MMA warp: cycles waiting for `ready`, issuing; epilogue warp 0: waiting for `full`, working; staging; tile-layers
+#endif
 };
 
 // Built-in network (net.cu)

@@ -7,7 +7,11 @@
 //   rows    = board cells in a padded raster: a position is (H+1) lines of (W+1) cells, line 0 and
 //             the last column are zero padding shared with the neighbouring line / position, so
 //             the 3x3 neighbour (dy,dx) of a row is simply row + dy*(W+1) + dx and always lands on
-//             a real cell or on a zero row (no bounds tests, no im2col copy);
+//             a real cell or on a zero row (no bounds tests, no im2col copy).  Positions never straddle
+//             a 128-row tile (PPT = 128 / rows-per-position whole positions per tile, the tile's tail rows
+//             stay zero), so the tiles of a batch are INDEPENDENT: tile t of layer l+1 needs only tile t
+//             of layer l, and the layers of different tiles overlap freely (round 1 packed positions
+//             densely, which made every tile wait for its two neighbours: 3.5 k cycles per layer);
 //   A tile  = 128 consecutive rows x 16 input channels, bf16, K-major, SWIZZLE_NONE: the buffer is
 //             [k-half][row][8 channels] so a row is 16 bytes and every tap of the convolution is
 //             the SAME buffer addressed through a descriptor whose start address is shifted by
@@ -18,10 +22,9 @@
 // Warp roles (32 * (4 * TILES + 1) threads): the LAST warp issues every tcgen05.mma (one elected
 // lane) and owns the TMEM allocation; each tile has its own four epilogue warps (one per TMEM lane
 // quarter), so all tiles of a layer drain in parallel.  There is no CTA-wide barrier inside the
-// tower: tile t of layer l+1 is issued as soon as the epilogues of tiles t-1, t, t+1 of layer l have
-// arrived on their `ready` mbarriers (the 3x3 halo never reaches further than one tile), and an
-// epilogue starts when the tile's tcgen05.commit arrives on its `full` mbarrier -- layers flow
-// through the tiles as a wavefront.  Epilogue: tcgen05.ld (32 lanes x 16 columns per warp), + bias,
+// tower: tile t of layer l+1 is issued as soon as the epilogue of tile t of layer l has arrived on its
+// `ready` mbarrier, and an epilogue starts when the tile's tcgen05.commit arrives on its `full`
+// mbarrier -- while the epilogue warps drain one tile the MMA warp already feeds the next.  Epilogue: tcgen05.ld (32 lanes x 16 columns per warp), + bias,
 // (+ skip), ReLU, pack to bf16, two 16-byte st.shared per row into the next layer's A buffer.  The
 // weights arrive with one cp.async.bulk (TMA) while the first batch's planes are decoded.  The
 // last layer's epilogue feeds the heads from the fp32 registers (1x1 convs -> per-cell ReLU ->
@@ -49,17 +52,21 @@ template <class G> struct TcBatch;
 #ifndef BB_TC_PIPES
 #define BB_TC_PIPES 2
 #endif
-template <> struct TcBatch<TicTacToe> { static constexpr int NP = BB_TC_PIPES == 3 ? 32 : 56, PIPES = BB_TC_PIPES; };   // 56 * 16 rows = 896
-template <> struct TcBatch<Connect4> { static constexpr int NP = BB_TC_PIPES == 3 ? 9 : 14, PIPES = BB_TC_PIPES; };     // 14 * 56 rows = 784
-template <> struct TcBatch<DragonChess> { static constexpr int NP = 4, PIPES = 2; };                                    //  4 * 81 rows = 324 (+ a 4032-float policy scratch row per pipeline)
+// TILES = 128-row tiles of one pipeline's batch; NP = PPT * TILES positions
+template <> struct TcBatch<TicTacToe> { static constexpr int TILES = BB_TC_PIPES == 3 ? 4 : 7, PIPES = BB_TC_PIPES; };   // 8 positions of 16 rows per tile: 56
+template <> struct TcBatch<Connect4> { static constexpr int TILES = BB_TC_PIPES == 3 ? 4 : 7, PIPES = BB_TC_PIPES; };    // 2 positions of 56 rows per tile: 14
+template <> struct TcBatch<DragonChess> { static constexpr int TILES = 3, PIPES = 2; };                                  // 1 position of 81 rows per tile: 3 (+ a 4032-float policy scratch row per pipeline)
 
 template <class G>
 struct TcGeom {
-  static constexpr int NP = TcBatch<G>::NP;
   static constexpr int LW = G::W + 1;                       // line width
   static constexpr int RPP = (G::H + 1) * LW;               // rows per position
-  static constexpr int R = NP * RPP;                        // raster rows of a batch
-  static constexpr int TILES = (R + 127) / 128;
+  static constexpr int PPT = 128 / RPP;                     // whole positions per 128-row tile
+  static constexpr int TILES = TcBatch<G>::TILES;
+  static constexpr int NP = PPT * TILES;                    // positions per batch
+  static_assert(PPT >= 1, "a position must fit one tile");
+  // row of (position p of the batch, line, column): positions never straddle a tile
+  __host__ __device__ static constexpr int row_of(int p, int line, int col) { return (p / PPT) * 128 + (p % PPT) * RPP + line * LW + col; }
   static constexpr int ROWS = TILES * 128 + 2 * TC_MARGIN;  // rows allocated per k-half plane
   static constexpr int PLANE = ROWS * 16;                   // bytes per k-half plane
   static constexpr int BUF = 2 * PLANE;                     // one 16-channel activation buffer
@@ -368,7 +375,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             if (open > 0) {
               unsigned want = min((unsigned)Ge::NP, max(1u, ((unsigned)open + srv - 1u) / srv));
               // the tower's cost is per 128-row tile, not per position: fill the last tile while tickets are open
-              const unsigned fill = (((want * Ge::RPP + 127u) >> 7) << 7) / Ge::RPP;
+              const unsigned fill = (want + Ge::PPT - 1u) / Ge::PPT * Ge::PPT;
               want = max(want, min(min(fill, (unsigned)Ge::NP), (unsigned)open));
               pend_lo = atomicAdd(&sv.q->head, want);
               pend_n = want;
@@ -414,23 +421,32 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       cnt = min(ppc, n - base);                             // positions of this batch
       batch += n_pipes;
     }
-    const int tiles = (cnt * Ge::RPP + 127) >> 7;           // 128-row tiles in use
+    const int tiles = (cnt + Ge::PPT - 1) / Ge::PPT;        // 128-row tiles in use
     if (is_mma) {
       // ---- MMA issuer: layers x tiles as a wavefront ---------------------------------------------
       {                                                       // warp-uniform: every lane waits, one elected lane issues
         if (!weights_in) { mbar_wait(wbar, 0); weights_in = true; }
         const uint32_t w_addr = smem_u32(sW);
+#ifdef BB_NET_TIMING
+        long long nt_wait = 0, nt_issue = 0;
+#endif
         for (int layer = 0; layer < layers; ++layer) {
           const bool odd = layer & 1;
           const uint32_t in_addr = smem_u32(layer == 0 ? bufIn : (odd ? bufX : bufY));
           const int kblocks = layer == 0 ? Ge::KB_IN : 1;
           const int wblk0 = layer == 0 ? 0 : Ge::KB_IN * 9 + (layer - 1) * 9;
           for (int t = 0; t < tiles; ++t) {
-            // inputs of tile t live in tiles t-1..t+1 of the previous layer's output; t-1 and t were
-            // observed while issuing tile t-1 (they cannot advance further before this tile is issued)
-            if (t == 0) { mbar_wait(&ready[0], ready_par & 1u); ready_par ^= 1u; }
-            if (t + 1 < tiles) { mbar_wait(&ready[t + 1], (ready_par >> (t + 1)) & 1u); ready_par ^= 1u << (t + 1); }
+            // the inputs of tile t are tile t of the previous layer's output, nothing else (positions do not straddle tiles)
+#ifdef BB_NET_TIMING
+            const long long nt0 = clock64();
+#endif
+            mbar_wait(&ready[t], (ready_par >> t) & 1u);
+            ready_par ^= 1u << t;
             tc_fence_after();
+#ifdef BB_NET_TIMING
+            const long long nt1 = clock64();
+            nt_wait += nt1 - nt0;
+#endif
             {
               const uint64_t adesc = umma_desc(in_addr + (t * 128 + TC_MARGIN) * 16, Ge::PLANE, 128);
               const uint64_t bdesc = umma_desc(w_addr + wblk0 * 512, 256, 128);
@@ -440,8 +456,18 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
                 umma_taps9<Ge::LW, false>(tmem_base + t * 16, a_lo + kb * (Ge::BUF >> 4), a_hi, b_lo + kb * 9 * 32, b_hi, IDESC);
             }
             umma_commit_elect(&full[t]);
+#ifdef BB_NET_TIMING
+            nt_issue += clock64() - nt1;
+#endif
           }
         }
+#ifdef BB_NET_TIMING
+        if (serve && lane == 0) {
+          atomicAdd(&sv.q->ndbg[0], (unsigned long long)nt_wait);
+          atomicAdd(&sv.q->ndbg[1], (unsigned long long)nt_issue);
+          atomicAdd(&sv.q->ndbg[5], (unsigned long long)(layers * tiles));
+        }
+#endif
       }
       __syncwarp();
     } else {
@@ -477,13 +503,17 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         for (int i = 0; i < (int)(sizeof(State) / 4); ++i) dst[i] = __ldcg(reinterpret_cast<const uint32_t*>(src) + i);
       }
       epi_bar_sync<Ge::EPI_THREADS>(pipe);
+#ifdef BB_NET_TIMING
+      long long ne_wait = 0, ne_work = 0, ne_ld = 0, ne_math = 0;
+      const long long ne_stage = clock64();
+#endif
       // input planes (AsInputArray) decoded from the staged states into the raster rows; okmask: this thread's row
       // is a board cell of the batch, per tile
       uint32_t okmask = 0;
       for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
-        const int row = t * 128 + q * 32 + lane;
-        const int pos = row / Ge::RPP, l = row % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
-        if (row < cnt * Ge::RPP && line >= 1 && col < G::W) {
+        const int rt = q * 32 + lane, row = t * 128 + rt;     // row inside the tile / inside the batch raster
+        const int pos = t * Ge::PPT + rt / Ge::RPP, l = rt % Ge::RPP, line = l / Ge::LW, col = l % Ge::LW;
+        if (rt < Ge::PPT * Ge::RPP && pos < cnt && line >= 1 && col < G::W) {
           okmask |= 1u << t;
           const int cell = (line - 1) * G::W + col;
           const State s = *reinterpret_cast<const State*>(sState + pos * ST_STRIDE);
@@ -517,11 +547,22 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
           const int row = t * 128 + q * 32 + lane;
           const bool cell_ok = (okmask >> t) & 1u;
+#ifdef BB_NET_TIMING
+          const long long ne0 = clock64();
+#endif
           mbar_wait(&full[t], (full_par >> t) & 1u);
           full_par ^= 1u << t;
           tc_fence_after();
+#ifdef BB_NET_TIMING
+          const long long ne1 = clock64();
+          ne_wait += ne1 - ne0;
+#endif
           float acc[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + t * 16, acc);
+#ifdef BB_NET_TIMING
+          const long long ne2 = clock64();
+          ne_ld += ne2 - ne1;
+#endif
           if (cell_ok) {
             uint8_t* slot = out + (row + TC_MARGIN) * 16;
 #pragma unroll
@@ -556,14 +597,30 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
               *reinterpret_cast<float4*>(slot) = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
             }
           }
+#ifdef BB_NET_TIMING
+          const long long ne3 = clock64();
+          ne_math += ne3 - ne2;
+#endif
           if (!last) {
             tc_fence_before();
             fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready[t]);
           }
+#ifdef BB_NET_TIMING
+          ne_work += clock64() - ne1;
+#endif
         }
       }
+#ifdef BB_NET_TIMING
+      if (serve && tid == 0) {
+        atomicAdd(&sv.q->ndbg[2], (unsigned long long)ne_wait);
+        atomicAdd(&sv.q->ndbg[3], (unsigned long long)ne_work);
+        atomicAdd(&sv.q->ndbg[4], (unsigned long long)ne_ld);
+        atomicAdd(&sv.q->ndbg[6], (unsigned long long)ne_math);
+      }
+      (void)ne_stage;
+#endif
     }
     // ---- heads: the whole pipeline (MMA warp included) meets here once per batch -----------------------
     team.sync();
@@ -573,13 +630,16 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const int p = pk / 3, k = pk % 3;
       float s = 0.f;
       for (int c = lane; c < G::H * G::W; c += 32)
-        s += reinterpret_cast<const float*>(bufX + (p * Ge::RPP + (c / G::W + 1) * Ge::LW + c % G::W + TC_MARGIN) * 16)[k];
+        s += reinterpret_cast<const float*>(bufX + (Ge::row_of(p, c / G::W + 1, c % G::W) + TC_MARGIN) * 16)[k];
 #pragma unroll
       for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
       if (lane == 0) hsum[p * 4 + k] = s;
     }
     team.sync();
     {
+      // (one warp per position instead of one thread -- lane a = action a, xor-tree softmax, each warp publishing its own
+      // slot -- was measured in round 2 and LOST 4 %: the SM is issue-bound, five warps' worth of full-width instructions
+      // cost the neighbouring epilogue and search warps more than the shorter dependent chain gains)
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
@@ -590,15 +650,15 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       __threadfence();
       team.sync();
       if (tid < cnt) *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
-      if (tid == 0) {
-        const long long tm3 = clock64();
-        atomicAdd(&sv.q->batches, 1ull);
-        atomicAdd(&sv.q->cyc_claim, (unsigned long long)(tm1 - tm0));
-        atomicAdd(&sv.q->cyc_tower, (unsigned long long)(tm2 - tm1));
-        atomicAdd(&sv.q->cyc_heads, (unsigned long long)(tm3 - tm2));
-      }
     }
     team.sync();                                          // X / hsum are rewritten by the next batch
+    if (serve && tid == 0) {
+      const long long tm3 = clock64();
+      atomicAdd(&sv.q->batches, 1ull);
+      atomicAdd(&sv.q->cyc_claim, (unsigned long long)(tm1 - tm0));
+      atomicAdd(&sv.q->cyc_tower, (unsigned long long)(tm2 - tm1));
+      atomicAdd(&sv.q->cyc_heads, (unsigned long long)(tm3 - tm2));
+    }
   }
   tc_fence_before();
   __syncthreads();

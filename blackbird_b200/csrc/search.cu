@@ -217,6 +217,8 @@ struct EngineT : bb_engine {
       const char* cr = getenv("BB_COMPACT_ROUNDS");
       d.compact_rounds = cr ? atoi(cr) : 8;
       if (d.compact_rounds < 1) d.compact_rounds = 1;
+      const char* pf = getenv("BB_PREFETCH");
+      d.prefetch = pf ? atoi(pf) : 0;             // measured neutral while the network kernel is the limiter (profiles/r02_summary.md): off by default
     }
     d.pool_cap = (uint32_t)c.max_plies * (uint32_t)(G::A < 64 ? G::A : 64);
     int rc;
@@ -535,6 +537,15 @@ struct EngineT : bb_engine {
       fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles; search warps busy %.3f, %.0f cycles per advance call\n", h.batches,
               (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches,
               (double)h.cyc_search_busy / (double)(h.cyc_search_total ? h.cyc_search_total : 1), (double)h.cyc_search_busy / (double)(h.search_calls ? h.search_calls : 1));
+#ifdef BB_NET_TIMING
+    if (getenv("BB_DEBUG_STREAM") && h.batches)
+      fprintf(stderr, "[bbengine] network pipeline per batch: MMA warp waits for ready %.0f, issues %.0f; epilogue warp waits for full %.0f, works %.0f; tile-layers %.1f (per tile-layer: wait %.0f issue %.0f | wait %.0f work %.0f)\n",
+              (double)h.ndbg[0] / h.batches, (double)h.ndbg[1] / h.batches, (double)h.ndbg[2] / h.batches, (double)h.ndbg[3] / h.batches, (double)h.ndbg[5] / h.batches,
+              (double)h.ndbg[0] / h.ndbg[5], (double)h.ndbg[1] / h.ndbg[5], (double)h.ndbg[2] / h.ndbg[5], (double)h.ndbg[3] / h.ndbg[5]);
+    if (getenv("BB_DEBUG_STREAM") && h.batches)
+      fprintf(stderr, "[bbengine] epilogue per tile-layer: tcgen05.ld + wait %.0f, bias/skip/relu/pack/store %.0f, fences + arrive %.0f\n", (double)h.ndbg[4] / h.ndbg[5],
+              (double)h.ndbg[6] / h.ndbg[5], ((double)h.ndbg[3] - h.ndbg[4] - h.ndbg[6]) / h.ndbg[5]);
+#endif
 #ifdef BB_SEARCH_TIMING
     if (getenv("BB_DEBUG_STREAM") && h.search_calls) {
       const char* nm[6] = {"load", "post_request", "expand", "select level", "backup", "other"};

@@ -48,8 +48,13 @@ __device__ __forceinline__ NodeHdr shfl_hdr(const NodeHdr& h, int src) {
 // cached value) arrives with the same memory round trip.  Returns the child index (warp-uniform);
 // *best_u receives U_j and *chosen the winner's header.
 // RO (rollout evaluator): priors are the constant 1 and the f64 field holds Node.Value: W_i = Value / Plays in f64.
+// pf_nodes != nullptr (narrow games): every lane also asks L2 for ITS child's own child block before the PUCT
+// arithmetic starts, so the next level's dependent load -- one DRAM round trip of ~1.3 k cycles, the search's critical
+// path (5.4 levels per descent) -- finds the winner's children on their way in whichever child wins.  DRAM is ~2 %
+// busy in this kernel; the extra traffic (all k child blocks instead of one) is what that idle bandwidth is spent on.
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 template <int CHUNKS, bool RO = false>
-__device__ __forceinline__ int puct_select(const Node* kids, int k, double c, double* best_u, NodeHdr* chosen) {
+__device__ __forceinline__ int puct_select(const Node* kids, int k, double c, double* best_u, NodeHdr* chosen, const Node* pf_nodes = nullptr) {
   const int lane = lane_id();
   Node r[CHUNKS];
   uint32_t tot = 0;
@@ -60,6 +65,13 @@ __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, do
       r[ci] = kids[j];
       tot += r[ci].s.plays;
     }
+  }
+  if (CHUNKS == 1 && pf_nodes && lane < k && r[0].h.child_base != NONE) {
+    const char* b = reinterpret_cast<const char*>(pf_nodes + r[0].h.child_base);
+    const int bytes = meta_nchild(r[0].h.meta) * (int)sizeof(Node);
+    prefetch_l2(b);
+    if (bytes > 128) prefetch_l2(b + 128);
+    if (((reinterpret_cast<uintptr_t>(b) & 127) + bytes) > 256) prefetch_l2(b + bytes - 1);
   }
   for (int j = CHUNKS * 32 + lane; j < k; j += 32) tot += kids[j].s.plays;
   tot = __reduce_add_sync(0xFFFFFFFFu, tot);                 // one REDUX instead of five shuffle rounds

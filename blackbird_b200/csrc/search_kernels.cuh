@@ -250,7 +250,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
                ch.child_base, meta_nchild(ch.meta), ch.meta, s.n_nodes, s.ply, s.half, s.root, s.root_plays, s.cp_n, s.cp_head);
 #endif
       BB_ASSERT(ch.child_base + (uint32_t)meta_nchild(ch.meta) <= s.n_nodes);
-      const int j = puct_select<SelectChunks<G>::N, RO>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
+      const int j = puct_select<SelectChunks<G>::N, RO>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen, E.prefetch ? nodes : nullptr);
       const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
       // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
       if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }

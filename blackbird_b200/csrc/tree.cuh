@@ -106,6 +106,7 @@ struct EngineDev {                // passed to kernels by value
   int search, max_depth, max_plies;
   int step_budget;                // tree levels a slot may descend per tick before it yields (keeps ticks short)
   int compact_rounds;             // subtree-copy rounds (32 scanned nodes each) a slot in BB_PH_COMPACT runs per tick
+  int prefetch;                   // 1: a select asks L2 for every child's own child block (BB_PREFETCH=1; off by default)
   double c;                       // ExplorationRate
   // evaluator mailbox
   TickCtl* ctl;
