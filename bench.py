@@ -295,7 +295,7 @@ def run_ours(args):
     if args.prelude > 0:
         eng.stream_moves(args.prelude * G, 32)
     flops = netinit.flops_per_eval(h, w, cin, 7, **NET)
-    names = ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'games_done', 'kernel_launches', 'moves', 'ticks')
+    names = ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'games_done', 'kernel_launches', 'moves', 'ticks', 'cache_lookups', 'cache_hits')
 
     def timed_loop(steps, warmup):
         """W untimed + K timed steps; CUDA events on the engine's stream, barrier + synchronize on both sides, time =
@@ -515,6 +515,9 @@ def run_ours(args):
             'dtype': args.precision, 'data': 'synthetic', 'config': config_dict(args, world),
             'games_per_sec': games_done / (ms * 1e-3), 'evals_per_sec': evals / (ms * 1e-3),
             'moves_per_sec': moves / (ms * 1e-3), 'ticks_per_step': ticks / max(1, args.steps) / world,
+            'eval_cache': {'lookups': cn['cache_lookups'], 'hits': cn['cache_hits'], 'hit_rate': cn['cache_hits'] / max(1.0, cn['cache_lookups']),
+                           'what': 'state-keyed memo of the evaluator shared by all game slots (the reference memoises GetPriors / SampleValue with lru_cache, '
+                                   'Blackbird.py:350,372); evals_per_sec counts the evaluations the network computed; BB_EVAL_CACHE=0 switches it off'},
             'roofline': dominant, 'roofline_other': other_k, 'other_noise_setting': other, 'lanes': eng.lanes, 'streaming': bool(streaming), 'cpu_baseline': cpu, 'e2e': e2e, 'e2e_records': e2e_records,
             'gpu_launches': int(launches), 'clocks': clocks}))
     if world > 1:

@@ -37,7 +37,7 @@ class bb_train_desc(C.Structure):
 
 class bb_counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'ticks',
-                                          'kernel_launches', 'moves', 'games_done')]
+                                          'kernel_launches', 'moves', 'games_done', 'cache_lookups', 'cache_hits')]
 
 
 VP, I32, I = C.c_void_p, C.c_int32, C.c_int

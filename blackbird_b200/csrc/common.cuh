@@ -65,6 +65,32 @@ struct StreamCtl {
 #endif
 };
 
+// Evaluation cache (streaming mode, action counts up to 9).  The reference memoises both evaluator hooks per state --
+// Model.SampleValue and Model.GetPriors are functools.lru_cache(maxsize=4096) methods (Blackbird.py:350,372), shared by
+// all games a Model plays -- and Connect4 searches are full of transpositions: 45 % of the nodes one 400-simulation game
+// evaluates repeat a state it has evaluated before, and two games share 39 % of their states (measured with the oracle).
+// Here the memo is ONE direct-mapped table in HBM shared by every game slot of the engine: 64-byte entries
+//   words 0-3 packed state (key) | 4..12 policy f32[A] | 13 value f32 | 14 tag | 15 unused
+// tag: 0 empty, 1 locked by a writer, otherwise the upper hash bits of the key (>= 2).  Writers are the network pipelines:
+// atomicExch(tag, LOCKED) when the batch is staged (whoever finds it locked already does not insert), fence, payload
+// stores with the answers, the batch's publication fence, tag store.  Readers are the search warps: one coalesced
+// 64-byte read (lane l = word l), key and tag compared, fence, tag read again -- unchanged means no writer touched
+// the payload in between.  With a pure evaluator (epsilon 0) the memo is transparent, so results stay bit-identical
+// (streaming == tick mode tests); with policy noise it freezes the first noisy answer of a state while the entry lives,
+// which is what the reference's lru_cache does to TensorFlow's noise.
+constexpr int ECACHE_WORDS = 16;
+constexpr uint32_t ECACHE_LOCKED = 1u;
+constexpr int ECACHE_MAX_ACTIONS = 9;
+__host__ __device__ __forceinline__ void ecache_hash(const uint32_t k[4], uint32_t mask, uint32_t* idx, uint32_t* tag) {
+  unsigned long long h = ((unsigned long long)k[1] << 32 | k[0]) * 0x9E3779B97F4A7C15ull;
+  h ^= ((unsigned long long)k[3] << 32 | k[2]) * 0xC2B2AE3D27D4EB4Full + (h >> 29);
+  h = (h ^ (h >> 32)) * 0xD6E8FEB86659FD93ull;
+  h ^= h >> 32;
+  *idx = (uint32_t)h & mask;
+  const uint32_t t = (uint32_t)(h >> 32);
+  *tag = t < 2u ? t + 2u : t;
+}
+
 // Built-in network (net.cu)
 struct NetDev;
 struct NetServe {                 // the request ring as the persistent network kernel sees it
@@ -73,6 +99,8 @@ struct NetServe {                 // the request ring as the persistent network 
   const void* q_state;            // [n_games] request states, by slot
   unsigned* resp_seq;
   unsigned q_mask;
+  uint32_t* ecache;               // evaluation cache (nullptr: off), ecache_mask + 1 entries of ECACHE_WORDS words
+  uint32_t ecache_mask;
 };
 // persistent network kernel for streaming mode: serves the ring until the search kernel has left and the ring is empty;
 // answers go to policy[slot][A] / value[slot]

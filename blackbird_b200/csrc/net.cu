@@ -155,11 +155,20 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max, 
 // FAST (the bf16 tensor-core kernel only; its tolerance is 2e-2): wide heads without noise take three passes per
 // position (logits + max with batched non-coherent weight loads, ex2.approx + sum, scaled store) instead of four
 // with two IEEE divisions per action.
+// serve mode: where the narrow heads also store their answers for the evaluation cache (common.cuh); ent[p] = entry index + 1
+// of batch position p when this pipeline holds the entry's lock, 0 otherwise
+struct CacheOut {
+  uint32_t* base = nullptr;
+  const uint32_t* ent = nullptr;
+  const uint8_t* states = nullptr;        // the batch's staged packed states
+  int stride = 0, state_bytes = 0;
+};
+
 template <class G, bool FAST = false>
 __device__ void heads_finish(const NetParams& np, const float* hd, const float* pol_w, const float* pol_b, const float* hsum,
                              float* red, int base, int n, int P, unsigned long long call, float* __restrict__ policy,
                              float* __restrict__ value, const Team& tm, const int* out_idx = nullptr, float* zbuf = nullptr,
-                             long long noise_base = -1) {
+                             long long noise_base = -1, const CacheOut co = CacheOut()) {
   constexpr int HW = G::H * G::W;
   const int tid = tm.tid, nthreads = tm.n;
   // noise element index of position p: serve mode keys it on the full 32-bit ticket (noise_base), launch mode on the batch row
@@ -169,11 +178,20 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
   const float* d1b = d1w + D;
   const float* d2w = d1b + D;
   const float d2b = d2w[D];
+  uint32_t* cent = nullptr;                            // this position's evaluation-cache entry, when this pipeline owns it
+  if (G::A <= ECACHE_MAX_ACTIONS && co.base && tid < P && co.ent[tid]) cent = co.base + (size_t)(co.ent[tid] - 1u) * ECACHE_WORDS;
   if (tid < P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
     const float s = hsum[tid * 4];
     float o = d2b;
     for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
-    value[out_idx ? out_idx[tid] : base + tid] = tanhf(o);
+    const float v = tanhf(o);
+    value[out_idx ? out_idx[tid] : base + tid] = v;
+    if (cent) {
+      cent[13] = __float_as_uint(v);
+      const uint32_t* st = reinterpret_cast<const uint32_t*>(co.states + tid * co.stride);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) cent[i] = i * 4 < co.state_bytes ? st[i] : 0u;
+    }
   }
   // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
   if (G::A <= 32) {
@@ -208,7 +226,11 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
       }
       const size_t orow = out_idx ? (size_t)out_idx[tid] : (size_t)(base + tid);
 #pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) policy[orow * G::A + a] = z[a] / tot;
+      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
+        const float pf = z[a] / tot;
+        policy[orow * G::A + a] = pf;
+        if (G::A <= ECACHE_MAX_ACTIONS && cent) cent[4 + a] = __float_as_uint(pf);
+      }
     }
   } else {
     for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions

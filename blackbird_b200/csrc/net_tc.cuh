@@ -242,7 +242,7 @@ template <class G>
 struct TcSmem {                                  // byte offsets into dynamic shared memory
   using Ge = TcGeom<G>;
   int w, bias, head, wbar, tmem, pipe0, pipe_stride, total;          // shared by both pipelines, then one block per pipeline
-  int x, y, in, hsum, red, idx, st, zb, claim, mbar;                 // offsets inside a pipeline's block
+  int x, y, in, hsum, red, idx, st, zb, ent, claim, mbar;            // offsets inside a pipeline's block
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
@@ -263,6 +263,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     q = (q + 15) & ~15;
     st = q; q += Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);   // the batch's packed states, staged once
     zb = q; q += (G::A > 32 ? G::A : Ge::NP * G::A) * 4;   // wide policy heads: one row of logits / probabilities; narrow ones: the batch's noise draws (heads_finish)
+    ent = q; q += 2 * Ge::NP * 4;                  // streaming mode: evaluation-cache entry (+1) this pipeline locked per position, and its tag
     claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     q = (q + 7) & ~7;
     mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
@@ -310,6 +311,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   constexpr int ST_STRIDE = (int)((sizeof(State) + 15) & ~15u);
   uint8_t* sState = pb + L.st;
   volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(pb + L.claim);
+  uint32_t* sEnt = reinterpret_cast<uint32_t*>(pb + L.ent);          // [NP] entry + 1 (0: not ours), then [NP] tags
   uint64_t* full = reinterpret_cast<uint64_t*>(pb + L.mbar);          // MMA -> epilogue, per tile
   uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
   const int layers = np.layers;
@@ -501,6 +503,20 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         uint32_t* dst = reinterpret_cast<uint32_t*>(sState + tid * ST_STRIDE);
 #pragma unroll
         for (int i = 0; i < (int)(sizeof(State) / 4); ++i) dst[i] = __ldcg(reinterpret_cast<const uint32_t*>(src) + i);
+        if (G::A <= ECACHE_MAX_ACTIONS && serve) {           // evaluation cache: take the entry this answer will go to
+          uint32_t own = 0u, tag = 0u;
+          if (sv.ecache) {
+            uint32_t k[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+            for (int i = 0; i < (int)(sizeof(State) / 4) && i < 4; ++i) k[i] = dst[i];
+            uint32_t idx;
+            ecache_hash(k, sv.ecache_mask, &idx, &tag);
+            if (atomicExch(sv.ecache + (size_t)idx * ECACHE_WORDS + 14, ECACHE_LOCKED) != ECACHE_LOCKED) own = idx + 1u;
+            __threadfence();                                 // the entry reads as invalid before any of its payload changes
+          }
+          sEnt[tid] = own;
+          sEnt[Ge::NP + tid] = tag;
+        }
       }
       epi_bar_sync<Ge::EPI_THREADS>(pipe);
 #ifdef BB_NET_TIMING
@@ -643,13 +659,21 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const int nh = 51 + 3 * np.dense + 1;
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
+      CacheOut co;
+      if (G::A <= ECACHE_MAX_ACTIONS && serve && sv.ecache) {
+        co.base = sv.ecache; co.ent = sEnt; co.states = sState; co.stride = ST_STRIDE; co.state_bytes = (int)sizeof(State);
+      }
       heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
-                      reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll);
+                      reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll, co);
     }
-    if (serve) {                                            // publish: answers first, then the per-slot sequence numbers
+    if (serve) {                                            // publish: answers first, then the per-slot sequence numbers (and the cache tags)
       __threadfence();
       team.sync();
-      if (tid < cnt) *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
+      if (tid < cnt) {
+        *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
+        if (G::A <= ECACHE_MAX_ACTIONS && sv.ecache && sEnt[tid])
+          *reinterpret_cast<volatile uint32_t*>(sv.ecache + (size_t)(sEnt[tid] - 1u) * ECACHE_WORDS + 14) = sEnt[Ge::NP + tid];
+      }
     }
     team.sync();                                          // X / hsum are rewritten by the next batch
     if (serve && tid == 0) {

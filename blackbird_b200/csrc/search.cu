@@ -154,6 +154,8 @@ struct EngineT : bb_engine {
   Counters* counters_dev = nullptr;
   // streaming mode (built-in tensor-core network only): request ring + persistent kernel pair
   StreamCtl* q_dev = nullptr;
+  uint32_t* ecache_dev = nullptr;   // evaluation cache of streaming mode (answers of the CURRENT weights only)
+  size_t ecache_entries = 0;
   cudaStream_t net_stream = nullptr;
   cudaEvent_t st_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double st_search_ms = 0, st_net_ms = 0;
@@ -256,6 +258,19 @@ struct EngineT : bb_engine {
       BB_CUDA(cudaMemset(d.q_ent, 0, qn * sizeof(unsigned long long)));
       BB_CUDA(cudaMemset(d.resp_seq, 0, n * sizeof(unsigned)));
       d.q = nullptr;                                               // set only in the copy handed to the streaming kernels
+      // evaluation cache (common.cuh): 2^22 entries of 64 bytes unless BB_EVAL_CACHE says otherwise (log2 entries; 0 = off)
+      d.ecache = nullptr;
+      d.ecache_mask = 0;
+      if (G::A <= ECACHE_MAX_ACTIONS && c.evaluator == BB_EVAL_NET) {
+        int lg = 22;
+        if (const char* ec = getenv("BB_EVAL_CACHE")) lg = atoi(ec);
+        if (lg > 28) lg = 28;
+        if (lg > 0) {
+          A_(ecache_dev, ((size_t)1 << lg) * ECACHE_WORDS);
+          ecache_entries = (size_t)1 << lg;
+          BB_CUDA(cudaMemset(ecache_dev, 0, ecache_entries * ECACHE_WORDS * sizeof(uint32_t)));
+        }
+      }
       BB_CUDA(cudaStreamCreateWithFlags(&net_stream, cudaStreamNonBlocking));
       for (int i = 0; i < 4; ++i) BB_CUDA(cudaEventCreate(&st_ev[i]));
     }
@@ -314,6 +329,11 @@ struct EngineT : bb_engine {
   int net_load(const bb_net_desc* nd, const float* w, size_t nfl) override {
     BB_CUDA(cudaSetDevice(cfg.device));
     stream_fits = -1;
+    if (ecache_dev) {                                             // new weights (or noise settings): every memoised answer is stale
+      int rc0 = sync_lanes();
+      if (rc0) return rc0;
+      BB_CUDA(cudaMemset(ecache_dev, 0, ecache_entries * ECACHE_WORDS * sizeof(uint32_t)));
+    }
     if (net) { net_destroy(net); net = nullptr; }
     return net_create(G::ID, nd, w, nfl, &net);
   }
@@ -504,6 +524,8 @@ struct EngineT : bb_engine {
     if (rc) return rc;
     EngineDev<G> e = d;
     e.q = q_dev;
+    e.ecache = ecache_dev;
+    e.ecache_mask = ecache_dev ? (uint32_t)(ecache_entries - 1) : 0u;
     const int sms = net_sm_count(net);
     int grid = (d.n_games + STREAM_WARPS_PER_CTA - 1) / STREAM_WARPS_PER_CTA;
     if (grid > sms) grid = sms;
@@ -513,7 +535,7 @@ struct EngineT : bb_engine {
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));
-    NetServe sv{q_dev, d.q_ent, d.q_state, d.resp_seq, d.q_mask};
+    NetServe sv{q_dev, d.q_ent, d.q_state, d.resp_seq, d.q_mask, e.ecache, e.ecache_mask};
     // the network kernel goes first so that its CTAs are resident before the search CTAs spin on it
     BB_CUDA(cudaEventRecord(st_ev[2], net_stream));
     if ((rc = net_serve(net, sv, d.resp_policy, d.resp_value, net_stream))) return rc;
@@ -870,6 +892,7 @@ struct EngineT : bb_engine {
     for (const Counters& x : c) {
       out->sims += x.sims; out->evals += x.evals; out->nodes += x.nodes; out->expansions += x.expansions;
       out->select_steps += x.select_steps; out->moves += x.moves; out->games_done += x.games_done;
+      out->cache_lookups += x.cache_lookups; out->cache_hits += x.cache_hits;
     }
     out->ticks = host_ticks / lanes.size(); out->kernel_launches = host_launches;
     if (do_reset) { BB_CUDA(cudaMemset(counters_dev, 0, c.size() * sizeof(Counters))); host_ticks = host_launches = 0; }

@@ -22,6 +22,7 @@ struct WarpScratch {                   // per-warp shared memory
   uint16_t action[STAGE_MAX];
   uint32_t scan[33];                   // subtree copy: exclusive scan of child counts
   uint32_t obase[32];                  // subtree copy: old child_base per scanned node
+  float cpol[16];                      // policy row of an evaluation-cache hit
 };
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
@@ -178,6 +179,28 @@ __device__ double pairwise_sum_sparse(int k, Get get) {
   return stack[0];
 }
 
+// ---- evaluation cache lookup (common.cuh): true = hit, policy in ws.cpol[0..A), raw value in *value -----------------------
+template <class G>
+__device__ __forceinline__ bool ecache_lookup(const EngineDev<G>& E, const typename G::State& st, WarpScratch& ws, float* value) {
+  static_assert(sizeof(typename G::State) <= 16, "the key is at most four words");
+  uint32_t k[4] = {0u, 0u, 0u, 0u};
+  memcpy(k, &st, sizeof(typename G::State));
+  uint32_t idx, tag;
+  ecache_hash(k, E.ecache_mask, &idx, &tag);
+  const uint32_t* ent = E.ecache + (size_t)idx * ECACHE_WORDS;
+  const int lane = lane_id();
+  const uint32_t w = lane < ECACHE_WORDS ? __ldcg(ent + lane) : 0u;             // one 64-byte transaction, through L2
+  const uint32_t want = lane < 4 ? (lane == 0 ? k[0] : lane == 1 ? k[1] : lane == 2 ? k[2] : k[3]) : tag;
+  if (__ballot_sync(0xFFFFFFFFu, (lane < 4 || lane == 14) && w != want)) return false;
+  __threadfence();                                                              // the second look at the tag comes after the payload reads
+  const uint32_t again = lane == 14 ? *reinterpret_cast<const volatile uint32_t*>(ent + 14) : tag;
+  if (__ballot_sync(0xFFFFFFFFu, again != tag)) return false;                   // a writer took the entry meanwhile
+  if (lane >= 4 && lane < 4 + G::A) ws.cpol[lane - 4] = __uint_as_float(w);
+  *value = __uint_as_float(__shfl_sync(0xFFFFFFFFu, w, 13));
+  __syncwarp();
+  return true;
+}
+
 // ---- a22: AddChildren (MCTS.py:122-139), lazily evaluated ---------------------------------------
 // Creates the k children of `node` (ascending action id) with Plays 0, Value 0 and
 // prior = f64(policy[a]) / sum.  Updates *node_hdr (and its copy in HBM).  Returns k, or -1 when
@@ -186,7 +209,7 @@ __device__ double pairwise_sum_sparse(int k, Get get) {
 // f64 field starts as Node.Value = 0.
 template <class G, bool RO = false>
 __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint32_t node, NodeHdr* node_hdr,
-                           const float* policy, WarpScratch& ws) {
+                           const float* policy, WarpScratch& ws, bool policy_in_smem = false) {
   const int lane = lane_id();
   const uint32_t base = s.n_nodes;
   const int child_player = G::next_player(s.cur_state);
@@ -201,7 +224,7 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     if (lane < k) {
       a = nth_bit(m, lane);
       if (!RO) {
-        p = (double)__ldcg(policy + a);                     // f32 policy * 1.0 (f64 mask); L2 load: written by another SM in streaming mode
+        p = (double)(policy_in_smem ? policy[a] : __ldcg(policy + a));   // f32 policy * 1.0 (f64 mask); L2 load: written by another SM in streaming mode
         ws.prior[lane] = p;
         ws.action[lane] = (uint16_t)a;
       }

@@ -180,7 +180,9 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
   const int dbg_phase0 = s.phase;
   int dbg_iters = 0, dbg_compact = 0;
 #endif
-  unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0;
+  unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0, n_look = 0, n_hit = 0;
+  constexpr bool EC = !RO && G::A <= ECACHE_MAX_ACTIONS;     // evaluation cache: narrow games, network evaluator
+  bool pol_cached = false;                                    // the pending expansion takes its policy from ws.cpol (cache hit)
   uint32_t* prow = E.path + (size_t)g * PATH_LEN;
   Path path;
   Node* nodes = E.half(g, s.half);
@@ -224,6 +226,19 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       if (ch.child_base == NONE) {                              // Children is None
         if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
         if (RO) { step = ST_EXPAND; continue; }                 // AddChildren with GetPriors == ones: nothing to ask
+        if constexpr (EC) if (E.ecache) {                       // the memo of GetPriors / SampleValue (Blackbird.py:350,372)
+          float v;
+          n_look += 1;
+          if (ecache_lookup(E, s.cur_state, ws, &v)) {
+            n_hit += 1;
+            ch.eval = v;
+            ch.meta |= META_HAS_VALUE;
+            if (lane == 0) nodes[s.cur].h = ch;
+            pol_cached = true;
+            step = ST_EXPAND;
+            continue;
+          }
+        }
         ST_ADD(5);
         post_request(E, s, g, par);                             // GetPriors(state) of this node
         ST_ADD(1);
@@ -234,7 +249,9 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
       ST_ADD(5);
-      const int k = expand_node<G, RO>(E, s, nodes, s.cur, &ch, RO ? nullptr : E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws);
+      const int k = expand_node<G, RO>(E, s, nodes, s.cur, &ch, RO ? nullptr : pol_cached ? ws.cpol : E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws,
+                                       pol_cached);
+      pol_cached = false;
       ST_ADD(2);
       if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
       n_exp += 1;
@@ -270,6 +287,16 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
         if (halves < 0) { s.phase = BB_PH_ERROR; break; }
         backup_rollout(s, nodes, path, halves);
       } else {
+      if constexpr (EC) if (E.ecache && !(ch.meta & META_HAS_VALUE)) {
+        float v;
+        n_look += 1;
+        if (ecache_lookup(E, s.cur_state, ws, &v)) {
+          n_hit += 1;
+          ch.eval = v;
+          ch.meta |= META_HAS_VALUE;
+          if (lane == 0) nodes[s.cur].h = ch;
+        }
+      }
       if (!(ch.meta & META_HAS_VALUE)) {
         ST_ADD(5);
         post_request(E, s, g, par);                             // getEvaluation(state) of the leaf
@@ -369,6 +396,8 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
     if (n_sel) atomicAdd(&c->select_steps, n_sel);
     if (n_moves) atomicAdd(&c->moves, n_moves);
     if (n_done) atomicAdd(&c->games_done, n_done);
+    if (n_look) atomicAdd(&c->cache_lookups, n_look);
+    if (n_hit) atomicAdd(&c->cache_hits, n_hit);
   }
   __syncwarp();
   return s.phase;

@@ -82,6 +82,7 @@ struct PairwisePlan {
 
 struct Counters {                 // mirrors bb_counters
   unsigned long long sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
+  unsigned long long cache_lookups, cache_hits;     // evaluation cache (streaming mode): evaluations asked of it / answered by it
 };
 
 // Per-tick control block.  Request / activity counters are double-buffered by tick parity so a
@@ -120,6 +121,8 @@ struct EngineDev {                // passed to kernels by value
   typename G::State* q_state;     // [n_games] the state a slot asks about (a slot has one open request at a time)
   unsigned* resp_seq;             // [n_games]
   unsigned q_mask;
+  uint32_t* ecache;               // evaluation cache (common.cuh); nullptr = off
+  uint32_t ecache_mask;
   // self-play
   int autoplay;                   // 1: choose / move root / end games on the device
   int refill;                     // 1: a finished game's slot starts the next game (steady-state stepping)

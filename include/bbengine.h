@@ -237,6 +237,11 @@ uint64_t bb_trainer_steps(bb_trainer* t);
 /* ---- counters (sims, evals, nodes, depth, expansions, launches) ------------- */
 typedef struct bb_counters {
   uint64_t sims, evals, nodes, expansions, select_steps, ticks, kernel_launches, moves, games_done;
+  /* streaming mode keeps the evaluator's answers in a state-keyed cache shared by all game slots -- the engine-wide form of
+   * the reference's functools.lru_cache on Model.SampleValue / Model.GetPriors (Blackbird.py:350,372).  `evals` counts the
+   * evaluations the network computed; these two count the evaluations asked of the cache and answered by it.
+   * BB_EVAL_CACHE=0 in the environment switches it off (log2 of the entry count otherwise, default 22). */
+  uint64_t cache_lookups, cache_hits;
 } bb_counters;
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset);
 int bb_engine_lanes(bb_engine* e);   /* lanes the engine runs with */

@@ -49,7 +49,7 @@ def test_game_description_needs_no_gpu(lib):
 def test_struct_layouts_match_header(lib):
     assert ctypes.sizeof(lib.bb_config) == 8 * 4 + 8 + 2 * 4 + 6 * 4
     assert ctypes.sizeof(lib.bb_net_desc) == 4 * 4 + 2 * 4 + 8 + 4 + 3 * 4
-    assert ctypes.sizeof(lib.bb_counters) == 9 * 8
+    assert ctypes.sizeof(lib.bb_counters) == 11 * 8
 
 
 def test_no_cpu_fallback(lib):
