@@ -60,7 +60,7 @@ struct StreamCtl {
 #ifdef BB_SEARCH_TIMING
   unsigned long long sdbg[12];
 #endif
-#ifdef BB_NET_TIMING
+#if defined(BB_NET_TIMING_TOWER) || defined(BB_NET_TIMING_HEADS)
   unsigned long long ndbg[8];     // MMA warp: cycles waiting for `ready`, issuing; epilogue warp 0: waiting for `full`, working; staging; tile-layers
 #endif
 };
@@ -113,6 +113,11 @@ int net_create(int game, const bb_net_desc* d, const float* w_host, size_t n_flo
 void net_destroy(NetDev* net);
 int net_forward(NetDev* net, const void* states_dev, int n, const int* count_dev, float* policy, float* value,
                 cudaStream_t stream);
+
+// Release / acquire fence at device scope.  __threadfence() is membar.gl = fence.sc.gpu, the sequentially consistent fence (~1.2 k
+// cycles measured in the serve-mode publication); every hand-off in the streaming engine is a message-passing pattern
+// (payload stores, fence, flag store | flag load, fence, payload loads) that needs no store -> load ordering.
+__device__ __forceinline__ void fence_acq_rel() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
 static inline unsigned grid_for(long long n, int block) { return (unsigned)((n + block - 1) / block); }
 

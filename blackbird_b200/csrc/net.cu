@@ -178,61 +178,69 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
   const float* d1b = d1w + D;
   const float* d2w = d1b + D;
   const float d2b = d2w[D];
-  uint32_t* cent = nullptr;                            // this position's evaluation-cache entry, when this pipeline owns it
-  if (G::A <= ECACHE_MAX_ACTIONS && co.base && tid < P && co.ent[tid]) cent = co.base + (size_t)(co.ent[tid] - 1u) * ECACHE_WORDS;
-  if (tid < P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
-    const float s = hsum[tid * 4];
-    float o = d2b;
-    for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(s, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
-    const float v = tanhf(o);
-    value[out_idx ? out_idx[tid] : base + tid] = v;
-    if (cent) {
-      cent[13] = __float_as_uint(v);
-      const uint32_t* st = reinterpret_cast<const uint32_t*>(co.states + tid * co.stride);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) cent[i] = i * 4 < co.state_bytes ? st[i] : 0u;
-    }
-  }
-  // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
   if (G::A <= 32) {
-    const bool noisy = np.eps > 0.f;
-    if (noisy) {                                           // one Beta draw per (position, action), spread over the whole team
-      const unsigned long long key = np.seed ^ (call * 0x632BE59BD9B4E019ull);
-      for (int i = tid; i < P * G::A; i += nthreads) {
-        const int p = i / G::A;
-        if (base + p < n) zbuf[i] = beta_noise(np.alpha, key, (nb + p) * G::A + (i - p * G::A));
+    // Narrow heads: GP lanes per position (8 for up to 8 actions, 16 up to 16, else 32), all positions of the batch side by
+    // side in one or two warps.  Lane j of a group owns action j (logit, softmax through fixed-order xor trees of width GP,
+    // its own noise draw, renormalisation) and the dense units j, j + GP, ... of the value head.  Round 1 gave a whole
+    // position to ONE thread (7 expf, 14 divisions, a tanh and a 16-step dependent loop in a row: most of the cycles a
+    // serve-mode batch spent after its tower); a whole WARP per position was measured too and lost -- the SM is short of
+    // issue slots, not of lanes.
+    constexpr int GP = G::A <= 8 ? 8 : G::A <= 16 ? 16 : 32;
+    for (int pb = 0; pb < P; pb += nthreads / GP)         // a team of 160 threads covers 20 Connect4 or 10 TicTacToe positions per pass
+    if ((tid & ~31) < (P - pb) * GP) {                    // whole warps only: the shuffles below need all 32 lanes
+      const int p = pb + tid / GP, j = tid % GP;
+      const bool live = p < P && base + p < n;
+      const int pc = live ? p : 0;
+      uint32_t* cent = nullptr;                          // this position's evaluation-cache entry, when this pipeline owns it
+      if (G::A <= ECACHE_MAX_ACTIONS && co.base && live && co.ent[p]) cent = co.base + (size_t)(co.ent[p] - 1u) * ECACHE_WORDS;
+      const size_t orow = out_idx ? (size_t)out_idx[pc] : (size_t)(base + pc);
+      // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
+      const float sv = hsum[pc * 4];
+      float part = 0.f;
+      for (int d = j; d < D; d += GP) part = fmaf(fmaxf(fmaf(sv, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], part);
+#pragma unroll
+      for (int o = GP / 2; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o, GP);
+      if (live && j == 0) {
+        const float v = tanhf(part + d2b);
+        value[orow] = v;
+        if (cent) {
+          cent[13] = __float_as_uint(v);
+          const uint32_t* st = reinterpret_cast<const uint32_t*>(co.states + p * co.stride);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) cent[i] = i * 4 < co.state_bytes ? st[i] : 0u;
+        }
       }
-      tm.sync();
-    }
-    if (tid < P && base + tid < n) {
-      const float s0 = hsum[tid * 4 + 1], s1 = hsum[tid * 4 + 2];
-      float z[G::A <= 32 ? G::A : 1];
-      float m = -INFINITY;
+      // policy: dense(2->A)+sum, softmax, noise mix, renormalise (NetworkFactory.py:165-182)
+      const bool act = j < G::A;
+      const int a = act ? j : 0;
+      const float s0 = hsum[pc * 4 + 1], s1 = hsum[pc * 4 + 2];
+      const float z = act ? fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a])) : -INFINITY;
+      float m = z;
 #pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-        z[a] = fmaf(s0, pol_w[a], fmaf(s1, pol_w[G::A + a], (float)HW * pol_b[a]));
-        m = fmaxf(m, z[a]);
-      }
-      float sum = 0.f;
+      for (int o = GP / 2; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o, GP));
+      const float e = act ? expf(z - m) : 0.f;
+      float sum = e;
 #pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) { z[a] = expf(z[a] - m); sum += z[a]; }
-      float tot = 0.f;
+      for (int o = GP / 2; o; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o, GP);
+      float pa = e / sum;
+      if (np.eps > 0.f && act && live)
+        pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (nb + p) * G::A + a);
+      float tot = pa;
 #pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-        float pa = z[a] / sum;
-        if (noisy) pa = (1.f - np.eps) * pa + np.eps * zbuf[tid * G::A + a];
-        z[a] = pa;
-        tot += pa;
-      }
-      const size_t orow = out_idx ? (size_t)out_idx[tid] : (size_t)(base + tid);
-#pragma unroll
-      for (int a = 0; a < (G::A <= 32 ? G::A : 1); ++a) {
-        const float pf = z[a] / tot;
+      for (int o = GP / 2; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o, GP);
+      if (live && act) {
+        const float pf = pa / tot;
         policy[orow * G::A + a] = pf;
         if (G::A <= ECACHE_MAX_ACTIONS && cent) cent[4 + a] = __float_as_uint(pf);
       }
     }
   } else {
+    if (tid < P && base + tid < n) {                     // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
+      const float sv = hsum[tid * 4];
+      float o = d2b;
+      for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(sv, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
+      value[out_idx ? out_idx[tid] : base + tid] = tanhf(o);
+    }
     for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
       const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
       float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;

@@ -394,7 +394,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             }
           }
           if (*vdone >= ctas) {                                 // the search has left: nothing more will be issued
-            __threadfence();
+            fence_acq_rel();
             if (pend_n) { if ((int)(*vt - pend_lo) > 0) continue; pend_n = 0; }
             if ((int)(*vt - *vh) <= 0) { c = 0; break; }        // nobody left to ask
             continue;
@@ -429,7 +429,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       {                                                       // warp-uniform: every lane waits, one elected lane issues
         if (!weights_in) { mbar_wait(wbar, 0); weights_in = true; }
         const uint32_t w_addr = smem_u32(sW);
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
         long long nt_wait = 0, nt_issue = 0;
 #endif
         for (int layer = 0; layer < layers; ++layer) {
@@ -439,13 +439,13 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           const int wblk0 = layer == 0 ? 0 : Ge::KB_IN * 9 + (layer - 1) * 9;
           for (int t = 0; t < tiles; ++t) {
             // the inputs of tile t are tile t of the previous layer's output, nothing else (positions do not straddle tiles)
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
             const long long nt0 = clock64();
 #endif
             mbar_wait(&ready[t], (ready_par >> t) & 1u);
             ready_par ^= 1u << t;
             tc_fence_after();
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
             const long long nt1 = clock64();
             nt_wait += nt1 - nt0;
 #endif
@@ -458,12 +458,12 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
                 umma_taps9<Ge::LW, false>(tmem_base + t * 16, a_lo + kb * (Ge::BUF >> 4), a_hi, b_lo + kb * 9 * 32, b_hi, IDESC);
             }
             umma_commit_elect(&full[t]);
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
             nt_issue += clock64() - nt1;
 #endif
           }
         }
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
         if (serve && lane == 0) {
           atomicAdd(&sv.q->ndbg[0], (unsigned long long)nt_wait);
           atomicAdd(&sv.q->ndbg[1], (unsigned long long)nt_issue);
@@ -494,7 +494,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
           } else {
             *ent = v & 0x7FFFFFFFFFFFFFFFull;                // entry read: ticket tk + ring may publish here
           }
-          __threadfence();                                   // acquire: the slot's state was written before the entry
+          fence_acq_rel();                                   // acquire: the slot's state was written before the entry
           src = reinterpret_cast<const State*>(sv.q_state) + slot;
           sIdx[tid] = slot;                                  // where the answer goes
         } else {
@@ -512,14 +512,14 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             uint32_t idx;
             ecache_hash(k, sv.ecache_mask, &idx, &tag);
             if (atomicExch(sv.ecache + (size_t)idx * ECACHE_WORDS + 14, ECACHE_LOCKED) != ECACHE_LOCKED) own = idx + 1u;
-            __threadfence();                                 // the entry reads as invalid before any of its payload changes
+            fence_acq_rel();                                 // the entry reads as invalid before any of its payload changes
           }
           sEnt[tid] = own;
           sEnt[Ge::NP + tid] = tag;
         }
       }
       epi_bar_sync<Ge::EPI_THREADS>(pipe);
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
       long long ne_wait = 0, ne_work = 0, ne_ld = 0, ne_math = 0;
       const long long ne_stage = clock64();
 #endif
@@ -563,19 +563,19 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
         for (int t = wg; t < tiles; t += Ge::EPI_GROUPS) {
           const int row = t * 128 + q * 32 + lane;
           const bool cell_ok = (okmask >> t) & 1u;
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
           const long long ne0 = clock64();
 #endif
           mbar_wait(&full[t], (full_par >> t) & 1u);
           full_par ^= 1u << t;
           tc_fence_after();
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
           const long long ne1 = clock64();
           ne_wait += ne1 - ne0;
 #endif
           float acc[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + t * 16, acc);
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
           const long long ne2 = clock64();
           ne_ld += ne2 - ne1;
 #endif
@@ -613,7 +613,7 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
               *reinterpret_cast<float4*>(slot) = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
             }
           }
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
           const long long ne3 = clock64();
           ne_math += ne3 - ne2;
 #endif
@@ -623,12 +623,12 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready[t]);
           }
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
           ne_work += clock64() - ne1;
 #endif
         }
       }
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
       if (serve && tid == 0) {
         atomicAdd(&sv.q->ndbg[2], (unsigned long long)ne_wait);
         atomicAdd(&sv.q->ndbg[3], (unsigned long long)ne_work);
@@ -652,6 +652,10 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       if (lane == 0) hsum[p * 4 + k] = s;
     }
     team.sync();
+#ifdef BB_NET_TIMING_HEADS
+    long long th1 = 0, th2 = 0, th3 = 0, th4 = 0;
+    if (serve && tid == 0) th1 = clock64();
+#endif
     {
       // (one warp per position instead of one thread -- lane a = action a, xor-tree softmax, each warp publishing its own
       // slot -- was measured in round 2 and LOST 4 %: the SM is issue-bound, five warps' worth of full-width instructions
@@ -666,16 +670,36 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
                       reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll, co);
     }
+#ifdef BB_NET_TIMING_HEADS
+    if (serve && tid == 0) th2 = clock64();
+#endif
     if (serve) {                                            // publish: answers first, then the per-slot sequence numbers (and the cache tags)
-      __threadfence();
+      fence_acq_rel();
+#ifdef BB_NET_TIMING_HEADS
+      if (tid == 0) th3 = clock64();
+#endif
       team.sync();
+#ifdef BB_NET_TIMING_HEADS
+      if (tid == 0) th4 = clock64();
+#endif
       if (tid < cnt) {
+        fence_acq_rel();                                    // release by the publishing thread itself (the answers were written by its team mates before the barrier)
         *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[sIdx[tid]]) = ticket0 + (unsigned)tid + 1u;
         if (G::A <= ECACHE_MAX_ACTIONS && sv.ecache && sEnt[tid])
           *reinterpret_cast<volatile uint32_t*>(sv.ecache + (size_t)(sEnt[tid] - 1u) * ECACHE_WORDS + 14) = sEnt[Ge::NP + tid];
       }
     }
     team.sync();                                          // X / hsum are rewritten by the next batch
+#ifdef BB_NET_TIMING_HEADS
+    if (serve && tid == 0) {
+      const long long th5 = clock64();
+      atomicAdd(&sv.q->ndbg[0], (unsigned long long)(th1 - tm2));   // hsum pass + sync
+      atomicAdd(&sv.q->ndbg[1], (unsigned long long)(th2 - th1));   // heads_finish
+      atomicAdd(&sv.q->ndbg[2], (unsigned long long)(th3 - th2));   // fence
+      atomicAdd(&sv.q->ndbg[3], (unsigned long long)(th4 - th3));   // sync after fence
+      atomicAdd(&sv.q->ndbg[7], (unsigned long long)(th5 - th4));   // publish + last sync
+    }
+#endif
     if (serve && tid == 0) {
       const long long tm3 = clock64();
       atomicAdd(&sv.q->batches, 1ull);

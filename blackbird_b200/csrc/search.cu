@@ -559,7 +559,7 @@ struct EngineT : bb_engine {
       fprintf(stderr, "[bbengine] streaming: %llu batches; per batch: wait %.0f, tower %.0f, heads+publish %.0f cycles; search warps busy %.3f, %.0f cycles per advance call\n", h.batches,
               (double)h.cyc_claim / h.batches, (double)h.cyc_tower / h.batches, (double)h.cyc_heads / h.batches,
               (double)h.cyc_search_busy / (double)(h.cyc_search_total ? h.cyc_search_total : 1), (double)h.cyc_search_busy / (double)(h.search_calls ? h.search_calls : 1));
-#ifdef BB_NET_TIMING
+#ifdef BB_NET_TIMING_TOWER
     if (getenv("BB_DEBUG_STREAM") && h.batches)
       fprintf(stderr, "[bbengine] network pipeline per batch: MMA warp waits for ready %.0f, issues %.0f; epilogue warp waits for full %.0f, works %.0f; tile-layers %.1f (per tile-layer: wait %.0f issue %.0f | wait %.0f work %.0f)\n",
               (double)h.ndbg[0] / h.batches, (double)h.ndbg[1] / h.batches, (double)h.ndbg[2] / h.batches, (double)h.ndbg[3] / h.batches, (double)h.ndbg[5] / h.batches,
@@ -567,6 +567,11 @@ struct EngineT : bb_engine {
     if (getenv("BB_DEBUG_STREAM") && h.batches)
       fprintf(stderr, "[bbengine] epilogue per tile-layer: tcgen05.ld + wait %.0f, bias/skip/relu/pack/store %.0f, fences + arrive %.0f\n", (double)h.ndbg[4] / h.ndbg[5],
               (double)h.ndbg[6] / h.ndbg[5], ((double)h.ndbg[3] - h.ndbg[4] - h.ndbg[6]) / h.ndbg[5]);
+#endif
+#ifdef BB_NET_TIMING_HEADS
+    if (getenv("BB_DEBUG_STREAM") && h.batches)
+      fprintf(stderr, "[bbengine] heads phase per batch: sums + sync %.0f, heads_finish %.0f, fence %.0f, sync %.0f, publish + last sync %.0f\n", (double)h.ndbg[0] / h.batches,
+              (double)h.ndbg[1] / h.batches, (double)h.ndbg[2] / h.batches, (double)h.ndbg[3] / h.batches, (double)h.ndbg[7] / h.batches);
 #endif
 #ifdef BB_SEARCH_TIMING
     if (getenv("BB_DEBUG_STREAM") && h.search_calls) {

@@ -192,7 +192,7 @@ __device__ __forceinline__ bool ecache_lookup(const EngineDev<G>& E, const typen
   const uint32_t w = lane < ECACHE_WORDS ? __ldcg(ent + lane) : 0u;             // one 64-byte transaction, through L2
   const uint32_t want = lane < 4 ? (lane == 0 ? k[0] : lane == 1 ? k[1] : lane == 2 ? k[2] : k[3]) : tag;
   if (__ballot_sync(0xFFFFFFFFu, (lane < 4 || lane == 14) && w != want)) return false;
-  __threadfence();                                                              // the second look at the tag comes after the payload reads
+  fence_acq_rel();                                                              // the second look at the tag comes after the payload reads
   const uint32_t again = lane == 14 ? *reinterpret_cast<const volatile uint32_t*>(ent + 14) : tag;
   if (__ballot_sync(0xFFFFFFFFu, again != tag)) return false;                   // a writer took the entry meanwhile
   if (lane >= 4 && lane < 4 + G::A) ws.cpol[lane - 4] = __uint_as_float(w);

@@ -20,7 +20,7 @@ __device__ __forceinline__ void post_request(const EngineDev<G>& E, Slot<G>& s, 
       idx = (int)atomicAdd(&E.q->tail, 1u);
       volatile unsigned long long* ent = reinterpret_cast<volatile unsigned long long*>(&E.q_ent[(unsigned)idx & E.q_mask]);
       unsigned long long was = *ent;                          // the entry's previous ticket (idx - ring) must have been read by its pipeline
-      __threadfence();                                        // state before entry
+      fence_acq_rel();                                        // state before entry
       while ((unsigned)(was >> 32) & RING_PUBLISHED) { __nanosleep(100); was = *ent; }
       *ent = ((unsigned long long)((unsigned)g | RING_PUBLISHED) << 32) | (unsigned)idx;
     }
@@ -447,7 +447,7 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
       if (st == 1) {
         const unsigned have = *reinterpret_cast<volatile unsigned*>(&E.resp_seq[g]);
         if (have != s_ticket[wl][j] + 1u) { any_busy = true; continue; }
-        __threadfence();                                     // acquire: the answer was written before its sequence number
+        fence_acq_rel();                                     // acquire: the answer was written before its sequence number
       }
       uint32_t ticket = 0;
       const long long t0 = clock64();
