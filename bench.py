@@ -28,6 +28,18 @@ sys.path.insert(0, ROOT)
 GAME, SEARCH, MAX_DEPTH, C_PUCT = 'Connect4', 'fixed', 10, 0.85
 NET = dict(blocks=4, filters=16, dense=16)
 METRIC, UNIT = 'connect4_mcts_simulations_per_sec', 'sims/s'
+MAX_PLIES, LABEL = None, 'BASELINE configs[1]'
+# --config: the default line is BASELINE configs[1] (the configuration the metric is quoted on); the others give the
+# remaining self-play configurations of BASELINE.json a bench line of the same shape (same timing rules, same keys)
+CONFIGS = {
+    'connect4': dict(game='Connect4', search='fixed', sims=800, games=4096, prelude=45, max_plies=None, label='BASELINE configs[1]'),
+    'connect4-dynamic': dict(game='Connect4', search='dynamic', sims=800, games=2048, prelude=45, max_plies=None,
+                             label='BASELINE configs[2]: one GPU share of 16384 games on 8 GPUs'),
+    'dragonchess': dict(game='DragonChess', search='fixed', sims=100, games=1024, prelude=4, max_plies=64,
+                        label='BASELINE configs[3], 64-ply cap per game (the reference has no move cap, SURVEY.md A.20)'),
+    'tictactoe': dict(game='TicTacToe', search='fixed', sims=10, games=4096, prelude=4, max_plies=None,
+                      label='BASELINE configs[0]: parameters_template.yaml defaults'),
+}
 
 
 def parse():
@@ -36,28 +48,41 @@ def parse():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--games', type=int, default=4096, help='concurrent games per GPU')
-    ap.add_argument('--sims', type=int, default=800, help='simulations per move (playLimit)')
+    ap.add_argument('--config', default='connect4', choices=sorted(CONFIGS), help='workload (default: BASELINE configs[1])')
+    ap.add_argument('--games', type=int, default=None, help='concurrent games per GPU (default: the config\'s)')
+    ap.add_argument('--sims', type=int, default=None, help='simulations per move (playLimit; default: the config\'s)')
     ap.add_argument('--epsilon', type=float, default=0.3, help='policy noise weight of the headline loop (parameters_template.yaml: 0.3, alpha 0.2)')
     ap.add_argument('--other-epsilon', type=float, default=0.0, help='second timed loop at this noise weight (0 = the parity setting); <0: skip')
     ap.add_argument('--cpu-seconds', type=float, default=25.0, help='cpu_baseline sample length (GPU arm)')
     ap.add_argument('--ref-seconds', type=float, default=150.0, help='--impl reference: total length of warm-up + timed windows')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
     ap.add_argument('--lanes', type=int, default=0, help='engine lanes (0 = engine default)')
-    ap.add_argument('--prelude', type=int, default=45, help='untimed move rounds at 32 sims/move that desynchronise the game slots')
+    ap.add_argument('--prelude', type=int, default=None, help='untimed move rounds at <= 32 sims/move that desynchronise the game slots')
     ap.add_argument('--e2e-rounds', type=int, default=4, help='e2e plays this many times --games whole games per GPU on the --games slots')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-e2e-records', action='store_true')
-    return ap.parse_args()
+    args = ap.parse_args()
+    global GAME, SEARCH, METRIC, MAX_PLIES, LABEL
+    c = CONFIGS[args.config]
+    GAME, SEARCH, MAX_PLIES, LABEL = c['game'], c['search'], c['max_plies'], c['label']
+    METRIC = '%s_mcts_simulations_per_sec' % GAME.lower()
+    args.games = args.games or c['games']
+    args.sims = args.sims or c['sims']
+    args.prelude = c['prelude'] if args.prelude is None else args.prelude
+    if args.config != 'connect4':                  # the CPU arm and the mirror-level e2e are measured on the headline configuration
+        args.no_cpu = True
+        args.no_e2e_records = True
+    return args
 
 
 def config_dict(args, n_gpus):
-    return {'workload': 'Connect4 FixedMCTS(maxDepth 10, c 0.85) self-play, %d sims/move, %d concurrent games/GPU, '
-                        'network blocks4/filters16/dense16 (BASELINE configs[1])' % (args.sims, args.games),
-            'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS', 'max_depth': MAX_DEPTH,
+    search = 'FixedMCTS(maxDepth 10, c 0.85)' if SEARCH == 'fixed' else 'DynamicMCTS(c 0.85)'
+    return {'workload': '%s %s self-play, %d sims/move, %d concurrent games/GPU, '
+                        'network blocks4/filters16/dense16 (%s)' % (GAME, search, args.sims, args.games, LABEL),
+            'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS' if SEARCH == 'fixed' else 'DynamicMCTS', 'max_depth': MAX_DEPTH,
             'step': 'one move round: the %d slots together play %d moves (FindMove+MoveRoot each), no barrier between moves, finished games restart in place' % (args.games, args.games),
-            'prelude': '%d untimed move rounds at 32 sims/move to desynchronise the slots, then the warm-up steps' % args.prelude,
+            'prelude': '%d untimed move rounds at %d sims/move to desynchronise the slots, then the warm-up steps' % (args.prelude, min(32, args.sims)),
             'epsilon': args.epsilon, 'alpha': 0.2,
             'noise': ('policy noise ON as in parameters_template.yaml (every evaluation mixes Beta(alpha, 1-alpha) draws into the policy, NetworkFactory.py:176-182)'
                       if args.epsilon > 0 else 'policy noise off (the parity setting)'),
@@ -269,9 +294,11 @@ def run_ours(args):
 
     G, P = args.games, args.sims
     h, w, cin = plane_shape(GAME)
+    from blackbird_b200.engine import n_actions, state_bytes
+    A, S = n_actions(GAME), state_bytes(GAME)
     eng = Engine(GAME, SEARCH, n_games=G, max_depth=MAX_DEPTH, exploration_rate=C_PUCT, evaluator='net',
-                 play_limit_hint=P, device=local, lanes=args.lanes)
-    weights = netinit.random_weights(cin, 7, seed=0, **NET)
+                 play_limit_hint=P, device=local, lanes=args.lanes, max_plies=MAX_PLIES)
+    weights = netinit.random_weights(cin, A, seed=0, **NET)
 
     def load_net(eps):
         eng.load_network(weights, NET['blocks'], NET['filters'], NET['dense'], epsilon=eps, alpha=0.2, seed=1 + rank, precision=args.precision)
@@ -291,10 +318,10 @@ def run_ours(args):
     # sizes) are in lock-step for a whole game length.  Playing ~1.5 game lengths of cheap moves
     # (32 simulations each) spreads the slots over all game phases; the warm-up steps that follow
     # then rebuild full 800-simulation trees before anything is timed.
-    eng.stream_moves(1, 32, 1.0, uniforms)           # uploads the uniform table
+    eng.stream_moves(1, min(32, P), 1.0, uniforms)   # uploads the uniform table
     if args.prelude > 0:
-        eng.stream_moves(args.prelude * G, 32)
-    flops = netinit.flops_per_eval(h, w, cin, 7, **NET)
+        eng.stream_moves(args.prelude * G, min(32, P))
+    flops = netinit.flops_per_eval(h, w, cin, A, **NET)
     names = ('sims', 'evals', 'nodes', 'expansions', 'select_steps', 'games_done', 'kernel_launches', 'moves', 'ticks', 'cache_lookups', 'cache_hits')
 
     def timed_loop(steps, warmup):
@@ -351,8 +378,9 @@ def run_ours(args):
     hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
     peak_src = 'measured (MEASURED_PEAKS.json, sustained bf16: the kernel runs inside a long step)' if peaks else 'fallback'
     traffic = {}
-    try:                                             # ncu DRAM bytes of the same kernels in tick mode (profiles/r02_traffic.json)
-        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')))
+    try:                                             # ncu DRAM bytes of the same kernels in tick mode (profiles/r02_traffic.json: Connect4)
+        if args.config == 'connect4':
+            traffic = json.load(open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')))
     except Exception:
         pass
     if streaming:
@@ -376,27 +404,27 @@ def run_ours(args):
     k_bar = cp['nodes'] / max(1, cp['expansions'])
     # select: one 32-byte node per child per level; expand: k 32-byte nodes + the parent's header; evaluator
     # mailbox: state out/in + policy/value out/in; backup: 8-byte read-modify-write per path node
-    b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * 16 + 2 * 4 * 8) + 16 * (d_bar + 1)
+    b_sim = d_bar * 32 * k_bar + nexp * (k_bar * 32 + 16) + (cp['evals'] / max(1, cp['sims'])) * (2 * S + 2 * 4 * (min(A, k_bar) + 1)) + 16 * (d_bar + 1)
     tree_gbs = cp['sims'] * b_sim / (adv_ms * 1e-3) / 1e9 if adv_ms > 0 else 0.0
     per_world = max(1, world)
     if streaming:
-        kname = 'k_net_forward_tc<Connect4> serve mode (bf16 tcgen05 tower, persistent: %d evals/launch/GPU, batches of %.2f)' % (
+        kname = 'k_net_forward_tc<%s> serve mode' % GAME + ' (bf16 tcgen05 tower, persistent: %d evals/launch/GPU, batches of %.2f)' % (
             cp['evals'] / n_launch / per_world, cp['evals'] / per_world / prof_ticks)
     elif args.precision == 'bf16':
-        kname = 'k_net_forward_tc<Connect4> (bf16 tcgen05 tower, %d evals/launch avg)' % (cp['evals'] / prof_ticks)
+        kname = 'k_net_forward_tc<%s> (bf16 tcgen05 tower, %d evals/launch avg)' % (GAME, cp['evals'] / prof_ticks)
     else:
-        kname = 'k_net_forward<Connect4> (fp32 SIMT tower, %d evals/launch avg)' % (cp['evals'] / prof_ticks)
+        kname = 'k_net_forward<%s> (fp32 SIMT tower, %d evals/launch avg)' % (GAME, cp['evals'] / prof_ticks)
     net_traffic = None
     if traffic.get('net_dram_bytes_per_eval') is not None:
         net_traffic = traffic['net_dram_bytes_per_eval'] * cp['evals'] / per_world / n_launch
     roofline = {'bound': 'tensor', 'kernel': kname,
                 'achieved': net_tflops / per_world, 'peak': tensor_peak, 'unit': 'TFLOP/s', 'frac': net_tflops / per_world / tensor_peak,
                 'traffic': net_traffic, 'traffic_how': traffic.get('how'), 'peak_source': peak_src, 'flops_per_eval': flops,
-                'algorithmic_bytes_per_eval': 16 + 4 * 8, 'dram_bytes_per_eval_ncu': traffic.get('net_dram_bytes_per_eval'),
+                'algorithmic_bytes_per_eval': S + 4 * (A + 1), 'dram_bytes_per_eval_ncu': traffic.get('net_dram_bytes_per_eval'),
                 'launch_ms_avg': eval_ms / n_launch, 'from': 'the timed loop (evals and CUDA-event time of the %d timed steps)' % args.steps if streaming else 'one profiled step',
                 'step_share': eval_ms / max(1e-9, eval_ms + adv_ms)}
-    roofline_tree = {'bound': 'hbm', 'kernel': ('k_search_stream<Connect4> (persistent select/expand/backup)' if streaming
-                                                else 'k_advance<Connect4> (select/expand/backup)'), 'achieved': tree_gbs / per_world, 'peak': hbm_peak,
+    roofline_tree = {'bound': 'hbm', 'kernel': ('k_search_stream<%s> (persistent select/expand/backup)' % GAME if streaming
+                                                else 'k_advance<%s> (select/expand/backup)' % GAME), 'achieved': tree_gbs / per_world, 'peak': hbm_peak,
                      'unit': 'GB/s', 'frac': tree_gbs / per_world / hbm_peak, 'bytes_per_sim_model': b_sim, 'mean_depth': d_bar,
                      'dram_bytes_per_sim_ncu': traffic.get('search_dram_bytes_per_sim'),
                      'traffic': (traffic['search_dram_bytes_per_sim'] * cp['sims'] / per_world / n_launch) if traffic.get('search_dram_bytes_per_sim') is not None else None,

@@ -101,6 +101,7 @@ struct NetServe {                 // the request ring as the persistent network 
   unsigned q_mask;
   uint32_t* ecache;               // evaluation cache (nullptr: off), ecache_mask + 1 entries of ECACHE_WORDS words
   uint32_t ecache_mask;
+  int legal_only;                 // wide policy heads: answer at the legal actions of the asked position only (engine-internal calls)
 };
 // persistent network kernel for streaming mode: serves the ring until the search kernel has left and the ring is empty;
 // answers go to policy[slot][A] / value[slot]
@@ -111,8 +112,9 @@ int net_tc_footprint(NetDev* net, int* regs, int* smem);
 bool net_is_tc(NetDev* net);
 int net_create(int game, const bb_net_desc* d, const float* w_host, size_t n_floats, NetDev** out);
 void net_destroy(NetDev* net);
+// legal_only (wide heads of the bf16 kernel): the caller reads the policy at the legal actions of each state only (the search does)
 int net_forward(NetDev* net, const void* states_dev, int n, const int* count_dev, float* policy, float* value,
-                cudaStream_t stream);
+                cudaStream_t stream, int legal_only = 0);
 
 // Release / acquire fence at device scope.  __threadfence() is membar.gl = fence.sc.gpu, the sequentially consistent fence (~1.2 k
 // cycles measured in the serve-mode publication); every hand-off in the streaming engine is a message-passing pattern

@@ -162,6 +162,7 @@ struct CacheOut {
   const uint32_t* ent = nullptr;
   const uint8_t* states = nullptr;        // the batch's staged packed states
   int stride = 0, state_bytes = 0;
+  int legal_only = 0;                     // wide heads: softmax over the LEGAL actions of the staged state only (see heads_finish)
 };
 
 template <class G, bool FAST = false>
@@ -244,6 +245,57 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
     for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
       const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
       float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
+      if (FAST && G::NROWS > 1 && co.legal_only && zbuf) {
+        // The search only ever reads the policy at the LEGAL actions of the position it asked about (GetPriors:
+        // getPolicy(state) * LegalActions() / sum, Blackbird.py:386-387), and the engine holds that position: generate
+        // its legal moves here, evaluate the <= ~100 logits that matter instead of all 4032, soft-max over those, and
+        // store them at their action index (the other entries of the row are left alone).  The normaliser cancels in
+        // GetPriors' division, so the priors are the reference's up to fp32 rounding of two different partial sums --
+        // well inside the bf16 kernel's tolerance; the fp32 kernel keeps the dense head.  4032 x 3 passes and a 16 KB
+        // row write per position become one pass over the legal list (DragonChess: 96 k -> ~10 k cycles of heads per batch).
+        typename G::State st;
+        memcpy(&st, co.states + p * co.stride, sizeof(st));
+        int* list = reinterpret_cast<int*>(zbuf);                       // [0, CAP) action ids, then CAP logits, then scan scratch
+        constexpr int CAP = 512;
+        float* zl = zbuf + CAP;
+        int* scan = reinterpret_cast<int*>(zbuf + 2 * CAP);             // [NROWS + 1]
+        uint64_t m = 0;
+        if (tid < G::NROWS) { m = G::legal_row(st, tid); scan[tid + 1] = popc64(m); }
+        if (tid == 0) scan[0] = 0;
+        tm.sync();
+        if (tid == 0) for (int r = 0; r < G::NROWS; ++r) scan[r + 1] += scan[r];
+        tm.sync();
+        const int k = min(scan[G::NROWS], CAP);
+        if (tid < G::NROWS) {
+          int j = scan[tid];
+          while (m && j < CAP) { const int bit = ctz64(m); m &= m - 1; list[j++] = G::action_of(tid, bit); }
+        }
+        tm.sync();
+        float mx = -INFINITY;
+        for (int i = tid; i < k; i += nthreads) {
+          const int a = list[i];
+          const float z = fmaf(s0, __ldg(pol_w + a), fmaf(s1, __ldg(pol_w + G::A + a), (float)HW * __ldg(pol_b + a)));
+          zl[i] = z;
+          mx = fmaxf(mx, z);
+        }
+        mx = block_reduce(mx, red, true, tm);
+        float sum = 0.f;
+        for (int i = tid; i < k; i += nthreads) { const float e = __expf(zl[i] - mx); zl[i] = e; sum += e; }
+        sum = block_reduce(sum, red, false, tm);
+        if (np.eps > 0.f) {                                             // (1 - eps) softmax + eps noise, renormalised -- over the legal actions
+          float tot = 0.f;
+          for (int i = tid; i < k; i += nthreads) {
+            const float pa = (1.f - np.eps) * (zl[i] / sum) + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (nb + p) * G::A + list[i]);
+            zl[i] = pa;
+            tot += pa;
+          }
+          sum = block_reduce(tot, red, false, tm);
+        }
+        const float inv = 1.f / sum;
+        for (int i = tid; i < k; i += nthreads) out[list[i]] = zl[i] * inv;
+        tm.sync();                                                      // list / zl are rewritten by the next position
+        continue;
+      }
       // intermediate values live in shared memory when the caller has room for A floats (every thread touches
       // only its own actions, so no barrier beyond the reductions'); otherwise in the output row itself.
       // Same operations in the same order either way: the results are bit-identical.
@@ -428,7 +480,7 @@ static int net_launch(NetDev* net, const void* states, int n, const int* count_d
 }
 
 template <class G>
-static int net_launch_tc(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
+static int net_launch_tc(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream, int legal_only) {
   using Ge = TcGeom<G>;
   const TcSmem<G> L(net->tc.w_blocks, net->p.layers);
   static bool configured[3] = {false, false, false};
@@ -456,7 +508,9 @@ static int net_launch_tc(NetDev* net, const void* states, int n, const int* coun
   const int cap = net->sm_count * ctas_per_sm[G::ID];
   const int want = (n + Ge::PIPES - 1) / Ge::PIPES;             // every CTA runs PIPES batches side by side
   const int grid = want < cap ? want : cap;
-  k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value, NetServe{});
+  NetServe launch{};
+  launch.legal_only = legal_only;
+  k_net_forward_tc<G><<<grid, Ge::THREADS, L.total, stream>>>(net->p, net->tc, (const typename G::State*)states, n, count_dev, policy, value, launch);
   BB_CUDA(cudaGetLastError());
   if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
   return BB_OK;
@@ -504,9 +558,9 @@ int net_tc_footprint(NetDev* net, int* regs, int* smem) {
 int net_sm_count(NetDev* net) { return net->sm_count; }
 bool net_is_tc(NetDev* net) { return net->use_tc; }
 
-int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream) {
+int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream, int legal_only) {
   if (n <= 0) return BB_OK;
-  if (net->use_tc) { BB_DISPATCH_GAME(net->game, return net_launch_tc<G>(net, states, n, count_dev, policy, value, stream)); }
+  if (net->use_tc) { BB_DISPATCH_GAME(net->game, return net_launch_tc<G>(net, states, n, count_dev, policy, value, stream, legal_only)); }
   else { BB_DISPATCH_GAME(net->game, return net_launch<G>(net, states, n, count_dev, policy, value, stream)); }
   return BB_EINVAL;
 }

@@ -664,9 +664,9 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       const float* pw = G::A <= 32 ? sHead + nh : np.pol_w;
       const float* pb = G::A <= 32 ? sHead + nh + 2 * G::A : np.pol_b;
       CacheOut co;
-      if (G::A <= ECACHE_MAX_ACTIONS && serve && sv.ecache) {
-        co.base = sv.ecache; co.ent = sEnt; co.states = sState; co.stride = ST_STRIDE; co.state_bytes = (int)sizeof(State);
-      }
+      co.states = sState; co.stride = ST_STRIDE; co.state_bytes = (int)sizeof(State);
+      co.legal_only = sv.legal_only;
+      if (G::A <= ECACHE_MAX_ACTIONS && serve && sv.ecache) { co.base = sv.ecache; co.ent = sEnt; }
       heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
                       reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll, co);
     }

@@ -387,7 +387,7 @@ struct EngineT : bb_engine {
       host_launches++;
     } else if (cfg.evaluator == BB_EVAL_NET) {
       if (!net) { set_error("evaluator is BB_EVAL_NET but no network is loaded"); return BB_ESTATE; }
-      int rc = net_forward(net, L.d.req_state, L.d.n_games, count, L.d.resp_policy, L.d.resp_value, L.stream);
+      int rc = net_forward(net, L.d.req_state, L.d.n_games, count, L.d.resp_policy, L.d.resp_value, L.stream, 1);   // the search reads legal entries only
       if (rc) return rc;
       host_launches++;
     }
@@ -535,7 +535,7 @@ struct EngineT : bb_engine {
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));
-    NetServe sv{q_dev, d.q_ent, d.q_state, d.resp_seq, d.q_mask, e.ecache, e.ecache_mask};
+    NetServe sv{q_dev, d.q_ent, d.q_state, d.resp_seq, d.q_mask, e.ecache, e.ecache_mask, 1};
     // the network kernel goes first so that its CTAs are resident before the search CTAs spin on it
     BB_CUDA(cudaEventRecord(st_ev[2], net_stream));
     if ((rc = net_serve(net, sv, d.resp_policy, d.resp_value, net_stream))) return rc;
