@@ -52,7 +52,7 @@ class Network(object):
         self._net_dirty = False
         self.lastLosses = None
         self.batchCount = 0
-        if self.loadModel(name):                                      # Network.py:21: a saved network wins
+        if self.loadModel(name, networkConstructor):                  # Network.py:21: a saved network wins
             return
         if networkConstructor is None:
             raise FileNotFoundError('no saved network %r and no networkConfig to build one' % name)
@@ -146,14 +146,35 @@ class Network(object):
         saveDir = os.path.join('blackbird_models', name)
         os.makedirs(saveDir, exist_ok=True)
         s = self._net_shape
+        # the reference's own format next to it: a TensorFlow checkpoint bundle (best.index + best.data-00000-of-00001) with the
+        # reference graph's variable names, which tf.compat.v1.train.Saver.restore reads (Network.py:86-112; tfbundle.py)
+        from . import tfbundle
+        cin = _engine.plane_shape(self._net_game)[2]
+        tfbundle.write_bundle(os.path.join(saveDir, 'best'),
+                              tfbundle.flat_to_tensors(self._net_loaded_weights, cin, s.policyShape, s.blocks, s.filters, s.dense))
         np.savez(os.path.join(saveDir, 'best.npz'), weights=self._net_loaded_weights,
                  shape=np.array([s.blocks, s.filters, s.dense, s.policyShape]), noise=np.array([s.epsilon, s.alpha]),
                  training=np.array([str(getattr(s, 'optimizer', 'sgd')), str(getattr(s, 'momentum', 0.9))]))
 
-    def loadModel(self, name):
+    def loadModel(self, name, networkConstructor=None):
         path = os.path.join('blackbird_models', name, 'best.npz')
         if not os.path.isfile(path):
-            return False
+            # a checkpoint saved by the reference (TensorFlow Saver bundle, Network.py:86-99): weights and shape come from the
+            # bundle, noise / optimizer settings from the caller's configuration (they live in the graph, not in the bundle)
+            prefix = os.path.join('blackbird_models', name, 'best')
+            if not os.path.isfile(prefix + '.index'):
+                return False
+            from . import tfbundle
+            from .NetworkFactory import NetworkFactory
+            flat, (cin, a, b, f, d) = tfbundle.tensors_to_flat(tfbundle.read_bundle(prefix))
+            if cin != _engine.plane_shape(self._net_game)[2]:
+                raise ValueError('checkpoint %s was trained on %d input planes, %s has %d' % (prefix, cin, self._net_game, _engine.plane_shape(self._net_game)[2]))
+            cfg = dict(getattr(networkConstructor, 'networkConfig', {}) or {})
+            cfg.update({'blocks': b, 'filters': f, 'eval': {'dense': d}})
+            cfg.setdefault('policy', {'dirichlet': {'epsilon': 0.0, 'alpha': 0.2}})
+            self._net_shape = NetworkFactory(cfg, a)
+            self.setWeights(flat)
+            return True
         from .NetworkFactory import NetworkFactory
         z = np.load(path)
         b, f, d, a = (int(x) for x in z['shape'])

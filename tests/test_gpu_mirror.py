@@ -340,3 +340,28 @@ def test_good_opponent_wall_clock(bb):
     nxt, v, probs = good.FindMove(s, 0.1)
     assert good.Root.Plays >= 8 and abs(probs.sum() - 1) < 1e-12 and 0 <= float(v) <= 1
     assert float(good.SampleValue(s, 1)) in (0.0, 0.5, 1.0)
+
+
+def test_checkpoint_bundle_interop(bb, tmp_path, monkeypatch):
+    """Network.saveModel writes a TensorFlow Saver bundle (best.index / best.data-00000-of-00001, the reference graph's
+    variable names) next to its own file; a model directory that holds ONLY such a bundle -- what the reference saves,
+    minus the TensorFlow graph file -- loads with identical weights and evaluates identically."""
+    from blackbird_b200 import tfbundle
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    cfg = {'maxDepth': 10, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': 10}
+    net = {'blocks': 4, 'filters': 16, 'eval': {'dense': 16}, 'policy': {'dirichlet': {'epsilon': 0.0, 'alpha': 0.2}}}
+    m = B.Model(bb['games']['Connect4'], 'Ckpt', cfg, net, {})
+    d = os.path.join('blackbird_models', 'Ckpt_1')
+    assert sorted(os.listdir(d)) == ['best.data-00000-of-00001', 'best.index', 'best.npz']
+    tensors = tfbundle.read_bundle(os.path.join(d, 'best'))
+    assert tensors['resTower/block_3/conv_2/kernel'].shape == (3, 3, 16, 16) and tensors['policy/policy/bias'].shape == (7,)
+    s = m.Game()
+    p0, v0 = m.getPolicy(s.AsInputArray()), m.getEvaluation(s.AsInputArray())
+    w0 = m.getWeights().copy()
+    m.Conn.Close()
+    os.remove(os.path.join(d, 'best.npz'))                             # only the TensorFlow bundle is left
+    m2 = B.Model(bb['games']['Connect4'], 'Ckpt', cfg, net, {})
+    assert np.array_equal(m2.getWeights(), w0)
+    assert np.array_equal(m2.getPolicy(s.AsInputArray()), p0) and m2.getEvaluation(s.AsInputArray()) == v0
+    m2.Conn.Close()
