@@ -96,6 +96,8 @@ SIGNATURES = {
     'bb_trainer_set_weights': (I, [VP, VP, C.c_size_t]),
     'bb_trainer_grads': (I, [VP, VP, C.c_size_t]),
     'bb_trainer_steps': (C.c_uint64, [VP]),
+    'bb_records_serialize_static': (I, [VP, VP, C.c_uint64, VP, VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    'bb_records_static_max_rows': (I, []),
     'bb_counters_read': (I, [VP, C.POINTER(bb_counters), I]),
     'bb_engine_lanes': (I, [VP]),
     'bb_engine_streaming': (I, [VP]),

@@ -84,6 +84,68 @@ __global__ void k_probe_wait(volatile unsigned* flag, unsigned* seen) {
 }
 __global__ void k_probe_set(volatile unsigned* flag) { *flag = 1u; }
 
+// ---- allocation-free record serialization (bb_records_serialize_static) ---------------------------------------------------
+// The per-game byte offsets that k_pack_records reads are scratch memory: bb_records_serialize builds them on the host and
+// keeps them in a cudaMalloc'ed buffer.  This variant keeps them in a file-scope device array instead, so the call
+// allocates nothing.  Every GPU that loads the library holds the array (512 KB) until the process exits; every call on
+// a device shares it, so two calls that overlap on the GPU race.  Nothing in it has to start at zero: the offsets kernel
+// rewrites every word a call reads (offsets [0, rows], then the totals) before the pack kernel runs.
+constexpr int REC_STATIC_MAX_ROWS = 65536;                     // games (record rows) per call
+static __device__ __align__(256) unsigned long long g_rec_static[REC_STATIC_MAX_ROWS + 8];   // [rows + 1] offsets | [MAX + 1] records | [MAX + 2] bytes
+
+// one CTA: exclusive scan of the games' byte sizes -> scratch (and the caller's game_off / rec_bytes, when given)
+template <class G>
+__global__ void __launch_bounds__(1024) k_record_offsets(EngineDev<G> E, int rows, unsigned long long* __restrict__ scratch,
+                                                          unsigned long long* __restrict__ game_off_out, uint32_t* __restrict__ rec_bytes_out) {
+  using F = RecFmt<G>;
+  __shared__ unsigned long long s_part[1024], s_recs[1024];
+  const int tid = threadIdx.x, per = (rows + 1023) / 1024;
+  const int lo = min(rows, tid * per), hi = min(rows, lo + per);
+  unsigned long long bytes = 0, recs = 0;
+  for (int g = lo; g < hi; ++g) {
+    const int w = E.winners[g];
+    const unsigned sz = (unsigned)F::SIZE0 + ((w == WIN_P1 || w == WIN_P2) ? 5u : 0u);
+    bytes += (unsigned long long)(E.n_moves[g] + 1) * sz;
+    recs += (unsigned long long)(E.n_moves[g] + 1);
+  }
+  s_part[tid] = bytes;
+  s_recs[tid] = recs;
+  __syncthreads();
+  if (tid == 0) {                                               // 1024 partial sums: a serial pass is a few microseconds
+    unsigned long long run = 0, nrec = 0;
+    for (int i = 0; i < 1024; ++i) { const unsigned long long b = s_part[i]; s_part[i] = run; run += b; nrec += s_recs[i]; }
+    scratch[rows] = run;
+    scratch[REC_STATIC_MAX_ROWS + 1] = nrec;
+    scratch[REC_STATIC_MAX_ROWS + 2] = run;
+    if (game_off_out) game_off_out[rows] = run;
+  }
+  __syncthreads();
+  unsigned long long off = s_part[tid];
+  for (int g = lo; g < hi; ++g) {
+    const int w = E.winners[g];
+    const unsigned sz = (unsigned)F::SIZE0 + ((w == WIN_P1 || w == WIN_P2) ? 5u : 0u);
+    scratch[g] = off;
+    if (game_off_out) game_off_out[g] = off;
+    if (rec_bytes_out) rec_bytes_out[g] = sz;
+    off += (unsigned long long)(E.n_moves[g] + 1) * sz;
+  }
+}
+
+// device address of g_rec_static on `device` (which must be current): resolved once per device.  In host code the array's
+// name is only a stand-in for the symbol, not an address a kernel can use.
+static int rec_static_ptr(int device, unsigned long long** out) {
+  static unsigned long long* ptrs[64] = {nullptr};
+  if (device < 0 || device >= 64) { set_error("bb_records_serialize_static: device %d out of range", device); return BB_EINVAL; }
+  if (!ptrs[device]) {
+    unsigned long long* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_rec_static);
+    if (e != cudaSuccess || !p) { set_error("cudaGetSymbolAddress(g_rec_static) failed on device %d: %s", device, cudaGetErrorString(e)); return BB_ECUDA; }
+    ptrs[device] = p;
+  }
+  *out = ptrs[device];
+  return BB_OK;
+}
+
 }  // namespace bb
 
 using namespace bb;
@@ -122,6 +184,7 @@ struct bb_engine {
   virtual int stream_stats(uint64_t*) = 0;
   virtual int stream_answers(void*, float*, float*, uint32_t*) = 0;
   virtual int records_serialize(void*, uint64_t, uint64_t*, uint64_t*, uint64_t*, uint32_t*) = 0;
+  virtual int records_serialize_static(void*, uint64_t, uint64_t*, uint32_t*, uint64_t*, uint64_t*) = 0;
   virtual int set_rng(const uint32_t*, uint32_t) = 0;
   virtual int rng_used(uint32_t*) = 0;
 };
@@ -888,6 +951,34 @@ struct EngineT : bb_engine {
     host_launches++;
     return BB_OK;
   }
+  // the same serialization without any allocation: offsets in the file-scope device array g_rec_static (see there)
+  int records_serialize_static(void* out_dev, uint64_t cap, uint64_t* game_off_dev, uint32_t* rec_bytes_dev, uint64_t* n_records, uint64_t* n_bytes) override {
+    if (!out_dev) { set_error("bb_records_serialize_static: null output buffer"); return BB_EINVAL; }
+    const size_t rows = rows_last;
+    if (rows > (size_t)REC_STATIC_MAX_ROWS) {
+      set_error("bb_records_serialize_static: %zu game rows, the static scratch array holds at most %d (use bb_records_serialize)", rows, REC_STATIC_MAX_ROWS);
+      return BB_EINVAL;
+    }
+    BB_CUDA(cudaSetDevice(cfg.device));
+    unsigned long long* scratch_static = nullptr;
+    int rc = rec_static_ptr(cfg.device, &scratch_static);
+    if (rc) return rc;
+    if ((rc = sync_lanes())) return rc;
+    k_record_offsets<G><<<1, 1024, 0, stream>>>(d, (int)rows, scratch_static, (unsigned long long*)game_off_dev, rec_bytes_dev);
+    BB_CUDA(cudaGetLastError());
+    unsigned long long totals[2] = {0, 0};                      // records, bytes
+    BB_CUDA(cudaMemcpyAsync(totals, scratch_static + REC_STATIC_MAX_ROWS + 1, sizeof totals, cudaMemcpyDeviceToHost, stream));
+    BB_CUDA(cudaStreamSynchronize(stream));
+    if (n_records) *n_records = totals[0];
+    if (n_bytes) *n_bytes = totals[1];
+    if (cap < totals[1]) { set_error("bb_records_serialize_static: buffer of %llu bytes, %llu needed", (unsigned long long)cap, totals[1]); return BB_EINVAL; }
+    if (rows == 0) return BB_OK;
+    k_pack_records<G><<<(unsigned)rows, 128, pack_records_smem<G>(), stream>>>(d, (int)rows, scratch_static, (uint8_t*)out_dev);
+    BB_CUDA(cudaGetLastError());
+    BB_CUDA(cudaStreamSynchronize(stream));
+    host_launches += 2;
+    return BB_OK;
+  }
   int counters(bb_counters* out, int do_reset) override {
     std::vector<Counters> c(lanes.size());
     int rc = sync_lanes();
@@ -1011,6 +1102,11 @@ int bb_records_serialize(bb_engine* e, void* out_dev, uint64_t cap, uint64_t* n_
   BB_NEED(e);
   return e->records_serialize(out_dev, cap, n_records, n_bytes, game_off_host, rec_bytes_host);
 }
+int bb_records_serialize_static(bb_engine* e, void* out_dev, uint64_t cap, uint64_t* game_off_dev, uint32_t* rec_bytes_dev, uint64_t* n_records, uint64_t* n_bytes) {
+  BB_NEED(e);
+  return e->records_serialize_static(out_dev, cap, game_off_dev, rec_bytes_dev, n_records, n_bytes);
+}
+int bb_records_static_max_rows(void) { return REC_STATIC_MAX_ROWS; }
 int bb_counters_read(bb_engine* e, bb_counters* out, int reset) { BB_NEED(e); return e->counters(out, reset); }
 int bb_engine_lanes(bb_engine* e) { BB_NEED(e); return e->n_lanes(); }
 int bb_engine_streaming(bb_engine* e) { BB_NEED(e); return e->streaming(); }

@@ -202,6 +202,21 @@ int bb_records_device(bb_engine* e, void** n_moves_dev, void** winner_dev, void*
 int bb_records_serialize(bb_engine* e, void* out_dev, uint64_t cap_bytes, uint64_t* n_records, uint64_t* n_bytes,
                          uint64_t* game_off_host, uint32_t* rec_bytes_host);
 
+/* bb_records_serialize for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * It produces the same byte stream, but the per-game offsets its pack kernel reads live in a file-scope
+ * `static __device__` array (512 KB, held by every GPU that loads the library until the process exits) instead of a
+ * cudaMalloc'ed buffer, and are computed on the device: the call makes no cudaMalloc / cudaFree and uses no allocating
+ * library routine.  Limits: at most bb_records_static_max_rows() = 65536 games per call (more -> BB_EINVAL, use
+ * bb_records_serialize); cap_bytes below the stream's size -> BB_EINVAL with *n_bytes set to what is needed.  The
+ * caller passes every buffer: out_dev (device, cap_bytes), game_off_dev (device, uint64 [rows + 1], may be NULL),
+ * rec_bytes_dev (device, uint32 [rows], may be NULL); n_records / n_bytes are host outputs (may be NULL).  All calls on
+ * one GPU share the array, and it keeps the last call's contents: a call rewrites every word it reads, so nothing needs
+ * clearing, but two calls that OVERLAP on the GPU (two engines on one device driven from two threads) race. */
+int bb_records_serialize_static(bb_engine* e, void* out_dev, uint64_t cap_bytes, uint64_t* game_off_dev, uint32_t* rec_bytes_dev,
+                                uint64_t* n_records, uint64_t* n_bytes);
+int bb_records_static_max_rows(void);
+
 /* ---- trainer step: Network.train (Network.py:66-84) over the loss / optimizers of
  *      NetworkFactory.py:185-245, on the GPU ------------------------------------------------------------ */
 typedef struct bb_trainer bb_trainer;
