@@ -112,3 +112,46 @@ def test_selfplay_sharded_rows_slots_and_uniforms_with_a_stub_engine():
         assert (play_limit, temp, n_rows) == (24, 1.0, 10) and u.shape == (10, 42)
         assert np.array_equal(u, game_uniforms(range(10), 42, 1000))
         assert len(raw['n_moves']) == 10
+
+
+def _worker_streams(rank, world, port, q):
+    try:
+        import torch
+        import torch.distributed as dist
+        sys.path.insert(0, ROOT)
+        from blackbird_b200.parallel import allgather_serialized
+        os.environ['MASTER_ADDR'] = '127.0.0.1'
+        os.environ['MASTER_PORT'] = str(port)
+        dist.init_process_group('gloo', rank=rank, world_size=world)
+        mine = lambda r: np.random.RandomState(5 + r).randint(0, 256, 1000 + 613 * r).astype(np.uint8)   # ragged: every rank another length
+        gathered, lens = allgather_serialized(torch.as_tensor(mine(rank)))
+        assert lens.tolist() == [1000 + 613 * r for r in range(world)]
+        assert gathered.shape[0] == world and gathered.shape[1] % 16 == 0 and gathered.shape[1] >= lens.max()
+        for r in range(world):
+            assert np.array_equal(gathered[r, :lens[r]].numpy(), mine(r)), r
+            assert not gathered[r, lens[r]:].any()
+        empty, lens0 = allgather_serialized(torch.empty((0,), dtype=torch.uint8) if rank else torch.as_tensor(mine(0)))
+        assert lens0.tolist() == [1000] + [0] * (world - 1)
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, 'ok'))
+    except Exception as e:       # noqa: BLE001
+        q.put((rank, 'FAIL %r' % (e,)))
+
+
+def test_allgather_of_compact_record_streams_gloo_world2():
+    """parallel.allgather_serialized: byte counts first, then the ragged streams padded to the longest."""
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_streams, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(30)
+    assert res == [(0, 'ok'), (1, 'ok')], res
