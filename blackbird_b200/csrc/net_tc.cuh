@@ -53,8 +53,11 @@ template <class G> struct TcBatch;
 #define BB_TC_PIPES 2
 #endif
 // TILES = 128-row tiles of one pipeline's batch; NP = PPT * TILES positions
-template <> struct TcBatch<TicTacToe> { static constexpr int TILES = BB_TC_PIPES == 3 ? 4 : 7, PIPES = BB_TC_PIPES; };   // 8 positions of 16 rows per tile: 56
-template <> struct TcBatch<Connect4> { static constexpr int TILES = BB_TC_PIPES == 3 ? 4 : 7, PIPES = BB_TC_PIPES; };    // 2 positions of 56 rows per tile: 14
+#ifndef BB_TC_TILES
+#define BB_TC_TILES 4                            // streaming batches hold 3 - 5 positions; four tiles leave room for the heads warp's double buffers
+#endif
+template <> struct TcBatch<TicTacToe> { static constexpr int TILES = BB_TC_TILES, PIPES = BB_TC_PIPES; };   // 8 positions of 16 rows per tile: 32
+template <> struct TcBatch<Connect4> { static constexpr int TILES = BB_TC_TILES, PIPES = BB_TC_PIPES; };    // 2 positions of 56 rows per tile: 8
 template <> struct TcBatch<DragonChess> { static constexpr int TILES = 3, PIPES = 2; };                                  // 1 position of 81 rows per tile: 3 (+ a 4032-float policy scratch row per pipeline)
 
 template <class G>
@@ -84,7 +87,15 @@ struct TcGeom {
 #endif
   static constexpr int EPI_GROUPS = BB_TC_EPI_GROUPS;
   static constexpr int EPI_THREADS = EPI_GROUPS * 128;      // epilogue threads of one pipeline
-  static constexpr int PIPE_THREADS = EPI_THREADS + 32;     // + its MMA-issuing warp
+  static constexpr int TEAM_THREADS = EPI_THREADS + 32;     // + its MMA-issuing warp: the threads that meet at the pipeline's named barrier
+  // Narrow heads (A <= 32) get a warp of their own per pipeline: it turns the last layer's head maps into value / policy,
+  // writes the answers and publishes them WHILE the epilogue and MMA warps already run the next batch's tower (double-
+  // buffered hand-off through two mbarrier pairs).  Heads + publish were 20 - 26 % of a batch's time with the MMA warp idle.
+#ifndef BB_TC_HEADS_WARP
+#define BB_TC_HEADS_WARP 0            // measured: 65.5 M vs 70.4 M sims/s -- the lone warp takes 13 k cycles per batch, and answer LATENCY, not pipeline occupancy, is what the slots wait for
+#endif
+  static constexpr bool HEADS_WARP = BB_TC_HEADS_WARP && G::A <= 32;
+  static constexpr int PIPE_THREADS = TEAM_THREADS + (HEADS_WARP ? 32 : 0);
   static constexpr int THREADS = PIPES * PIPE_THREADS;
   static constexpr int TMEM_PIPE_COLS = TILES * 16;         // one 16-column accumulator per tile
   static constexpr int TMEM_COLS = PIPES * TMEM_PIPE_COLS <= 32 ? 32 : PIPES * TMEM_PIPE_COLS <= 64 ? 64 : PIPES * TMEM_PIPE_COLS <= 128 ? 128
@@ -243,6 +254,7 @@ struct TcSmem {                                  // byte offsets into dynamic sh
   using Ge = TcGeom<G>;
   int w, bias, head, wbar, tmem, pipe0, pipe_stride, total;          // shared by both pipelines, then one block per pipeline
   int x, y, in, hsum, red, idx, st, zb, ent, claim, mbar;            // offsets inside a pipeline's block
+  int hmap, info, hbar, idx_stride, st_stride2, ent_stride;          // heads warp: double-buffered head maps / batch info / mbarriers; strides of the doubled buffers
   __host__ __device__ TcSmem(int w_blocks, int layers) {
     int o = 0;
     w = o; o += w_blocks * 512;
@@ -259,18 +271,111 @@ struct TcSmem {                                  // byte offsets into dynamic sh
     if (Ge::KB_IN == 1) in = y; else { in = q; q += Ge::KB_IN * Ge::BUF; }
     hsum = q; q += Ge::NP * 4 * 4;
     red = q; q += 32 * 4;
-    idx = q; q += Ge::NP * 4;                      // streaming mode: slot id of every position of the batch
+    constexpr int NB = Ge::HEADS_WARP ? 2 : 1;     // buffers the heads warp reads are doubled: it works on batch i while batch i + 1 is staged
+    idx_stride = Ge::NP * 4;
+    idx = q; q += NB * idx_stride;                 // streaming mode: slot id of every position of the batch
     q = (q + 15) & ~15;
-    st = q; q += Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);   // the batch's packed states, staged once
+    st_stride2 = Ge::NP * (int)((sizeof(typename G::State) + 15) & ~15u);
+    st = q; q += NB * st_stride2;                  // the batch's packed states, staged once
     zb = q; q += (G::A > 32 ? G::A : Ge::NP * G::A) * 4;   // wide policy heads: one row of logits / probabilities; narrow ones: the batch's noise draws (heads_finish)
-    ent = q; q += 2 * Ge::NP * 4;                  // streaming mode: evaluation-cache entry (+1) this pipeline locked per position, and its tag
+    ent_stride = 2 * Ge::NP * 4;
+    ent = q; q += NB * ent_stride;                 // streaming mode: evaluation-cache entry (+1) this pipeline locked per position, and its tag
     claim = q; q += 2 * 4;                         // streaming mode: first ticket and size of the claimed batch
     q = (q + 7) & ~7;
     mbar = q; q += 2 * Ge::TILES * 8;              // full[TILES], ready[TILES]
+    hbar = q; q += 4 * 8;                          // hfull[2] (epilogue -> heads warp), hfree[2] (heads warp -> epilogue)
+    info = q; q += 2 * 4 * 4;                      // per buffer: positions of the batch (0 = leave), first ticket / base
+    q = (q + 15) & ~15;
+    hmap = q; if (Ge::HEADS_WARP) q += 2 * Ge::TILES * 128 * 16;   // per raster row (value, policy0, policy1) of the last layer's 1x1 head convolutions
     pipe_stride = (q + 127) & ~127;
     total = pipe0 + Ge::PIPES * pipe_stride;
   }
 };
+
+// The heads warp's work on one batch (narrow heads): GP lanes per position (8 up to 8 actions, 16 up to 16, else 32), 32 / GP
+// positions per pass.  Lane j of a group sums cells j, j + GP, ... of the three head maps, the group combines them with a
+// fixed-order xor tree, then the value head (dense units j, j + GP, ...) and the policy head (action j: logit, soft-max, its own
+// noise draw, renormalisation) as in heads_finish.  In serve mode every pass ends with the release fence and the groups'
+// publications (answer sequence number, evaluation-cache tag).
+template <class G>
+__device__ void heads_warp_batch(const NetParams& np, const float* sHead, const uint8_t* hmap, int cnt, bool serve, unsigned first, unsigned long long call,
+                                 float* __restrict__ policy, float* __restrict__ value, const int* sIdx, const uint32_t* sEnt, const uint8_t* sState,
+                                 int st_stride, const NetServe& sv) {
+  using Ge = TcGeom<G>;
+  constexpr int A = G::A, HW = G::H * G::W, GP = A <= 8 ? 8 : A <= 16 ? 16 : 32, PPW = 32 / GP, NPm = Ge::NP;
+  const int lane = threadIdx.x & 31, g = lane / GP, j = lane % GP;
+  const int D = np.dense, nh = 51 + 3 * D + 1;
+  const float* d1w = sHead + 17 + 34;
+  const float* d1b = d1w + D;
+  const float* d2w = d1b + D;
+  const float d2b = d2w[D];
+  const float* pol_w = sHead + nh;
+  const float* pol_b = pol_w + 2 * A;
+  const bool cache = A <= ECACHE_MAX_ACTIONS && serve && sv.ecache != nullptr;
+  for (int p0 = 0; p0 < cnt; p0 += PPW) {
+    const int p = p0 + g;
+    const bool live = p < cnt;
+    const int pc = live ? p : p0;
+    float sv_ = 0.f, s0 = 0.f, s1 = 0.f;                    // sums over H,W of relu(bn(1x1 conv)): value map, two policy maps
+    for (int c = j; c < HW; c += GP) {
+      const float4 m = *reinterpret_cast<const float4*>(hmap + Ge::row_of(pc, c / G::W + 1, c % G::W) * 16);
+      sv_ += m.x; s0 += m.y; s1 += m.z;
+    }
+#pragma unroll
+    for (int o = GP / 2; o; o >>= 1) {
+      sv_ += __shfl_xor_sync(0xFFFFFFFFu, sv_, o, GP);
+      s0 += __shfl_xor_sync(0xFFFFFFFFu, s0, o, GP);
+      s1 += __shfl_xor_sync(0xFFFFFFFFu, s1, o, GP);
+    }
+    const size_t orow = serve ? (size_t)sIdx[pc] : (size_t)(first + (unsigned)pc);
+    uint32_t* cent = nullptr;
+    if (cache && live && sEnt[p]) cent = sv.ecache + (size_t)(sEnt[p] - 1u) * ECACHE_WORDS;
+    float part = 0.f;                                       // value: dense(1->D)+sum, ReLU, dense(D->1), tanh
+    for (int d = j; d < D; d += GP) part = fmaf(fmaxf(fmaf(sv_, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], part);
+#pragma unroll
+    for (int o = GP / 2; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o, GP);
+    if (live && j == 0) {
+      const float v = tanhf(part + d2b);
+      value[orow] = v;
+      if (cent) {
+        cent[13] = __float_as_uint(v);
+        const uint32_t* st = reinterpret_cast<const uint32_t*>(sState + p * st_stride);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cent[i] = i * 4 < (int)sizeof(typename G::State) ? st[i] : 0u;
+      }
+    }
+    const bool act = j < A;                                 // policy: dense(2->A)+sum, softmax, noise mix, renormalise
+    const int a = act ? j : 0;
+    const float z = act ? fmaf(s0, pol_w[a], fmaf(s1, pol_w[A + a], (float)HW * pol_b[a])) : -INFINITY;
+    float m = z;
+#pragma unroll
+    for (int o = GP / 2; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o, GP));
+    const float e = act ? expf(z - m) : 0.f;
+    float sum = e;
+#pragma unroll
+    for (int o = GP / 2; o; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o, GP);
+    float pa = e / sum;
+    if (np.eps > 0.f && act && live)
+      pa = (1.f - np.eps) * pa + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), ((unsigned long long)first + (unsigned)p) * A + a);
+    float tot = pa;
+#pragma unroll
+    for (int o = GP / 2; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o, GP);
+    if (live && act) {
+      const float pf = pa / tot;
+      policy[orow * A + a] = pf;
+      if (cent) cent[4 + a] = __float_as_uint(pf);
+    }
+    if (serve) {                                            // publish this pass: answers first, then sequence numbers and cache tags
+      fence_acq_rel();
+      __syncwarp();
+      if (live && j == 0) {
+        fence_acq_rel();
+        *reinterpret_cast<volatile unsigned*>(&sv.resp_seq[orow]) = first + (unsigned)p + 1u;
+        if (cent) *reinterpret_cast<volatile uint32_t*>(cent + 14) = sEnt[NPm + p];
+      }
+    }
+  }
+}
 
 template <class G>
 __global__ void __launch_bounds__(576, 2)   // <= 56 registers whatever the thread count: the CTA shares its SM's register file with a search CTA
@@ -294,7 +399,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   const int tid = tid_cta - pipe * Ge::PIPE_THREADS;        // thread index inside the pipeline
   const int pwarp = tid >> 5;                               // warp index inside the pipeline: 0..7 epilogue, 8 MMA issuer
   const bool is_mma = pwarp == 4 * Ge::EPI_GROUPS;
-  const Team team{tid, Ge::PIPE_THREADS, 1 + pipe};         // named barrier 1 + pipeline: the pipelines never wait for each other
+  const bool is_heads = Ge::HEADS_WARP && pwarp == 4 * Ge::EPI_GROUPS + 1;   // never joins the team's barrier
+  const Team team{tid, Ge::TEAM_THREADS, 1 + pipe};         // named barrier 1 + pipeline: the pipelines never wait for each other
   uint8_t* sW = tc_smem + L.w;
   float* sBias = reinterpret_cast<float*>(tc_smem + L.bias);
   float* sHead = reinterpret_cast<float*>(tc_smem + L.head);
@@ -307,11 +413,15 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   uint8_t* bufIn = pb + L.in;
   float* hsum = reinterpret_cast<float*>(pb + L.hsum);
   float* red = reinterpret_cast<float*>(pb + L.red);
-  int* sIdx = reinterpret_cast<int*>(pb + L.idx);
+  int* sIdx = reinterpret_cast<int*>(pb + L.idx);                     // (buffer 0; the heads-warp build switches per batch)
   constexpr int ST_STRIDE = (int)((sizeof(State) + 15) & ~15u);
   uint8_t* sState = pb + L.st;
   volatile unsigned* sClaim = reinterpret_cast<volatile unsigned*>(pb + L.claim);
   uint32_t* sEnt = reinterpret_cast<uint32_t*>(pb + L.ent);          // [NP] entry + 1 (0: not ours), then [NP] tags
+  uint64_t* hfull = reinterpret_cast<uint64_t*>(pb + L.hbar);         // [2] epilogue warps -> heads warp: head maps of buffer b written
+  uint64_t* hfree = hfull + 2;                                        // [2] heads warp -> epilogue warps: buffer b may be rewritten
+  volatile unsigned* sInfo = reinterpret_cast<volatile unsigned*>(pb + L.info);   // [2][4]: positions of the batch (0 = leave), first ticket / base
+  uint8_t* hmap = pb + L.hmap;
   uint64_t* full = reinterpret_cast<uint64_t*>(pb + L.mbar);          // MMA -> epilogue, per tile
   uint64_t* ready = full + TILES;                                     // epilogue -> MMA, per tile (4 warp arrivals)
   const int layers = np.layers;
@@ -320,13 +430,14 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   if (is_mma) {
     if (lane == 0) {
       for (int t = 0; t < TILES; ++t) { mbar_init(&full[t], 1); mbar_init(&ready[t], 4); }
+      if (Ge::HEADS_WARP) for (int b = 0; b < 2; ++b) { mbar_init(&hfull[b], 4 * Ge::EPI_GROUPS); mbar_init(&hfree[b], 1); }
       if (pipe == 0) mbar_init(wbar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       if (pipe == 0) bulk_g2s(sW, tp.w, (uint32_t)tp.w_blocks * 512u, wbar);
     }
     __syncwarp();
     if (pipe == 0) tmem_alloc(tmem_slot, Ge::TMEM_COLS);
-  } else {
+  } else if (!is_heads) {
     if (pipe == 0) {
       for (int i = tid; i < layers * 16; i += Ge::EPI_THREADS) sBias[i] = np.tower_b[i];
       const int nh = 51 + 3 * np.dense + 1;                 // value conv, policy conv, d1 w/b, d2 w/b
@@ -354,8 +465,34 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
   unsigned pend_lo = 0, pend_n = 0;                         // serve mode, thread 0 of the pipeline: tickets claimed but not yet served
 
   int batch = (int)blockIdx.x * Ge::PIPES + pipe;
-  for (;;) {
+  if (is_heads) {
+    // ---- heads warp: batch k of this pipeline arrives in buffer k & 1 ------------------------------------------
+    if (lane == 0) { mbar_arrive(&hfree[0]); mbar_arrive(&hfree[1]); }      // both buffers start free
+    for (unsigned k = 0;; ++k) {
+      const unsigned b = k & 1u;
+      mbar_wait(&hfull[b], (k >> 1) & 1u);
+      const int hcnt = (int)sInfo[b * 4];
+      if (hcnt == 0) break;                                   // the pipeline has run out of work
+      const long long th0 = clock64();
+      heads_warp_batch<G>(np, sHead, hmap + b * (TILES * 128 * 16), hcnt, serve, sInfo[b * 4 + 1], call, policy, value,
+                          reinterpret_cast<const int*>(pb + L.idx + b * L.idx_stride), reinterpret_cast<const uint32_t*>(pb + L.ent + b * L.ent_stride),
+                          pb + L.st + b * L.st_stride2, ST_STRIDE, sv);
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&hfree[b]);
+        if (serve) atomicAdd(&sv.q->cyc_heads, (unsigned long long)(clock64() - th0));
+      }
+    }
+  } else {
+  unsigned bno = 0;                                           // batches this pipeline has started (heads-warp build: buffer = bno & 1)
+  for (;; ++bno) {
     int base, cnt;
+    if (Ge::HEADS_WARP) {                                     // this batch's copies of the buffers the heads warp reads
+      const unsigned b = bno & 1u;
+      sIdx = reinterpret_cast<int*>(pb + L.idx + b * L.idx_stride);
+      sState = pb + L.st + b * L.st_stride2;
+      sEnt = reinterpret_cast<uint32_t*>(pb + L.ent + b * L.ent_stride);
+    }
     unsigned ticket0 = 0;
     long long tm0 = 0, tm1 = 0, tm2 = 0;
     if (serve && tid == 0) tm0 = clock64();
@@ -415,14 +552,24 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       ticket0 = sClaim[0];
       cnt = (int)sClaim[1];
       base = 0;
-      if (cnt == 0) break;
       if (tid == 0) tm1 = clock64();
     } else {
-      if (batch >= n_batches) break;
-      base = batch * ppc;
-      cnt = min(ppc, n - base);                             // positions of this batch
+      base = batch < n_batches ? batch * ppc : 0;
+      cnt = batch < n_batches ? min(ppc, n - base) : 0;     // positions of this batch
       batch += n_pipes;
     }
+    if (Ge::HEADS_WARP && !is_mma) {
+      // buffer b is free once the heads warp has finished the batch before last; then hand it this batch's size and
+      // first ticket (or, with no work left, the word to leave)
+      const unsigned b = bno & 1u;
+      mbar_wait(&hfree[b], (bno >> 1) & 1u);
+      if (tid == 0) { sInfo[b * 4] = (unsigned)cnt; sInfo[b * 4 + 1] = serve ? ticket0 : (unsigned)base; }
+      if (cnt == 0) {
+        epi_bar_sync<Ge::EPI_THREADS>(pipe);
+        if (lane == 0) mbar_arrive(&hfull[b]);
+      }
+    }
+    if (cnt == 0) break;
     const int tiles = (cnt + Ge::PPT - 1) / Ge::PPT;        // 128-row tiles in use
     if (is_mma) {
       // ---- MMA issuer: layers x tiles as a wavefront ---------------------------------------------
@@ -610,7 +757,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
                 p0 = fmaf(acc[c], sHead[17 + c * 2], p0);
                 p1 = fmaf(acc[c], sHead[17 + c * 2 + 1], p1);
               }
-              *reinterpret_cast<float4*>(slot) = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
+              float4* hdst = Ge::HEADS_WARP ? reinterpret_cast<float4*>(hmap + (bno & 1u) * (TILES * 128 * 16) + row * 16) : reinterpret_cast<float4*>(slot);
+              *hdst = make_float4(fmaxf(v, 0.f), fmaxf(p0, 0.f), fmaxf(p1, 0.f), 0.f);
             }
           }
 #ifdef BB_NET_TIMING_TOWER
@@ -638,7 +786,20 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       (void)ne_stage;
 #endif
     }
-    // ---- heads: the whole pipeline (MMA warp included) meets here once per batch -----------------------
+    if constexpr (Ge::HEADS_WARP) {
+      // ---- narrow heads: hand the batch's head maps to the heads warp and go on with the next batch ------------
+      if (!is_mma) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&hfull[bno & 1u]);       // this warp's rows of the last layer are in hmap
+      }
+      if (serve && tid == 0) {
+        tm2 = clock64();
+        atomicAdd(&sv.q->batches, 1ull);
+        atomicAdd(&sv.q->cyc_claim, (unsigned long long)(tm1 - tm0));
+        atomicAdd(&sv.q->cyc_tower, (unsigned long long)(tm2 - tm1));
+      }
+    } else {
+    // ---- wide heads: the whole pipeline (MMA warp included) meets here once per batch ------------------
     team.sync();
     if (serve && tid == 0) tm2 = clock64();
     // per-position sums over H,W of the three head maps: one warp per (position, map), fixed-order tree
@@ -707,6 +868,8 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       atomicAdd(&sv.q->cyc_tower, (unsigned long long)(tm2 - tm1));
       atomicAdd(&sv.q->cyc_heads, (unsigned long long)(tm3 - tm2));
     }
+    }
+  }
   }
   tc_fence_before();
   __syncthreads();
