@@ -108,7 +108,7 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
     written = 0
     try:
         if evaluator == 'net':
-            model._load_network_into(eng, precision=precision, seed=random.getrandbits(48))
+            model._load_network_into(eng, precision=precision)      # noise seed from the OS (Network._entropy)
         # one engine call for all nGames: the slots (as many as fit the memory budget) start the next unplayed game
         # as soon as they end one (bb_selfplay_games), so the GPU stays full until the last games run out
         u = _uniform_table(nGames, eng.max_plies) if uniforms is None else np.asarray(uniforms)[:nGames]

@@ -9,13 +9,17 @@ step of csrc/train.cu; saveModel / loadModel keep the reference
 the flat vector (TF Saver bundles are SURVEY.md 8f-4).
 """
 import os
-import random
 
 import numpy as np
 import torch
 
 from . import engine as _engine
 from . import netinit
+
+
+def _entropy(bits):
+    """Seed material from the OS: independent of Python's and numpy's global streams, which callers seed to replay games."""
+    return int.from_bytes(os.urandom(8), 'little') >> (64 - bits)
 
 
 def states_from_planes(game, planes, device=0):
@@ -42,7 +46,7 @@ def states_from_planes(game, planes, device=0):
 class Network(object):
     PRECISION = 'fp32'                 # 'fp32': 1e-5 parity kernel; 'bf16': tcgen05 kernel (bulk self-play default)
 
-    def __init__(self, name, networkConstructor=None, tensorflowConfig={}, game=None, seed=0, device=0):
+    def __init__(self, name, networkConstructor=None, tensorflowConfig={}, game=None, seed=None, device=0):
         self._net_name = name
         self._net_game = game
         self._net_device = device
@@ -59,7 +63,8 @@ class Network(object):
         self._net_shape = networkConstructor
         cin = _engine.plane_shape(game)[2]
         self.setWeights(netinit.random_weights(cin, networkConstructor.policyShape, blocks=networkConstructor.blocks,
-                                               filters=networkConstructor.filters, dense=networkConstructor.dense, seed=seed))
+                                               filters=networkConstructor.filters, dense=networkConstructor.dense,
+                                               seed=_entropy(31) if seed is None else seed))   # unseeded, like tf.global_variables_initializer
         self.saveModel(name)                                          # Network.py:25
 
     # -- weights ----------------------------------------------------------------------------------
@@ -75,8 +80,9 @@ class Network(object):
         self._sync_weights()
         return self._net_loaded_weights
 
-    def _load_network_into(self, eng, precision=None, epsilon=None, seed=0):
+    def _load_network_into(self, eng, precision=None, epsilon=None, seed=None):
         self._sync_weights()
+        seed = _entropy(48) if seed is None else seed     # TF's noise is unseeded too; never drawn from `random` / `np.random` (the arena goldens replay those streams)
         s = self._net_shape
         eng.load_network(self._net_loaded_weights, s.blocks, s.filters, s.dense,
                          epsilon=s.epsilon if epsilon is None else epsilon, alpha=s.alpha, seed=seed,
@@ -113,7 +119,7 @@ class Network(object):
             s = self._net_shape
             self._net_trainer = Trainer(self._net_game, self._net_loaded_weights, s.blocks, s.filters, s.dense,
                                         optimizer=getattr(s, 'optimizer', 'sgd'), momentum=getattr(s, 'momentum', 0.9),
-                                        epsilon=s.epsilon, alpha=s.alpha, seed=random.getrandbits(48), device=self._net_device)
+                                        epsilon=s.epsilon, alpha=s.alpha, seed=_entropy(48), device=self._net_device)
         self._net_trainer.step(state, eval, policy, learningRate)
         self._net_dirty = True
         self.batchCount += 1
@@ -127,7 +133,7 @@ class Network(object):
             s = self._net_shape
             self._net_trainer = Trainer(self._net_game, self._net_loaded_weights, s.blocks, s.filters, s.dense,
                                         optimizer=getattr(s, 'optimizer', 'sgd'), momentum=getattr(s, 'momentum', 0.9),
-                                        epsilon=s.epsilon, alpha=s.alpha, seed=random.getrandbits(48), device=self._net_device)
+                                        epsilon=s.epsilon, alpha=s.alpha, seed=_entropy(48), device=self._net_device)
         self._net_trainer.step_stream(stream_dev, rec_offsets, learningRate)
         self._net_dirty = True
         self.batchCount += 1
