@@ -319,6 +319,84 @@ __global__ void __launch_bounds__(256) k_tr_conv_bwd_w_tiled(const float* __rest
     if (p < pairs) out[p] = acc[q];
   }
 }
+// The same for the template width (co = 16), all nine taps in one CTA: the chunk's dpre rows and its input rows with a halo
+// of W + 1 rows either side are staged once; a thread owns one ci and four co for all taps (36 accumulators, ten shared
+// loads per 36 FMAs), the CTA's NS row subsets are added in ascending order at the end.  Same partial layout as above.
+template <int CI, int CH>
+struct WRowCfg {
+  static constexpr int T = CI * 4;                                  // threads per row subset
+  static constexpr int NS = (256 / T) < 8 ? (256 / T) : 8;          // row subsets per CTA
+  static constexpr int HALO = 9;                                    // W + 1 <= 9
+  static constexpr int STAGE = CH * 16 + (CH + 2 * HALO) * CI + CH / 2;   // floats (masks: 256 u16)
+  static constexpr int RED = NS * (9 * CI * 16 + 16);
+  static constexpr int SMEM = (STAGE > RED ? STAGE : RED) * 4;
+};
+template <int CI, int CH>
+__global__ void __launch_bounds__(256) k_tr_conv_bwd_w_row16(const float* __restrict__ in, const float* __restrict__ dpre, float* __restrict__ part,
+                                                              int N, int H, int W) {
+  typedef WRowCfg<CI, CH> C;
+  extern __shared__ __align__(16) float tw_smem[];
+  float* s_dp = tw_smem;                                            // [CH][16]
+  float* s_in = tw_smem + CH * 16;                           // [CH + 2 HALO][CI]
+  unsigned short* s_mask = (unsigned short*)(s_in + (CH + 2 * C::HALO) * CI);
+  const int chunk = blockIdx.x, total = N * H * W, row0 = chunk * CH, tid = threadIdx.x;
+  for (int i = tid; i < CH * 16; i += 256) s_dp[i] = (row0 + i / 16 < total) ? dpre[(size_t)row0 * 16 + i] : 0.f;
+  for (int i = tid; i < (CH + 2 * C::HALO) * CI; i += 256) {
+    const long long e = (long long)row0 - C::HALO + i / CI;
+    s_in[i] = (e >= 0 && e < total) ? in[(size_t)e * CI + i % CI] : 0.f;
+  }
+  if (tid < CH) {
+    const int e = row0 + tid, cell = e % (H * W), y = cell / W, x = cell % W;
+    unsigned m = 0;
+    if (e < total)
+      for (int tap = 0; tap < 9; ++tap) {
+        const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W) m |= 1u << tap;
+      }
+    s_mask[tid] = (unsigned short)m;
+  }
+  __syncthreads();
+  const int sub = tid / C::T, lt = tid % C::T, ci = lt >> 2, cq = lt & 3;
+  float acc[9][4], accb[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int t9 = 0; t9 < 9; ++t9) { acc[t9][0] = acc[t9][1] = acc[t9][2] = acc[t9][3] = 0.f; }
+  if (sub < C::NS) {
+    for (int r = sub; r < CH; r += C::NS) {
+      const unsigned m = s_mask[r];
+      const float4 dp = *reinterpret_cast<const float4*>(s_dp + r * 16 + cq * 4);
+      accb[0] += dp.x; accb[1] += dp.y; accb[2] += dp.z; accb[3] += dp.w;
+#pragma unroll
+      for (int t9 = 0; t9 < 9; ++t9) {
+        if (m >> t9 & 1) {
+          const float xv = s_in[(r + C::HALO + (t9 / 3 - 1) * W + (t9 % 3 - 1)) * CI + ci];
+          acc[t9][0] = fmaf(xv, dp.x, acc[t9][0]); acc[t9][1] = fmaf(xv, dp.y, acc[t9][1]);
+          acc[t9][2] = fmaf(xv, dp.z, acc[t9][2]); acc[t9][3] = fmaf(xv, dp.w, acc[t9][3]);
+        }
+      }
+    }
+  }
+  __syncthreads();                                                  // staging is dead: the same memory takes the subsets' partials
+  constexpr int PER = 9 * CI * 16 + 16;
+  if (sub < C::NS) {
+    float* red = tw_smem + sub * PER;
+#pragma unroll
+    for (int t9 = 0; t9 < 9; ++t9)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) red[(t9 * CI + ci) * 16 + cq * 4 + k] = acc[t9][k];
+    if (ci == 0)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) red[9 * CI * 16 + cq * 4 + k] = accb[k];
+  }
+  __syncthreads();
+  constexpr int pairs = CI * 16;
+  float* out = part + (size_t)chunk * 10 * pairs;
+  for (int i = tid; i < PER; i += 256) {
+    float a = 0.f;
+#pragma unroll
+    for (int q = 0; q < C::NS; ++q) a += tw_smem[q * PER + i];
+    out[i] = a;                                                     // [tap][ci][co] for i < 9 pairs, then "tap 9" = bias at 9 pairs + co: the layout of the tiled kernel
+  }
+}
 // dw[tap][ci][co] = sum over chunks (ascending) of part[chunk][tap][...]; db likewise from "tap 9"
 // (a warp per output: lane l adds chunks l, l + 32, ... in ascending order, then the fixed xor tree)
 __global__ void k_tr_wgrad_reduce(const float* __restrict__ part, int chunks, int pairs, int co_n, float* __restrict__ dw, float* __restrict__ db) {
@@ -524,9 +602,9 @@ __global__ void k_tr_heads_bwd(const float* __restrict__ a, const float* __restr
 // parameter gradients of the heads: one block per output element
 //   [0,F) dwv' | F dbv' | [F+1, F+1+2F) dwp'[c][k] | +2 dbp'[k] | D dw1 | D db1 | D dw2 | 1 db2 | 2A dWp | A dbp
 struct HeadGradOut { float* wv; float* bv; float* wp; float* bp; float* d1w; float* d1b; float* d2w; float* d2b; float* pw; float* pb; };
-__global__ void k_tr_head_grads(const float* __restrict__ a, HeadBufs B, HeadGradOut G, TrainDims dm, int N) {
+__global__ void k_tr_head_grads(const float* __restrict__ a, HeadBufs B, HeadGradOut G, TrainDims dm, int N, int first) {
   __shared__ float red[32];
-  int b = blockIdx.x;
+  int b = blockIdx.x + first;                                       // first = 3F + 3 when k_tr_head_conv_grads has the convolutions
   const int F = dm.F, D = dm.D, A = dm.A, HW = dm.HW;
   const int tot = N * HW;
   float acc = 0.f;
@@ -544,6 +622,56 @@ __global__ void k_tr_head_grads(const float* __restrict__ a, HeadBufs B, HeadGra
   // HW * sum for the per-cell dense biases: multiply BEFORE the block sum is wrong for partial sums only if done per thread -- it is linear, fine
   acc = block_sum(acc, red);
   if (threadIdx.x == 0) *dst = acc;
+}
+
+// The 1x1 head convolutions' parameter gradients (the first 3F + 3 outputs above), row-chunked: a CTA takes TR_HCHUNK rows,
+// thread (subset, c) accumulates a[e][c] * {dvmap, dpmap0, dpmap1}[e] over its subset's rows (coalesced rows of a), the
+// subsets are added in ascending order; part[chunk][3F + 3] is reduced by k_tr_head_conv_reduce (a warp per output).
+// One block per output read the whole activation map with stride F: 0.6 ms of a 3.4 ms step at batch 4096.
+constexpr int TR_HCHUNK = 1024;
+__global__ void __launch_bounds__(256) k_tr_head_conv_grads(const float* __restrict__ a, HeadBufs B, float* __restrict__ part, int F, int total) {
+  __shared__ float red[16 * 3 * 17];                                 // [NS <= 16][3][F + 1] with F <= 16 ... sized by the host check F <= 16
+  const int NS = 256 / F < 16 ? 256 / F : 16;
+  const int sub = threadIdx.x / F, c = threadIdx.x % F;
+  const int row0 = blockIdx.x * TR_HCHUNK, rows = min(TR_HCHUNK, total - row0);
+  float av = 0.f, ap0 = 0.f, ap1 = 0.f, bv = 0.f, bp0 = 0.f, bp1 = 0.f;
+  if (sub < NS)
+    for (int r = sub; r < rows; r += NS) {
+      const size_t e = (size_t)row0 + r;
+      const float x = a[e * F + c], dv = B.dvmap[e], d0 = B.dpmap[e * 2], d1 = B.dpmap[e * 2 + 1];
+      av = fmaf(x, dv, av); ap0 = fmaf(x, d0, ap0); ap1 = fmaf(x, d1, ap1);
+      bv += dv; bp0 += d0; bp1 += d1;
+    }
+  if (sub < NS) {
+    float* r = red + sub * 3 * (F + 1);
+    r[c] = av; r[(F + 1) + c] = ap0; r[2 * (F + 1) + c] = ap1;
+    if (c == 0) { r[F] = bv; r[(F + 1) + F] = bp0; r[2 * (F + 1) + F] = bp1; }
+  }
+  __syncthreads();
+  // output order of k_tr_head_grads: [0,F) dwv | F dbv | [F+1, 3F+1) dwp[c][k] | 3F+1, 3F+2 dbp[k]
+  for (int o = threadIdx.x; o < 3 * F + 3; o += 256) {
+    int idx;
+    if (o < F) idx = o;
+    else if (o == F) idx = F;
+    else if (o < 3 * F + 1) { const int cc = (o - F - 1) / 2, k = (o - F - 1) % 2; idx = (1 + k) * (F + 1) + cc; }
+    else idx = (1 + (o - 3 * F - 1)) * (F + 1) + F;
+    float s = 0.f;
+    for (int q = 0; q < NS; ++q) s += red[q * 3 * (F + 1) + idx];
+    part[(size_t)blockIdx.x * (3 * F + 3) + o] = s;
+  }
+}
+__global__ void k_tr_head_conv_reduce(const float* __restrict__ part, int chunks, HeadGradOut G, int F) {
+  const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, n_out = 3 * F + 3;
+  if (o >= n_out) return;
+  float acc = 0.f;
+  for (int c = lane; c < chunks; c += 32) acc += part[(size_t)c * n_out + o];
+#pragma unroll
+  for (int k = 16; k; k >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, k);
+  if (lane) return;
+  if (o < F) G.wv[o] = acc;
+  else if (o == F) G.bv[0] = acc;
+  else if (o < 3 * F + 1) G.wp[o - F - 1] = acc;
+  else G.bp[o - 3 * F - 1] = acc;
 }
 
 // ---- L2 term and optimizers --------------------------------------------------------------------------------------------
@@ -605,6 +733,7 @@ struct bb_trainer {
   int cap_B = 0;                        // batch capacity of the activation buffers
   std::vector<float*> act, dact;        // [L+1]: input, tower outputs
   HeadBufs hb{};
+  float* hpart = nullptr;               // [chunks][3F + 3] partial gradients of the head convolutions
   float* wpart = nullptr;               // [chunks][10][pairs] partial weight gradients of the tiled kernel (per batch capacity)
   int8_t* planes_own = nullptr;         // batch assembled from a record stream
   float *eval_own = nullptr, *policy_own = nullptr, *noise_dev = nullptr;
@@ -658,11 +787,13 @@ int ensure_batch(bb_trainer* t, int B) {
   A_(t->hb.colsum, (size_t)d.A); A_(t->hb.scal, 8);
   A_(t->planes_own, cells * d.Cin); A_(t->eval_own, n); A_(t->policy_own, n * d.A); A_(t->recoff_dev, n);
   t->wpart = nullptr;
+  t->hpart = nullptr;
+  if (d.F <= 16) A_(t->hpart, ((cells + TR_HCHUNK - 1) / TR_HCHUNK) * (size_t)(3 * d.F + 3));
   {
     const size_t Fm = (size_t)(d.F > d.Cin ? d.F : d.Cin);
     if (Fm * d.F <= 1024 && Fm + d.F <= 96) {                                     // the tiled weight-gradient path applies to every tower layer
-      const size_t chunks = (cells + TR_WCHUNK - 1) / TR_WCHUNK;
-      A_(t->wpart, chunks * 10 * Fm * d.F);
+      const size_t chunks = (cells + 63) / 64;                                     // (the quarter-chunk form of small batches)
+      A_(t->wpart, (chunks < 4 * 296 ? chunks : (cells + TR_WCHUNK - 1) / TR_WCHUNK + 1) * 10 * Fm * d.F);
     }
   }
 #undef A_
@@ -703,7 +834,14 @@ int enqueue_step(bb_trainer* t, const int8_t* planes, const float* evalLabel, co
   k_tr_heads_bwd<<<B, 128, 0, s>>>(t->act[d.L], evalLabel, noise, eps, P, t->hb, t->dact[d.L], d, B);
   HeadGradOut G{t->gwf + cv.wf, t->gwf + cv.bf, t->gwf + cp.wf, t->gwf + cp.bf, t->g + t->o_d1w, t->g + t->o_d1b,
                 t->g + t->o_d2w, t->g + t->o_d2b, t->g + t->o_pw, t->g + t->o_pb};
-  k_tr_head_grads<<<3 * d.F + 3 + 3 * d.D + 1 + 3 * d.A, 128, 0, s>>>(t->act[d.L], t->hb, G, d, B);
+  if (d.F <= 16 && t->hpart) {
+    const int hchunks = (int)((cells + TR_HCHUNK - 1) / TR_HCHUNK);
+    k_tr_head_conv_grads<<<hchunks, 256, 0, s>>>(t->act[d.L], t->hb, t->hpart, d.F, (int)cells);
+    k_tr_head_conv_reduce<<<(3 * d.F + 3 + 7) / 8, 256, 0, s>>>(t->hpart, hchunks, G, d.F);
+    k_tr_head_grads<<<3 * d.D + 1 + 3 * d.A, 128, 0, s>>>(t->act[d.L], t->hb, G, d, B, 3 * d.F + 3);
+  } else {
+    k_tr_head_grads<<<3 * d.F + 3 + 3 * d.D + 1 + 3 * d.A, 128, 0, s>>>(t->act[d.L], t->hb, G, d, B, 0);
+  }
   // dact[l+1] holds dL/d(output of layer l).  Skip gradients: output of layer l (even, > 0) = relu(conv + act[l-1]), so
   // dpre of layer l is added to dact[l-1]; that buffer is first WRITTEN by the data gradient of layer l-1... which runs
   // later.  So: the data gradient of layer l-1 accumulates into dact[l-1] when a skip has already been stored there.
@@ -719,9 +857,17 @@ int enqueue_step(bb_trainer* t, const int8_t* planes, const float* evalLabel, co
     k_tr_relu_bwd<<<blocks_for(cells * c.co), 256, 0, s>>>(t->dact[l + 1], t->act[l + 1], dskip, cells * c.co);
     const int pairs = c.ci * c.co;
     if (pairs <= 1024 && c.ci + c.co <= 96 && t->wpart) {                             // narrow layers: tiled, two-stage (deterministic) reduction
-      const int chunks = (int)((cells + TR_WCHUNK - 1) / TR_WCHUNK);
+      int chunks = (int)((cells + TR_WCHUNK - 1) / TR_WCHUNK);
       const size_t smem = (size_t)TR_WCHUNK * (c.ci + c.co) * sizeof(float);
-      if (pairs <= 256) k_tr_conv_bwd_w_tiled<1><<<dim3(chunks, 10), 256, smem, s>>>(t->act[l], t->dact[l + 1], t->wpart, B, d.H, d.W, c.ci, c.co);
+      const bool row16 = c.co == 16 && d.W <= 8 && (c.ci == 16 || c.ci == 17 || c.ci == 3);
+      const bool small = cells < (size_t)TR_WCHUNK * 296;                              // fewer than two CTAs per SM at the full chunk: quarter chunks
+      if (row16 && small) chunks = (int)((cells + 63) / 64);
+#define BB_WROW(CI_, CH_) k_tr_conv_bwd_w_row16<CI_, CH_><<<chunks, 256, WRowCfg<CI_, CH_>::SMEM, s>>>(t->act[l], t->dact[l + 1], t->wpart, B, d.H, d.W)
+      if (row16 && c.ci == 16) { if (small) BB_WROW(16, 64); else BB_WROW(16, 256); }
+      else if (row16 && c.ci == 17) { if (small) BB_WROW(17, 64); else BB_WROW(17, 256); }
+      else if (row16 && c.ci == 3) { if (small) BB_WROW(3, 64); else BB_WROW(3, 256); }
+#undef BB_WROW
+      else if (pairs <= 256) k_tr_conv_bwd_w_tiled<1><<<dim3(chunks, 10), 256, smem, s>>>(t->act[l], t->dact[l + 1], t->wpart, B, d.H, d.W, c.ci, c.co);
       else k_tr_conv_bwd_w_tiled<4><<<dim3(chunks, 10), 256, smem, s>>>(t->act[l], t->dact[l + 1], t->wpart, B, d.H, d.W, c.ci, c.co);
       k_tr_wgrad_reduce<<<(9 * pairs + c.co + 7) / 8, 256, 0, s>>>(t->wpart, chunks, pairs, c.co, t->gwf + c.wf, t->gwf + c.bf);
     } else {
@@ -814,6 +960,9 @@ int bb_trainer_create(const bb_train_desc* desc, const float* w, size_t n_floats
   t->n_fold = foff;
   d.n_l2 = (int)l2.size();
   if (cudaSetDevice(t->device) != cudaSuccess) { set_error("cudaSetDevice failed"); delete t; return BB_ECUDA; }
+#define BB_WATTR(CI_, CH_) cudaFuncSetAttribute(k_tr_conv_bwd_w_row16<CI_, CH_>, cudaFuncAttributeMaxDynamicSharedMemorySize, WRowCfg<CI_, CH_>::SMEM)
+  BB_WATTR(16, 256); BB_WATTR(17, 256); BB_WATTR(3, 256); BB_WATTR(16, 64); BB_WATTR(17, 64); BB_WATTR(3, 64);
+#undef BB_WATTR
   cudaFuncSetAttribute(k_tr_conv_bwd_w_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_WCHUNK * 96 * (int)sizeof(float));
   cudaFuncSetAttribute(k_tr_conv_bwd_w_tiled<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_WCHUNK * 96 * (int)sizeof(float));
   int rc = BB_OK;
