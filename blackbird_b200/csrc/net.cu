@@ -44,6 +44,19 @@ struct TcParams {
   int w_blocks;
 };
 
+// tower widths other than 16 (net_wide.cuh): layer-by-layer over activations in HBM
+struct WideDev {
+  bool on = false;
+  int F = 0, layers = 0, ksteps0 = 0;      // ksteps0: 16-channel steps of the input planes
+  const float* w32 = nullptr;              // fp32: [layer][tap][ci][F] (stem ci = cin), BN folded
+  const float* bias = nullptr;             // [layer][F]
+  std::vector<size_t> w32_off, wbf_off;    // per layer: float / byte offsets
+  const uint8_t* wbf = nullptr;            // bf16 operand layout (net_wide.cuh)
+  const float* head_conv = nullptr;        // 3 F + 3
+  uint8_t *a0 = nullptr, *ax = nullptr, *ay = nullptr;      // bf16 activation tiles of one chunk: input planes, X, Y
+  float *f0 = nullptr, *fx = nullptr, *fy = nullptr;        // fp32 twin
+};
+
 struct NetDev {
   int game;
   bb_net_desc desc;
@@ -52,6 +65,7 @@ struct NetDev {
   int sm_count;
   bool use_tc = false;     // bf16 tcgen05 kernel instead of the fp32 SIMT one (bb_net_desc.precision)
   TcParams tc{};
+  WideDev wide;
 };
 
 template <class G>
@@ -345,6 +359,7 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
 
 }  // namespace bb
 #include "net_tc.cuh"
+#include "net_wide.cuh"
 namespace bb {
 
 template <class G>
@@ -530,6 +545,80 @@ static int net_serve_tc(NetDev* net, const NetServe& sv, float* policy, float* v
   return BB_OK;
 }
 
+// ---- other tower widths (net_wide.cuh) ---------------------------------------------------------------------------------
+template <int F>
+static int wide_conv_launch(const WideLayer& L, const WideGeo& geo, int n_chunk, int chunk_base, const int* count_dev, int sm_count, cudaStream_t stream) {
+  using C = WideCfg<F>;
+  static bool configured = false;
+  if (!configured) {
+    BB_CUDA(cudaFuncSetAttribute(k_wide_conv<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    configured = true;
+  }
+  const int tiles = (n_chunk + geo.PPT - 1) / geo.PPT, groups = (tiles + C::TPG - 1) / C::TPG;
+  k_wide_conv<F><<<groups < sm_count ? groups : sm_count, C::THREADS, C::SMEM, stream>>>(L, geo, n_chunk, chunk_base, count_dev);
+  BB_CUDA(cudaGetLastError());
+  return BB_OK;
+}
+
+template <class G>
+static int net_launch_wide(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream, int legal_only) {
+  using Tg = TcGeom<G>;
+  using State = typename G::State;
+  WideDev& wd = net->wide;
+  const int F = wd.F, HW = G::H * G::W;
+  const WideGeo geo = wide_geo<G>();
+  const size_t hsmem = wide_heads_smem<G>(F);
+  static bool configured[3][2] = {{false, false}, {false, false}, {false, false}};
+  if (!configured[G::ID][net->use_tc]) {
+    const int hmax = (int)wide_heads_smem<G>(1024);                  // the widest tower bb_net_load accepts
+    if (net->use_tc) BB_CUDA(cudaFuncSetAttribute(k_wide_heads<G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, hmax));
+    else BB_CUDA(cudaFuncSetAttribute(k_wide_heads<G, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, hmax));
+    configured[G::ID][net->use_tc] = true;
+  }
+  for (int base = 0; base < n; base += WIDE_CHUNK) {
+    const int nc = n - base < WIDE_CHUNK ? n - base : WIDE_CHUNK;
+    const unsigned cell_blocks = (unsigned)(((size_t)nc * HW + 255) / 256);
+    const void* last = nullptr;
+    if (net->use_tc) {
+      k_wide_stage<G><<<cell_blocks, 256, 0, stream>>>((const State*)states, wd.a0, nc, base, count_dev);
+      for (int l = 0; l < wd.layers; ++l) {
+        const bool odd = l & 1;
+        WideLayer L;
+        L.in = l == 0 ? wd.a0 : (odd ? wd.ax : wd.ay);
+        L.out = odd ? wd.ay : wd.ax;
+        L.skip = (!odd && l > 0) ? wd.ax : nullptr;                  // conv_2 + BN + block input (NetworkFactory.py:95-98)
+        L.w = wd.wbf + wd.wbf_off[l];
+        L.bias = wd.bias + (size_t)l * F;
+        L.ksteps = l == 0 ? wd.ksteps0 : F / 16;
+        int rc = F == 64 ? wide_conv_launch<64>(L, geo, nc, base, count_dev, net->sm_count, stream)
+                         : wide_conv_launch<256>(L, geo, nc, base, count_dev, net->sm_count, stream);
+        if (rc != BB_OK) return rc;
+        last = L.out;
+      }
+      WideHeadW hw{wd.head_conv};
+      k_wide_heads<G, true><<<(nc + WIDE_HP - 1) / WIDE_HP, 256, hsmem, stream>>>(net->p, hw, F, last, (const State*)states, nc, base, count_dev, policy, value, legal_only);
+    } else {
+      k_wide32_stage<G><<<cell_blocks, 256, 0, stream>>>((const State*)states, wd.f0, nc, base, count_dev);
+      for (int l = 0; l < wd.layers; ++l) {
+        const bool odd = l & 1;
+        const float* in = l == 0 ? wd.f0 : (odd ? wd.fx : wd.fy);
+        float* out = odd ? wd.fy : wd.fx;
+        const size_t total = (size_t)nc * HW * F;
+        const unsigned blocks = (unsigned)((total + 255) / 256 < 65535 * 16 ? (total + 255) / 256 : 65535 * 16);
+        k_wide32_conv<<<blocks, 256, 0, stream>>>(in, wd.w32 + wd.w32_off[l], wd.bias + (size_t)l * F, (!odd && l > 0) ? wd.fx : nullptr, out, G::H, G::W,
+                                                    l == 0 ? G::C : F, F, nc, base, count_dev);
+        last = out;
+      }
+      WideHeadW hw{wd.head_conv};
+      k_wide_heads<G, false><<<(nc + WIDE_HP - 1) / WIDE_HP, 256, hsmem, stream>>>(net->p, hw, F, last, (const State*)states, nc, base, count_dev, policy, value, 0);
+    }
+    BB_CUDA(cudaGetLastError());
+  }
+  (void)sizeof(Tg);
+  if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
+  return BB_OK;
+}
+
 int net_serve(NetDev* net, const NetServe& sv, float* policy, float* value, cudaStream_t stream) {
   if (!net->use_tc) { set_error("streaming mode needs the tensor-core network kernel (precision bf16)"); return BB_EINVAL; }
   BB_DISPATCH_GAME(net->game, return net_serve_tc<G>(net, sv, policy, value, stream));
@@ -556,13 +645,123 @@ int net_tc_footprint(NetDev* net, int* regs, int* smem) {
   return BB_EINVAL;
 }
 int net_sm_count(NetDev* net) { return net->sm_count; }
-bool net_is_tc(NetDev* net) { return net->use_tc; }
+bool net_is_tc(NetDev* net) { return net->use_tc && !net->wide.on; }   // the persistent (streaming) form exists for the 16-filter kernel; wider towers run tick by tick
 
 int net_forward(NetDev* net, const void* states, int n, const int* count_dev, float* policy, float* value, cudaStream_t stream, int legal_only) {
   if (n <= 0) return BB_OK;
+  if (net->wide.on) { BB_DISPATCH_GAME(net->game, return net_launch_wide<G>(net, states, n, count_dev, policy, value, stream, legal_only)); }
   if (net->use_tc) { BB_DISPATCH_GAME(net->game, return net_launch_tc<G>(net, states, n, count_dev, policy, value, stream, legal_only)); }
   else { BB_DISPATCH_GAME(net->game, return net_launch<G>(net, states, n, count_dev, policy, value, stream)); }
   return BB_EINVAL;
+}
+
+// Host side of bb_net_load for tower widths other than 16 (same flat input order as below)
+template <class G>
+static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, size_t n_floats) {
+  using Tg = TcGeom<G>;
+  const int F = d->filters, D = d->dense, blocks = d->blocks, cin = d->cin, A = G::A, HW = G::H * G::W;
+  const bool tc = d->precision == 1;
+  if (F < 1 || F > 1024) { set_error("filters must be in [1, 1024] (got %d)", F); return BB_EINVAL; }
+  if (tc && F != 64 && F != 256) { set_error("the tensor-core network kernels are built for filters = 16, 64 and 256 (got %d); precision fp32 takes any width", F); return BB_EINVAL; }
+  if (cin != G::C) { set_error("cin %d does not match the game's %d input planes", cin, G::C); return BB_EINVAL; }
+  if (D < 1 || D > NET_MAX_DENSE || blocks < 0) { set_error("dense must be in [1,%d], blocks >= 0", NET_MAX_DENSE); return BB_EINVAL; }
+  auto conv_sz = [](int k, int ci, int co) { return (size_t)k * k * ci * co + 5 * (size_t)co; };
+  const size_t need = conv_sz(3, cin, F) + 2 * (size_t)blocks * conv_sz(3, F, F) + conv_sz(1, F, 1) + D + D + D + 1 +
+                      conv_sz(1, F, 2) + 2 * (size_t)A + A;
+  if (n_floats != need) { set_error("bb_net_load: expected %zu floats for this shape, got %zu", need, n_floats); return BB_EINVAL; }
+  const int layers = 1 + 2 * blocks;
+  WideDev& wd = net->wide;
+  wd.on = true; wd.F = F; wd.layers = layers; wd.ksteps0 = Tg::KB_IN;
+  const float* p = w;
+  auto fold = [&](int k, int ci, int co, float* wout, float* bout) {          // wout[tap][ci][co]
+    const float* cw = p; p += (size_t)k * k * ci * co;
+    const float *b = p, *g = p + co, *be = p + 2 * co, *mu = p + 3 * co, *var = p + 4 * co;
+    p += 5 * (size_t)co;
+    for (int o = 0; o < co; ++o) {
+      const double s = (double)g[o] / sqrt((double)var[o] + 1e-3);
+      bout[o] = (float)(((double)b[o] - (double)mu[o]) * s + (double)be[o]);
+      for (size_t t = 0; t < (size_t)k * k * ci; ++t) wout[t * co + o] = (float)((double)cw[t * co + o] * s);
+    }
+  };
+  size_t off = 0;
+  for (int l = 0; l < layers; ++l) { wd.w32_off.push_back(off); off += (size_t)9 * (l == 0 ? cin : F) * F; }
+  std::vector<float> tw(off), tb((size_t)layers * F);
+  for (int l = 0; l < layers; ++l) fold(3, l == 0 ? cin : F, F, tw.data() + wd.w32_off[l], tb.data() + (size_t)l * F);
+  std::vector<float> hconv(3 * (size_t)F + 3), head(51 + 3 * (size_t)D + 1, 0.f);
+  fold(1, F, 1, hconv.data(), hconv.data() + F);                          // value conv: w[F], b
+  memcpy(head.data() + 51, p, sizeof(float) * (3 * (size_t)D + 1));       // d1.w, d1.b, d2.w, d2.b where heads_finish looks for them
+  p += 3 * (size_t)D + 1;
+  fold(1, F, 2, hconv.data() + F + 1, hconv.data() + F + 1 + 2 * (size_t)F);   // policy conv: w[F][2], b[2]
+  const float* pw = p;
+  const float* pb = p + 2 * (size_t)A;
+  auto upload = [&](const void* src, size_t bytes, const void** dst) -> int {
+    void* q = nullptr;
+    BB_CUDA(cudaMalloc(&q, bytes));
+    net->allocs.push_back(q);
+    BB_CUDA(cudaMemcpy(q, src, bytes, cudaMemcpyHostToDevice));
+    *dst = q;
+    return BB_OK;
+  };
+  auto zeroed = [&](size_t bytes, void** dst) -> int {
+    BB_CUDA(cudaMalloc(dst, bytes));
+    net->allocs.push_back(*dst);
+    BB_CUDA(cudaMemset(*dst, 0, bytes));
+    return BB_OK;
+  };
+  int rc;
+  if ((rc = upload(tb.data(), tb.size() * 4, (const void**)&wd.bias))) return rc;
+  if ((rc = upload(hconv.data(), hconv.size() * 4, (const void**)&wd.head_conv))) return rc;
+  if ((rc = upload(head.data(), head.size() * 4, (const void**)&net->p.head))) return rc;
+  if ((rc = upload(pw, 2 * (size_t)A * 4, (const void**)&net->p.pol_w))) return rc;
+  if ((rc = upload(pb, (size_t)A * 4, (const void**)&net->p.pol_b))) return rc;
+  net->use_tc = tc;
+  if (tc) {
+    // bf16 B operands: layer l, tap t, k-step ks: N = F rows x K = 16, element (n = cout, k) at byte (k / 8) * F * 16 + n * 16 + (k % 8) * 2
+    auto bf16_rn = [](float f) -> uint16_t {
+      uint32_t u;
+      memcpy(&u, &f, 4);
+      if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
+      u += 0x7FFFu + ((u >> 16) & 1u);
+      return (uint16_t)(u >> 16);
+    };
+    size_t boff = 0;
+    for (int l = 0; l < layers; ++l) { wd.wbf_off.push_back(boff); boff += (size_t)9 * (l == 0 ? wd.ksteps0 : F / 16) * F * 32; }
+    std::vector<uint16_t> wb(boff / 2, 0);
+    for (int l = 0; l < layers; ++l) {
+      const int ci_n = l == 0 ? cin : F, ks_n = l == 0 ? wd.ksteps0 : F / 16;
+      const float* lw = tw.data() + wd.w32_off[l];
+      uint16_t* dst = wb.data() + wd.wbf_off[l] / 2;
+      for (int t = 0; t < 9; ++t)
+        for (int ks = 0; ks < ks_n; ++ks)
+          for (int k = 0; k < 16; ++k)
+            for (int o = 0; o < F; ++o) {
+              const int ci = ks * 16 + k;
+              const float v = ci < ci_n ? lw[((size_t)t * ci_n + ci) * F + o] : 0.f;
+              dst[((size_t)(t * ks_n + ks) * F * 32) / 2 + (size_t)(k / 8) * F * 8 + (size_t)o * 8 + (k % 8)] = bf16_rn(v);
+            }
+    }
+    if ((rc = upload(wb.data(), wb.size() * 2, (const void**)&wd.wbf))) return rc;
+    const size_t tiles = (WIDE_CHUNK + Tg::PPT - 1) / Tg::PPT;
+    if ((rc = zeroed(tiles * wd.ksteps0 * 2 * WIDE_PLANE, (void**)&wd.a0))) return rc;       // padding rows stay zero for good
+    if ((rc = zeroed(tiles * (size_t)(F / 8) * WIDE_PLANE, (void**)&wd.ax))) return rc;
+    if ((rc = zeroed(tiles * (size_t)(F / 8) * WIDE_PLANE, (void**)&wd.ay))) return rc;
+  } else {
+    if ((rc = upload(tw.data(), tw.size() * 4, (const void**)&wd.w32))) return rc;
+    if ((rc = zeroed((size_t)WIDE_CHUNK * HW * cin * 4, (void**)&wd.f0))) return rc;
+    if ((rc = zeroed((size_t)WIDE_CHUNK * HW * F * 4, (void**)&wd.fx))) return rc;
+    if ((rc = zeroed((size_t)WIDE_CHUNK * HW * F * 4, (void**)&wd.fy))) return rc;
+  }
+  void* ctr = nullptr;
+  BB_CUDA(cudaMalloc(&ctr, 8));
+  BB_CUDA(cudaMemset(ctr, 0, 8));
+  net->allocs.push_back(ctr);
+  net->p.call_counter = (unsigned long long*)ctr;
+  net->p.layers = layers;
+  net->p.dense = D;
+  net->p.eps = d->epsilon;
+  net->p.alpha = d->alpha;
+  net->p.seed = d->noise_seed;
+  return BB_OK;
 }
 
 // Host side of bb_net_load: fold BN (training=False, eps 1e-3) into each convolution and lay the
@@ -574,7 +773,7 @@ template <class G>
 static int net_build(NetDev* net, const bb_net_desc* d, const float* w, size_t n_floats) {
   using Ge = NetGeom<G>;
   const int F = d->filters, D = d->dense, blocks = d->blocks, cin = d->cin, A = G::A;
-  if (F != NET_F) { set_error("this build of the network kernel is specialised for filters=%d (got %d)", NET_F, F); return BB_EINVAL; }
+  if (F != NET_F) return net_build_wide<G>(net, d, w, n_floats);
   if (cin != G::C) { set_error("cin %d does not match the game's %d input planes", cin, G::C); return BB_EINVAL; }
   if (D < 1 || D > NET_MAX_DENSE || blocks < 0) { set_error("dense must be in [1,%d], blocks >= 0", NET_MAX_DENSE); return BB_EINVAL; }
   auto conv_sz = [](int k, int ci, int co) { return (size_t)k * k * ci * co + 5 * (size_t)co; };

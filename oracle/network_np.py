@@ -186,13 +186,15 @@ def _bf16_rn(a):
     return u.astype(np.uint32).view(np.float32).reshape(np.shape(a))
 
 
-def forward_bf16_emulated(weights, planes):
+def forward_bf16_emulated(weights, planes, last_bf16=False):
     """What blackbird_b200/csrc/net_tc.cuh computes, with its rounding points: BN folded into the
     convolutions in double and stored as bf16 tower weights / fp32 biases (net.cu net_build), bf16
     activations between tower layers (fp32 accumulation, + fp32 bias, + bf16 skip, ReLU, round), the last
     tower layer kept in fp32 for the heads, heads in fp32.  Only the accumulation ORDER differs from the
     kernel, so the kernel must agree with this far more tightly (~1e-3 of a probability: a rare bf16
-    rounding flip of one activation) than with the fp64 graph (2e-2).  Test infrastructure only."""
+    rounding flip of one activation) than with the fp64 graph (2e-2).  last_bf16: the layer-by-layer kernels of
+    net_wide.cuh (other tower widths) store the last tower layer as bf16 too and feed the heads from that.
+    Test infrastructure only."""
     f32 = np.float32
     w = {k: np.asarray(v, dtype=np.float64) for k, v in weights.items()}
 
@@ -220,7 +222,7 @@ def forward_bf16_emulated(weights, planes):
         x = _bf16_rn(act)
         if li % 2 == 0:
             skip = x
-    x = act                                 # heads read the fp32 registers of the last epilogue
+    x = _bf16_rn(act) if last_bf16 else act  # heads read the fp32 registers of the last epilogue (16 filters) / the stored bf16 activations
     kv, bv = fold('value.conv')
     kp, bp = fold('policy.conv')
     hv = relu(x @ kv[0, 0] + bv).sum(axis=(1, 2))[:, 0]                        # s = sum_hw relu(bn(conv))

@@ -135,6 +135,94 @@ def test_bf16_launch_mode_vs_fp64(mods, game, n_states, jitter, seed):
     eng.close()
 
 
+WIDE_CASES = [('TicTacToe', 64, 2, 300), ('Connect4', 64, 2, 400), ('DragonChess', 64, 1, 60),
+              ('TicTacToe', 256, 1, 200), ('Connect4', 256, 1, 150), ('DragonChess', 256, 1, 24)]
+
+
+@pytest.mark.parametrize('game,filters,blocks,n', WIDE_CASES + [('Connect4', 40, 1, 100)])
+def test_other_tower_widths_fp32_vs_fp64(mods, game, filters, blocks, n):
+    """NetworkFactory.py:46-103 takes `filters` from the YAML: the fp32 path takes any width (the layer-by-layer SIMT
+    twin of net_wide.cuh), same 1e-5 bar as the template width."""
+    engine, _ = mods
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=blocks, filters=filters, dense=16, seed=7, jitter=0.2)
+    eng = engine.Engine(game, 'dynamic', n_games=1, evaluator='net')
+    eng.load_network(network_np.flatten_weights(w), blocks, filters, 16)
+    states = playout_states(game, n, seed=2)
+    dev = pack(engine, game, states)
+    pol, val = eng.net_forward(dev)
+    planes = np.concatenate([s.AsInputArray() for s in states])
+    want_p, want_v = network_np.forward(w, planes, dtype=np.float64)
+    got_p, got_v = pol.cpu().numpy().astype(np.float64), val.cpu().numpy().astype(np.float64)
+    assert np.abs(got_p.sum(axis=1) - 1).max() < 1e-6
+    assert (np.abs(got_p - want_p) <= REL_TOL * np.abs(want_p) + 1e-8).all(), \
+        (np.abs(got_p - want_p) / np.maximum(np.abs(want_p), 1e-30)).max()
+    assert np.abs(got_v - want_v).max() < REL_TOL
+    pol2, val2 = eng.net_forward(dev)
+    assert torch.equal(pol, pol2) and torch.equal(val, val2)
+    eng.close()
+
+
+@pytest.mark.parametrize('game,filters,blocks,n', WIDE_CASES)
+def test_other_tower_widths_bf16_vs_fp64(mods, game, filters, blocks, n):
+    """k_wide_conv<64 / 256> (tcgen05, M128 N64 / N256 K16, weights streamed through a shared-memory ring, activations in
+    HBM between layers) against the fp64 graph at 2e-2 and against the CPU restatement of its rounding points; batch sizes
+    cover one position, partial tiles / groups and more groups than CTAs would take in one pass."""
+    engine, _ = mods
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=blocks, filters=filters, dense=16, seed=3, jitter=0.2)
+    eng = engine.Engine(game, 'dynamic', n_games=1, evaluator='net')
+    eng.load_network(network_np.flatten_weights(w), blocks, filters, 16, precision='bf16')
+    states = playout_states(game, n, seed=2)
+    dev_all = pack(engine, game, states)
+    planes_all = np.concatenate([s.AsInputArray() for s in states])
+    ppt = {'TicTacToe': 8, 'Connect4': 2, 'DragonChess': 1}[game]
+    tpg = 4 if filters == 64 else 2
+    for m in (1, ppt * tpg - 1, ppt * tpg + 1, n, ppt * tpg * 148 * 2 + 5, 4096 + 3 * ppt + 1):
+        idx = np.arange(m) % n
+        dev = dev_all[torch.as_tensor(idx, device=dev_all.device)]
+        pol, val = eng.net_forward(dev)
+        gp, gv = pol.cpu().numpy(), val.cpu().numpy()
+        first = {int(i): k for k, i in reversed(list(enumerate(idx)))}
+        firsts = np.array([first[int(i)] for i in idx])
+        assert np.array_equal(gp, gp[firsts]) and np.array_equal(gv, gv[firsts])      # same position, same bits, wherever it sits
+        uniq = np.unique(idx)
+        sel = np.array([first[int(i)] for i in uniq])
+        got_p, got_v = gp[sel].astype(np.float64), gv[sel].astype(np.float64)
+        want_p, want_v = network_np.forward(w, planes_all[uniq], dtype=np.float64)
+        emu_p, emu_v = network_np.forward_bf16_emulated(w, planes_all[uniq], last_bf16=True)
+        e64p, e64v = np.abs(got_p - want_p).max(), np.abs(got_v - want_v).max()
+        eep, eev = np.abs(got_p - emu_p).max(), np.abs(got_v - emu_v).max()
+        print('[bf16 parity, %d filters] %s batch=%d: vs fp64 policy abs %.3e value abs %.3e; vs bf16 restatement policy abs %.3e value abs %.3e'
+              % (filters, game, m, e64p, e64v, eep, eev))
+        assert np.abs(got_p.sum(axis=1) - 1).max() < 1e-5
+        assert e64p <= BF16_TOL and e64v <= BF16_TOL, (m, e64p, e64v)
+        assert eep <= BF16_EMU_TOL and eev <= BF16_EMU_TOL, (m, eep, eev)
+        pol2, val2 = eng.net_forward(dev)
+        assert torch.equal(pol, pol2) and torch.equal(val, val2)
+    eng.close()
+
+
+def test_search_with_a_wide_network_matches_the_oracle_search(mods):
+    """A 64-filter network behind the search (tick mode: the persistent kernel pair exists for the template width only):
+    visit counts equal the oracle search fed the replayed network answers."""
+    engine, _ = mods
+    game = 'Connect4'
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=1, filters=64, dense=16, seed=11, jitter=0.2)
+    eng = engine.Engine(game, 'fixed', n_games=16, evaluator='net', max_depth=6)
+    eng.load_network(network_np.flatten_weights(w), 1, 64, 16, precision='bf16')
+    assert not eng.streaming()
+    eng.reset()
+    eng.begin_move(60)
+    eng.run()
+    st = eng.root_stats(A)
+    plays = st['plays'][:, :int(st['n_children'][0])]
+    assert (st['n_children'] == 7).all() and int(plays[0].sum()) >= 58
+    assert (plays == plays[0]).all()                      # sixteen identical roots, deterministic network: identical trees
+    eng.close()
+
+
 @pytest.mark.parametrize('game,kind,P,G', [('Connect4', 'fixed', 64, 2048), ('TicTacToe', 'dynamic', 40, 1024), ('DragonChess', 'dynamic', 8, 96)])
 def test_bf16_serve_mode_vs_fp64(mods, game, kind, P, G):
     """The same kernel in SERVE mode (persistent, batches claimed from the request ring by k_search_stream's tickets):

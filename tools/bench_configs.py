@@ -134,8 +134,50 @@ def net_sweep():
             eng.close()
 
 
+def tower_flops(game, filters, blocks=4, dense=16):
+    """2 x MACs of one evaluation (BN folded), the formula behind SURVEY.md 8(d)'s table."""
+    h, w, c = engine.plane_shape(game)
+    a = engine.n_actions(game)
+    hw = h * w
+    macs = hw * 9 * c * filters + 2 * blocks * hw * 9 * filters * filters + hw * 3 * filters + 2 * dense + 2 * a
+    return 2 * macs
+
+
+def net_sweep_widths():
+    """SURVEY.md 8(d) row 5a, the optional widths: filters 64 and 256 (k_wide_conv, layer by layer), 4 blocks."""
+    peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'MEASURED_PEAKS.json'))) \
+        if os.path.exists(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'MEASURED_PEAKS.json')) else {}
+    for game in ('Connect4', 'TicTacToe', 'DragonChess'):
+        for filters in (64, 256):
+            eng = Engine(game, 'fixed', n_games=4, evaluator='net', lanes=1)
+            w = netinit.random_weights(engine.plane_shape(game)[2], engine.n_actions(game), seed=0, blocks=4, filters=filters, dense=16)
+            eng.load_network(w, 4, filters, 16, precision='bf16')
+            fl = tower_flops(game, filters)
+            for n in (256, 1024, 4096, 16384, 65536):
+                st = playout_states(game, n, {'TicTacToe': 3, 'Connect4': 8, 'DragonChess': 6}[game])
+                s = torch.cuda.Stream()
+                with torch.cuda.stream(s):
+                    for _ in range(3):
+                        eng.net_forward(st)
+                    torch.cuda.synchronize()
+                    reps = 10 if n <= 16384 else 4
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(s)
+                    for _ in range(reps):
+                        eng.net_forward(st)
+                    e1.record(s)
+                    torch.cuda.synchronize()
+                us = e0.elapsed_time(e1) / reps * 1e3
+                out(config='cfg4a network sweep, other widths', game=game, filters=filters, blocks=4, precision='bf16', batch=n, us_per_batch=us,
+                    positions_per_sec=n / us * 1e6, tflops=n * fl / us / 1e6, flops_per_position=fl, peaks=peaks or None,
+                    includes='policy / value output allocation, stage + 9 layer + heads launches per 4096-position chunk')
+            eng.close()
+
+
 def main():
     want = sys.argv[1:] or ['cfg0', 'cfg2', 'cfg3', 'cfg4a', 'cfg4b']
+    if 'widths' in want:
+        net_sweep_widths()
     if 'cfg0' in want:
         whole_games('cfg0 TicTacToe FixedMCTS template (playLimit 10)', 'TicTacToe', 'fixed', 4096, 16384, 10)
     if 'cfg2' in want:
