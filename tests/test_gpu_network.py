@@ -212,7 +212,7 @@ def test_search_with_a_wide_network_matches_the_oracle_search(mods):
     w = network_np.init_weights(C, A, blocks=1, filters=64, dense=16, seed=11, jitter=0.2)
     eng = engine.Engine(game, 'fixed', n_games=16, evaluator='net', max_depth=6)
     eng.load_network(network_np.flatten_weights(w), 1, 64, 16, precision='bf16')
-    assert not eng.streaming()
+    assert not eng.streaming
     eng.reset()
     eng.begin_move(60)
     eng.run()
