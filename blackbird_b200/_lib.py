@@ -21,7 +21,7 @@ GAME_IDS = {'TicTacToe': TICTACTOE, 'Connect4': CONNECT4, 'DragonChess': DRAGONC
 class bb_config(C.Structure):
     _fields_ = [('game', C.c_int32), ('search', C.c_int32), ('max_depth', C.c_int32), ('evaluator', C.c_int32),
                 ('n_games', C.c_int32), ('node_cap', C.c_int32), ('max_plies', C.c_int32), ('device', C.c_int32),
-                ('exploration_rate', C.c_double), ('value_f64', C.c_int32), ('lanes', C.c_int32), ('reserved', C.c_int32 * 6)]
+                ('exploration_rate', C.c_double), ('value_f64', C.c_int32), ('lanes', C.c_int32), ('contexts', C.c_int32), ('reserved', C.c_int32 * 5)]
 
 
 class bb_net_desc(C.Structure):

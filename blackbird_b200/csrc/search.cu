@@ -265,6 +265,9 @@ struct EngineT : bb_engine {
     plan_rec(P, 0, G::A);
     BB_CUDA(cudaMemcpyToSymbol(c_plan, &P, sizeof P, sizeof(PairwisePlan) * G::ID));
     const size_t n = c.n_games, cap = c.node_cap;
+    const size_t nw = n * (size_t)(c.contexts > 0 ? c.contexts : 1);   // evaluator mailboxes: one per slot, or per (slot, context) in virtual-loss mode
+    d.vl = c.contexts;
+    d.ctx = nullptr;
     d.n_games = c.n_games;
     d.g0 = 0;
     d.n_total = c.n_games;
@@ -290,12 +293,13 @@ struct EngineT : bb_engine {
 #define A_(p, cnt) if ((rc = alloc(&p, cnt)) != BB_OK) return rc
     A_(d.slots, n);
     A_(d.nodes, n * 2 * cap);
-    A_(d.path, n * PATH_LEN);
+    A_(d.path, nw * PATH_LEN);
+    if (c.contexts > 0) A_(d.ctx, nw);
     A_(ctl_dev, lanes.size());
     A_(d.req_slot, n);
     A_(d.req_state, n);
-    A_(d.resp_policy, n * G::A);
-    A_(d.resp_value, n);
+    A_(d.resp_policy, nw * G::A);
+    A_(d.resp_value, nw);
     A_(d.rec_states, n * (c.max_plies + 1));
     A_(d.rec_off, n * (c.max_plies + 2));
     A_(d.pool_actions, n * d.pool_cap);
@@ -311,15 +315,15 @@ struct EngineT : bb_engine {
     d.next_row = next_row_dev;
     {
       size_t qn = RING_MIN_ENTRIES;                                // power of two, >= 4 tickets per slot (see StreamCtl)
-      while (qn < 4 * n) qn <<= 1;
+      while (qn < 4 * nw) qn <<= 1;
       d.q_mask = (unsigned)(qn - 1);
       A_(q_dev, 1);
       A_(d.q_ent, qn);
-      A_(d.q_state, n);
-      A_(d.resp_seq, n);
+      A_(d.q_state, nw);
+      A_(d.resp_seq, nw);
       BB_CUDA(cudaMemset(q_dev, 0, sizeof(StreamCtl)));
       BB_CUDA(cudaMemset(d.q_ent, 0, qn * sizeof(unsigned long long)));
-      BB_CUDA(cudaMemset(d.resp_seq, 0, n * sizeof(unsigned)));
+      BB_CUDA(cudaMemset(d.resp_seq, 0, nw * sizeof(unsigned)));
       d.q = nullptr;                                               // set only in the copy handed to the streaming kernels
       // evaluation cache (common.cuh): 2^22 entries of 64 bytes unless BB_EVAL_CACHE says otherwise (log2 entries; 0 = off)
       d.ecache = nullptr;
@@ -364,6 +368,7 @@ struct EngineT : bb_engine {
     // it is idle, so a search CTA with the default (small) carve-out could never join an SM that runs a network
     // CTA (which needs ~100 KB and therefore the large carve-out).  Same preference for all three.
     BB_CUDA(cudaFuncSetAttribute(k_search_stream<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    BB_CUDA(cudaFuncSetAttribute(k_search_stream<G, true>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     BB_CUDA(cudaFuncSetAttribute(k_advance<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     return reset(nullptr);
   }
@@ -413,7 +418,7 @@ struct EngineT : bb_engine {
     BB_CUDA(cudaMemsetAsync(ctl_dev, 0, lanes.size() * sizeof(TickCtl), stream));
     BB_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(StreamCtl), stream));
     BB_CUDA(cudaMemsetAsync(d.q_ent, 0, ((size_t)d.q_mask + 1) * sizeof(unsigned long long), stream));
-    BB_CUDA(cudaMemsetAsync(d.resp_seq, 0, (size_t)d.n_games * sizeof(unsigned), stream));
+    BB_CUDA(cudaMemsetAsync(d.resp_seq, 0, (size_t)d.n_games * (size_t)(d.vl > 0 ? d.vl : 1) * sizeof(unsigned), stream));
     for (Lane& L : lanes) L.par = 0;
     BB_CUDA(cudaStreamSynchronize(stream));
     return BB_OK;
@@ -433,6 +438,7 @@ struct EngineT : bb_engine {
 
   // one tick of one lane = advance kernel + evaluator kernel; request counters alternate by tick parity
   int tick(Lane& L) {
+    if (d.vl > 0) { set_error("virtual-loss mode (bb_config.contexts) runs in streaming mode only: load a bf16 network of the template width (bb_net_load, precision 1)"); return BB_EINVAL; }
     const bool timed = prof && L.prof_used + 3 <= L.prof_ev.size();
     if (timed) cudaEventRecord(L.prof_ev[L.prof_used], L.stream);
     if (cfg.evaluator == BB_EVAL_ROLLOUT)
@@ -568,7 +574,8 @@ struct EngineT : bb_engine {
       int nregs = 0, nsmem = 0;
       cudaFuncAttributes fa{};
       stream_fits = 0;
-      if (net_tc_footprint(net, &nregs, &nsmem) == BB_OK && cudaFuncGetAttributes(&fa, k_search_stream<G>) == cudaSuccess) {
+      if (net_tc_footprint(net, &nregs, &nsmem) == BB_OK &&
+          (d.vl > 0 ? cudaFuncGetAttributes(&fa, k_search_stream<G, true>) : cudaFuncGetAttributes(&fa, k_search_stream<G>)) == cudaSuccess) {
         int sregs = ((fa.numRegs * 32 + 255) / 256 * 256) * ((STREAM_WARPS_PER_CTA + 3) / 4);   // per register-file quarter
         if (getenv("BB_STREAM_FORCE")) sregs = 0;                 // experiments only: a wrong guess ends in the watchdog, not a hang
         stream_fits = (nregs + sregs <= 16384 && nsmem + (int)fa.sharedSizeBytes + 1024 <= 227 * 1024) ? 1 : 0;
@@ -604,7 +611,8 @@ struct EngineT : bb_engine {
     if ((rc = net_serve(net, sv, d.resp_policy, d.resp_value, net_stream))) return rc;
     BB_CUDA(cudaEventRecord(st_ev[3], net_stream));
     BB_CUDA(cudaEventRecord(st_ev[0], stream));
-    k_search_stream<G><<<grid, 32 * STREAM_WARPS_PER_CTA, 0, stream>>>(e);
+    if (d.vl > 0) k_search_stream<G, true><<<grid, 32 * STREAM_WARPS_PER_CTA, 0, stream>>>(e);
+    else k_search_stream<G><<<grid, 32 * STREAM_WARPS_PER_CTA, 0, stream>>>(e);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaEventRecord(st_ev[1], stream));
     host_launches += 3;
@@ -1038,6 +1046,8 @@ int bb_engine_create(const bb_config* cfg, bb_engine** out) {
     set_error("value_f64 goes with BB_EVAL_ROLLOUT and only with it: rollout values are exact Python numbers (f64), network values accumulate in f32 (SURVEY.md A.9)");
     return BB_EINVAL;
   }
+  if (cfg->contexts < 0 || cfg->contexts > 64) { set_error("contexts must be in [0, 64] (got %d)", cfg->contexts); return BB_EINVAL; }
+  if (cfg->contexts > 0 && cfg->evaluator != BB_EVAL_NET) { set_error("virtual-loss mode (contexts > 0) needs the built-in network evaluator (BB_EVAL_NET)"); return BB_EINVAL; }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { set_error("no CUDA device: the engine has no CPU fallback"); return BB_ECUDA; }
   if (cfg->device < 0 || cfg->device >= ndev) { set_error("device %d out of range (%d devices)", cfg->device, ndev); return BB_EINVAL; }

@@ -333,7 +333,8 @@ struct Path {
 // whether the PARENT's side to move is playerForValue.  The path is in registers, so all the
 // read-modify-writes are independent and issue in one memory round trip (lane d owns depth d).
 // Ancestors above Root are never read again in self-play (A.13) and are not kept.
-template <class G>
+// VO (virtual-loss mode): values only -- the descent has already counted the visit at every node it passed.
+template <class G, bool VO = false>
 __device__ void backup(const Slot<G>& s, Node* nodes, const Path& path, float eval) {
   const int lane = lane_id();
   float v = __fmul_rn(__fadd_rn(eval, 1.0f), 0.5f);         // (value + 1) * 0.5 in f32
@@ -348,7 +349,7 @@ __device__ void backup(const Slot<G>& s, Node* nodes, const Path& path, float ev
         const uint32_t parent = nodes[m].h.parent;
         const int pp = meta_player(nodes[parent].h.meta);
         NodeStat st = nodes[m].s;
-        nodes[m].s.plays = st.plays + 1;
+        if (!VO) nodes[m].s.plays = st.plays + 1;
         nodes[m].s.value = __fadd_rn(st.value, pp == p ? v : flip);
         m = parent;
         --d;
@@ -370,7 +371,7 @@ __device__ void backup(const Slot<G>& s, Node* nodes, const Path& path, float ev
       BB_ASSERT((e & 0x7FFFFFFFu) < s.n_nodes);
       uint2* q = reinterpret_cast<uint2*>(&nodes[e & 0x7FFFFFFFu].s);
       uint2 w = *q;                                          // (plays, value)
-      w.x += 1;
+      if (!VO) w.x += 1;
       if (parent_player != 0) w.y = __float_as_uint(__fadd_rn(__uint_as_float(w.y), parent_player == p ? v : flip));
       *q = w;
     }

@@ -403,6 +403,244 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
   return s.phase;
 }
 
+
+// ---- virtual-loss mode (bb_config.contexts = W; streaming mode only) -----------------------------------------------------
+// W simulations of a game are in flight at a time.  A simulation counts its visit at every node ON THE WAY DOWN (the root at the
+// start of the descent, each child when it is selected) and adds its value on the way up, so the next descent already sees the
+// visits of the ones still waiting for the network and is steered elsewhere -- the "virtual loss": a visit without a value
+// lowers Value / Plays.  Everything else is the exact mode's code (select, expansion, the value transform).
+// Order is fixed, so results do not depend on when answers arrive: contexts take turns in strict cyclic order; a context runs
+// until it must wait (its evaluation is posted, or it met a node whose evaluation another context has asked for: META_PENDING)
+// or its simulation ends; then the NEXT context's turn comes, and a context that waits for an answer is waited for.  Between
+// two turns of a context every other context has had one, so a pending node it met has been resolved when it looks again.
+// With W = 1 the visits counted on the way down are never read before the values arrive: the records equal the exact mode's
+// bit for bit (tests).  W > 1 is NOT the reference's search: reported separately, never the bench line.
+template <class G>
+__device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, uint32_t* ticket, uint32_t* mailbox) {
+  const int lane = lane_id();
+  const int W = E.vl;
+  Slot<G> s = E.slots[g];
+  if (!phase_busy(s.phase)) return s.phase;
+  unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0, n_look = 0, n_hit = 0;
+  constexpr bool EC = G::A <= ECACHE_MAX_ACTIONS;
+  Path path;
+  Node* nodes = E.half(g, s.half);
+  NodeHdr ch;
+  ch.parent = NONE; ch.child_base = NONE; ch.meta = 0; ch.eval = 0.f;
+  if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) s.phase = BB_PH_RUN;   // "the context whose turn it is waits": the caller has seen its answer
+  int budget = E.step_budget * (W > 4 ? 4 : W);
+  bool waiting = false;
+  for (;;) {
+    if (s.phase == BB_PH_COMPACT) {
+      budget -= 2 * E.compact_rounds;
+      run_compaction(E, s, g, ws, E.compact_rounds);
+      if (s.phase != BB_PH_MOVE_READY || !E.autoplay || s.moves_budget == 0) break;
+      nodes = E.half(g, s.half);
+      begin_move(E, s, nodes, path, E.play_limit);
+    }
+    if (s.phase != BB_PH_RUN) break;
+    // ---- the turn of context c ---------------------------------------------------------------------------------------
+    const uint32_t c = s.ctx_cur, mb = (uint32_t)g * (uint32_t)W + c;
+    Ctx<G>* cx = E.ctx + mb;
+    uint32_t* prow = E.path + (size_t)mb * PATH_LEN;
+    const int cst = cx->st;
+    int step = ST_TOP;
+    bool cached = false;                                        // the evaluation this context parks on was answered by the memo
+    float cached_v = 0.f;
+    if (cst == CTX_WAIT_EXPAND || cst == CTX_WAIT_LEAF) {
+      const uint32_t tk = cx->req_idx;
+      if (*reinterpret_cast<volatile unsigned*>(&E.resp_seq[mb]) != tk + 1u) {       // not answered yet: the slot waits for THIS context
+        s.req_idx = tk;
+        s.phase = BB_PH_WAIT_LEAF;
+        waiting = true;
+        break;
+      }
+      fence_acq_rel();
+      s.cur_state = cx->cur_state; s.cur = cx->cur; s.depth = cx->depth; s.last_action = cx->last_action;
+      path.load(prow);
+      ch = nodes[s.cur].h;
+      ch.eval = __ldcg(&E.resp_value[mb]);
+      ch.meta = (ch.meta | META_HAS_VALUE) & ~META_PENDING;
+      if (lane == 0) nodes[s.cur].h = ch;
+      step = cst == CTX_WAIT_EXPAND ? ST_EXPAND : ST_LEAF;
+    } else if (cst == CTX_RETRY) {
+      s.cur_state = cx->cur_state; s.cur = cx->cur; s.depth = cx->depth; s.last_action = cx->last_action;
+      path.load(prow);
+      ch = nodes[s.cur].h;
+      BB_ASSERT(!(ch.meta & META_PENDING));
+    } else {                                                      // idle: start the next simulation, if the move has any left
+      if (s.root_plays >= s.end_plays) {
+        if (s.ctx_busy != 0) { s.ctx_cur = (c + 1u) % (uint32_t)W; continue; }
+        // ---- every simulation of the move has come back: MCTS.py:298-299, then the self-play step as in the exact mode ----
+        s.ctx_cur = 0;
+        s.phase = BB_PH_MOVE_READY;
+        if (!E.autoplay) break;
+        BB_ASSERT(s.root < s.n_nodes);
+        const NodeHdr rh = nodes[s.root].h;
+        const int k = meta_nchild(rh.meta);
+        BB_ASSERT(rh.child_base + (uint32_t)k <= s.n_nodes && s.ply < E.max_plies);
+        int j;
+        if (E.temp_mode == 1) {
+          const int row = E.n_rows ? (int)s.row : (int)(((unsigned)g + s.game_no) % (unsigned)E.n_total);
+          j = sample_child(nodes + rh.child_base, k, E.uniforms[(size_t)row * E.max_plies + s.ply]);
+        } else {
+          double u;
+          NodeHdr dummy;
+          dummy.meta = 0;
+          j = puct_select<SelectChunks<G>::N, false>(nodes + rh.child_base, k, E.c, &u, &dummy);
+          if (j != 0x7FFFFFFF && !(u > 0.0) && j < meta_action(dummy.meta)) j = 0x7FFFFFFF;
+        }
+        if (rh.child_base == NONE || k == 0 || j < 0 || j >= k) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
+        play_move(E, s, g, nodes, j, &n_done);
+        n_moves += 1;
+        if (s.moves_budget > 0) s.moves_budget -= 1;
+        bool again = s.phase == BB_PH_GAME_OVER && E.refill;
+        if (s.phase == BB_PH_GAME_OVER && E.n_rows) {
+          unsigned r = 0;
+          if (lane == 0) r = atomicAdd(E.next_row, 1u);
+          r = __shfl_sync(0xFFFFFFFFu, r, 0);
+          again = r < (unsigned)E.n_rows;
+          if (again) {
+            s.row = r;
+            if (lane == 0) E.rec_off[(size_t)r * (E.max_plies + 2)] = 0;
+          }
+        }
+        if (again) {
+          s.game_no += 1;
+          s.root_state = G::initial();
+          s.root = NONE;
+          s.n_nodes = 0;
+          s.ply = 0;
+          s.pool_used = 0;
+          s.winner = WIN_NONE;
+          s.phase = BB_PH_MOVE_READY;
+          if (s.moves_budget != 0) begin_move(E, s, nodes, path, E.play_limit);
+        }
+        if (budget <= 0) break;
+        continue;
+      }
+      start_descent(s, path);
+      if (lane == 0) nodes[s.root].s.plays += 1;               // the visit, on the way down
+      s.root_plays += 1;
+      s.ctx_busy += 1;
+      ch = nodes[s.root].h;
+    }
+    // ---- run the context until its simulation ends or it must wait -----------------------------------------------------
+    int park = -1;                                              // CTX_* to park the context with; CTX_IDLE = simulation finished
+    while (park < 0) {
+      if (step == ST_TOP) {
+        if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }
+        if (ch.child_base == NONE) {
+          if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; }
+          if (ch.meta & META_PENDING) { park = CTX_RETRY; break; }
+          // A memoised answer is taken exactly like a computed one -- the context parks, the node is pending, the answer sits in
+          // the mailbox when the turn comes back -- so that WHEN another game's answer reached the cache cannot change the order
+          // of events in this game (the memo is filled by all games: hit or miss depends on timing).
+          if constexpr (EC) if (E.ecache) {
+            n_look += 1;
+            if (ecache_lookup(E, s.cur_state, ws, &cached_v)) { n_hit += 1; cached = true; }
+          }
+          park = CTX_WAIT_EXPAND;
+          break;
+        }
+        step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;
+      } else if (step == ST_EXPAND) {
+        const int k = expand_node<G, false>(E, s, nodes, s.cur, &ch, E.resp_policy + (size_t)mb * G::A, ws, false);
+        if (k < 0) { s.phase = BB_PH_ERROR; s.status = BB_ENOMEM; break; }
+        n_exp += 1;
+        n_nodes += k;
+        step = (E.search == BB_DYNAMIC || k == 0) ? ST_LEAF : ST_SELECT;
+      } else if (step == ST_SELECT) {
+        double u;
+        NodeHdr chosen = ch;
+        BB_ASSERT(ch.child_base + (uint32_t)meta_nchild(ch.meta) <= s.n_nodes);
+        const int j = puct_select<SelectChunks<G>::N, false>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
+        const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
+        if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
+        G::apply(s.cur_state, a);
+        s.cur = ch.child_base + (uint32_t)j;
+        ch = chosen;
+        if (lane == 0) nodes[s.cur].s.plays += 1;              // the visit, on the way down
+        __syncwarp();
+        s.last_action = a;
+        s.depth += 1;
+        path.set(s.depth, s.cur, meta_player(ch.meta));
+        n_sel += 1;
+        budget -= 1;
+        step = ST_TOP;
+      } else {                                                  // ST_LEAF
+        if (!(ch.meta & META_HAS_VALUE)) {
+          if (ch.meta & META_PENDING) { park = CTX_RETRY; break; }
+          if constexpr (EC) if (E.ecache) {
+            n_look += 1;
+            if (ecache_lookup(E, s.cur_state, ws, &cached_v)) { n_hit += 1; cached = true; }
+          }
+          park = CTX_WAIT_LEAF;
+          break;
+        }
+        backup<G, true>(s, nodes, path, ch.eval);
+        n_sims += 1;
+        s.ctx_busy -= 1;
+        park = CTX_IDLE;
+      }
+    }
+    if (s.phase == BB_PH_ERROR) break;
+    // ---- park the context; the next one's turn ---------------------------------------------------------------------------
+    if ((park == CTX_WAIT_EXPAND || park == CTX_WAIT_LEAF) && cached) {
+      if constexpr (EC) if (lane < G::A) E.resp_policy[(size_t)mb * G::A + lane] = ws.cpol[lane];
+      if (lane == 0) {
+        ch.meta |= META_PENDING;
+        nodes[s.cur].h = ch;
+        E.resp_value[mb] = cached_v;
+        E.resp_seq[mb] = 0xFFFFFFFFu;                          // "ticket" 0xFFFFFFFE: answered
+      }
+      s.req_idx = 0xFFFFFFFEu;
+      __syncwarp();
+    } else if (park == CTX_WAIT_EXPAND || park == CTX_WAIT_LEAF) {
+      int idx = 0;
+      if (lane == 0) {
+        ch.meta |= META_PENDING;
+        nodes[s.cur].h = ch;
+        E.q_state[mb] = s.cur_state;
+        idx = (int)atomicAdd(&E.q->tail, 1u);
+        volatile unsigned long long* ent = reinterpret_cast<volatile unsigned long long*>(&E.q_ent[(unsigned)idx & E.q_mask]);
+        unsigned long long was = *ent;
+        fence_acq_rel();
+        while ((unsigned)(was >> 32) & RING_PUBLISHED) { __nanosleep(100); was = *ent; }
+        *ent = ((unsigned long long)(mb | RING_PUBLISHED) << 32) | (unsigned)idx;
+      }
+      s.req_idx = (uint32_t)__shfl_sync(0xFFFFFFFFu, idx, 0);
+      n_evals += 1;
+    }
+    if (park != CTX_IDLE) {
+      path.store(prow);
+      if (lane == 0) { cx->cur_state = s.cur_state; cx->cur = s.cur; cx->depth = s.depth; cx->last_action = s.last_action; cx->req_idx = s.req_idx; }
+    }
+    if (lane == 0) cx->st = park;
+    __syncwarp();
+    s.ctx_cur = (c + 1u) % (uint32_t)W;
+    if (budget <= 0 && park == CTX_IDLE) break;                 // yield between simulations (keeps a pass over the warp's slots short)
+  }
+  if (ticket) *ticket = s.req_idx;
+  if (mailbox) *mailbox = (uint32_t)g * (uint32_t)W + s.ctx_cur;
+  (void)waiting;
+  if (lane == 0) {
+    E.slots[g] = s;
+    Counters* c = E.counters;
+    if (n_sims) atomicAdd(&c->sims, n_sims);
+    if (n_evals) atomicAdd(&c->evals, n_evals);
+    if (n_nodes) atomicAdd(&c->nodes, n_nodes);
+    if (n_exp) atomicAdd(&c->expansions, n_exp);
+    if (n_sel) atomicAdd(&c->select_steps, n_sel);
+    if (n_moves) atomicAdd(&c->moves, n_moves);
+    if (n_done) atomicAdd(&c->games_done, n_done);
+    if (n_look) atomicAdd(&c->cache_lookups, n_look);
+    if (n_hit) atomicAdd(&c->cache_hits, n_hit);
+  }
+  __syncwarp();
+  return s.phase;
+}
+
 // ---- streaming mode: persistent search kernel ------------------------------------------------------
 // Every warp owns the slots g = w, w + W, w + 2W ... (W = warps of the grid) for the whole launch and
 // round-robins over them: a slot whose answer has not arrived is skipped, every other busy slot is
@@ -412,11 +650,12 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
 constexpr int STREAM_MAX_OWN = 64;      // slots per warp (65536 slots on 148 SMs x 12 warps need 37)
 constexpr unsigned STREAM_WATCHDOG_SPINS = 4u << 20;   // idle polls (~0.5 us each) before a warp gives up
 
-template <class G>
+template <class G, bool VL = false>
 __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) {   // <= 128 registers: one CTA fits an SM NEXT TO the network CTA
   __shared__ WarpScratch s_ws[STREAM_WARPS_PER_CTA];
   __shared__ uint32_t s_ticket[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];
   __shared__ uint8_t s_state[STREAM_WARPS_PER_CTA][STREAM_MAX_OWN];   // 0 runnable, 1 waiting for an answer, 2 finished
+  __shared__ uint32_t s_mbox[VL ? STREAM_WARPS_PER_CTA : 1][VL ? STREAM_MAX_OWN : 1];   // virtual-loss mode: the mailbox (slot x contexts + context) the slot waits on
   const int wl = threadIdx.x >> 5, lane = lane_id();
   const int W = gridDim.x * STREAM_WARPS_PER_CTA;
   const int w = blockIdx.x * STREAM_WARPS_PER_CTA + wl;
@@ -427,6 +666,7 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
       // a slot left waiting by an earlier launch keeps its ticket (the answer is in flight or already there)
       s_state[wl][n_own] = (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) ? 1 : (phase_busy(ph) ? 0 : 2);
       s_ticket[wl][n_own] = E.slots[g].req_idx;
+      if (VL) s_mbox[wl][n_own] = (uint32_t)g * (uint32_t)E.vl + E.slots[g].ctx_cur;
     }
     ++n_own;
   }
@@ -445,20 +685,21 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
       if (st == 2) continue;
       const int g = w + j * W;
       if (st == 1) {
-        const unsigned have = *reinterpret_cast<volatile unsigned*>(&E.resp_seq[g]);
+        const unsigned have = *reinterpret_cast<volatile unsigned*>(&E.resp_seq[VL ? s_mbox[wl][j] : (uint32_t)g]);
         if (have != s_ticket[wl][j] + 1u) { any_busy = true; continue; }
         fence_acq_rel();                                     // acquire: the answer was written before its sequence number
       }
       uint32_t ticket = 0;
       const long long t0 = clock64();
-      const int ph = advance_slot(E, g, 0u, s_ws[wl], &ticket);
+      uint32_t mbox = 0;
+      const int ph = VL ? advance_slot_vl(E, g, s_ws[wl], &ticket, &mbox) : advance_slot(E, g, 0u, s_ws[wl], &ticket);
       t_busy += clock64() - t0;
       ++calls;
       progressed = true;
       int nst = 2;
       if (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) nst = 1;
       else if (phase_busy(ph)) nst = 0;
-      if (lane == 0) { s_state[wl][j] = (uint8_t)nst; s_ticket[wl][j] = ticket; }
+      if (lane == 0) { s_state[wl][j] = (uint8_t)nst; s_ticket[wl][j] = ticket; if (VL) s_mbox[wl][j] = mbox; }
       __syncwarp();
       any_busy |= nst != 2;
     }
@@ -474,7 +715,7 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
           int j0 = 0;
           while (j0 < n_own && s_state[wl][j0] != 1) ++j0;
           printf("[bbengine] streaming watchdog: warp %d waited too long (slot %d ticket %u, answer seq %u, head %u tail %u)\n", w,
-                 w + j0 * W, j0 < n_own ? s_ticket[wl][j0] : 0u, j0 < n_own ? E.resp_seq[w + j0 * W] : 0u, E.q->head, E.q->tail);
+                 w + j0 * W, j0 < n_own ? s_ticket[wl][j0] : 0u, j0 < n_own ? E.resp_seq[VL ? s_mbox[wl][j0] : (uint32_t)(w + j0 * W)] : 0u, E.q->head, E.q->tail);
           *stop = 2u;
         }
         break;
@@ -545,6 +786,8 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.cp_head = s.cp_n = s.cp_src = 0;
   s.row = (uint32_t)g;
   s.rng_pos = 0;
+  s.ctx_cur = s.ctx_busy = 0;
+  for (int c = 0; c < E.vl; ++c) E.ctx[(size_t)g * E.vl + c].st = CTX_IDLE;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;
   if (E.winners) E.winners[g] = WIN_NONE;
@@ -571,7 +814,7 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_begin_move(EngineDev<G> 
   if (!phase_busy(s.phase)) {
     Path path;
     begin_move(E, s, E.half(g, s.half), path, play_limit);
-    path.store(E.path + (size_t)g * PATH_LEN);
+    if (!E.vl) path.store(E.path + (size_t)g * PATH_LEN);    // (virtual-loss mode: path rows belong to contexts, which start their own descents)
   }
   if (lane_id() == 0) E.slots[g] = s;
 }

@@ -40,6 +40,7 @@ struct __align__(32) Node {
 };
 
 constexpr uint32_t META_HAS_VALUE = 1u << 23;
+constexpr uint32_t META_PENDING = 1u << 24;   // virtual-loss mode: an evaluation of this node's state is in flight (asked by another context)
 __host__ __device__ __forceinline__ uint32_t meta_pack(int action, int nchild, int player, bool has_value) {
   return (uint32_t)action | ((uint32_t)nchild << 12) | ((uint32_t)(player - 1) << 22) | (has_value ? META_HAS_VALUE : 0u);
 }
@@ -69,6 +70,20 @@ struct Slot {
   uint32_t cp_src;                // old id of the new root
   uint32_t row;                   // record / uniform row of the game this slot is playing (= slot id unless n_rows > n_games)
   uint32_t rng_pos;               // rollout evaluator: next unread word of the slot's MT19937 word stream
+  uint32_t ctx_cur, ctx_busy;     // virtual-loss mode: the context whose turn it is (strict cyclic order), contexts with a simulation in progress
+};
+
+// Virtual-loss mode (bb_config.contexts = W >= 1; DESIGN.md "x1"): W simulations of one game are in flight at a time.  A
+// context is the _findLeaf locals of one of them -- parked here while its evaluation is out; Slot.cur / cur_state /
+// depth / last_action / req_idx are the working copy of the context whose turn it is.
+enum { CTX_IDLE = 0, CTX_WAIT_EXPAND = 1, CTX_WAIT_LEAF = 2, CTX_RETRY = 3 };
+template <class G>
+struct Ctx {
+  typename G::State cur_state;
+  uint32_t cur;
+  int32_t depth, last_action;
+  uint32_t req_idx;
+  int32_t st;                     // CTX_*
 };
 
 // numpy pairwise-sum plan for a dense vector of length A, built on the host.
@@ -121,6 +136,8 @@ struct EngineDev {                // passed to kernels by value
   typename G::State* q_state;     // [n_games] the state a slot asks about (a slot has one open request at a time)
   unsigned* resp_seq;             // [n_games]
   unsigned q_mask;
+  Ctx<G>* ctx;                    // [n_games][vl] parked contexts (virtual-loss mode); mailboxes (q_state, resp_*, path rows) are indexed g * vl + context
+  int vl;                         // contexts per slot; 0 = exact mode (one simulation in flight per game, the reference's order)
   uint32_t* ecache;               // evaluation cache (common.cuh); nullptr = off
   uint32_t ecache_mask;
   // self-play

@@ -152,7 +152,9 @@ class Engine(object):
     """n_games concurrent searches / self-play games on one GPU."""
 
     def __init__(self, game, search='dynamic', n_games=1, max_depth=10, exploration_rate=0.85, evaluator='kat',
-                 node_cap=None, max_plies=None, play_limit_hint=100, device=0, lanes=0):
+                 node_cap=None, max_plies=None, play_limit_hint=100, device=0, lanes=0, contexts=0):
+        """contexts: 0 = exact mode (one simulation in flight per game: the reference's search, default); W >= 1 = virtual-loss
+        mode with W simulations of a game in flight (W = 1 reproduces the exact mode; W > 1 is a different, non-exact search)."""
         _need_cuda()
         self.game, self.search, self.n_games, self.device = game, search, int(n_games), device
         self.A = _ACTIONS[game]
@@ -168,6 +170,8 @@ class Engine(object):
         cfg.n_games, cfg.node_cap, cfg.max_plies, cfg.device = self.n_games, self.node_cap, self.max_plies, device
         cfg.exploration_rate = float(exploration_rate)
         cfg.lanes = int(lanes)
+        cfg.contexts = int(contexts)
+        self.contexts = int(contexts)
         self._h = C.c_void_p()
         check(lib.bb_engine_create(C.byref(cfg), C.byref(self._h)))
         self.evaluator = evaluator

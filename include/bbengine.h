@@ -84,7 +84,12 @@ typedef struct bb_config {
   int32_t value_f64;         /* 0: Node.Value accumulates in f32 (Model path, A.9); 1: f64       */
   int32_t lanes;             /* independent sub-populations of slots (own stream + mailbox each) whose ticks
                                 overlap on the GPU; 0 = choose (2 from 512 slots up).  Results do not depend on it. */
-  int32_t reserved[6];
+  int32_t contexts;          /* 0: exact mode -- one simulation in flight per game, the reference's order (default).
+                                W >= 1: virtual-loss mode -- W simulations of a game in flight, visits counted on the way down,
+                                values on the way up, contexts resumed in strict cyclic order (deterministic).  W = 1 gives the
+                                exact mode's results; W > 1 is NOT the reference's search (north_star (2), SURVEY.md 7.3-2:
+                                reported separately).  Needs BB_EVAL_NET with the streaming kernel pair (bf16, 16 filters). */
+  int32_t reserved[5];
 } bb_config;
 
 int bb_engine_create(const bb_config* cfg, bb_engine** out);
