@@ -57,6 +57,8 @@ def parse():
     ap.add_argument('--ref-seconds', type=float, default=150.0, help='--impl reference: total length of warm-up + timed windows')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
     ap.add_argument('--lanes', type=int, default=0, help='engine lanes (0 = engine default)')
+    ap.add_argument('--contexts', type=int, default=0, help='0 (default): exact mode, the reference\'s search. W >= 1: virtual-loss mode with W simulations of a '
+                    'game in flight -- NOT the reference\'s search for W > 1; the line says so in config.search_mode and is never the headline')
     ap.add_argument('--prelude', type=int, default=None, help='untimed move rounds at <= 32 sims/move that desynchronise the game slots')
     ap.add_argument('--e2e-rounds', type=int, default=4, help='e2e plays this many times --games whole games per GPU on the --games slots')
     ap.add_argument('--no-e2e', action='store_true')
@@ -84,6 +86,9 @@ def config_dict(args, n_gpus):
             'step': 'one move round: the %d slots together play %d moves (FindMove+MoveRoot each), no barrier between moves, finished games restart in place' % (args.games, args.games),
             'prelude': '%d untimed move rounds at %d sims/move to desynchronise the slots, then the warm-up steps' % (args.prelude, min(32, args.sims)),
             'epsilon': args.epsilon, 'alpha': 0.2,
+            'search_mode': ('exact: one simulation in flight per game, results identical to the reference\'s' if not getattr(args, 'contexts', 0) else
+                            'virtual loss, %d simulations in flight per game%s' % (args.contexts, ' (same results as exact)' if args.contexts == 1 else
+                                                                                   ' -- NON-EXACT: a different search from the reference\'s, reported separately')),
             'noise': ('policy noise ON as in parameters_template.yaml (every evaluation mixes Beta(alpha, 1-alpha) draws into the policy, NetworkFactory.py:176-182)'
                       if args.epsilon > 0 else 'policy noise off (the parity setting)'),
             'parallelism': 'games sharded over %d GPU(s), no data-path collective' % n_gpus,
@@ -297,7 +302,7 @@ def run_ours(args):
     from blackbird_b200.engine import n_actions, state_bytes
     A, S = n_actions(GAME), state_bytes(GAME)
     eng = Engine(GAME, SEARCH, n_games=G, max_depth=MAX_DEPTH, exploration_rate=C_PUCT, evaluator='net',
-                 play_limit_hint=P, device=local, lanes=args.lanes, max_plies=MAX_PLIES)
+                 play_limit_hint=P, device=local, lanes=args.lanes, max_plies=MAX_PLIES, contexts=args.contexts)
     weights = netinit.random_weights(cin, A, seed=0, **NET)
 
     def load_net(eps):
