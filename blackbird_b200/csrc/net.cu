@@ -615,6 +615,17 @@ static int net_launch_wide(NetDev* net, const void* states, int n, const int* co
     BB_CUDA(cudaGetLastError());
   }
   (void)sizeof(Tg);
+#ifdef BB_WIDE_TIMING
+  if (getenv("BB_DEBUG_WIDE") && net->use_tc) {
+    unsigned long long h[8];
+    cudaStreamSynchronize(stream);
+    cudaMemcpyFromSymbol(h, g_wide_dbg, sizeof h);
+    if (h[4]) fprintf(stderr, "[bbengine] k_wide_conv<%d> MMA warp per tile group: waits for tiles %.0f, for the accumulator %.0f, for weight stages %.0f of %.0f cycles (%llu groups)\n", F,
+                      (double)h[0] / h[4], (double)h[1] / h[4], (double)h[2] / h[4], (double)h[3] / h[4], h[4]);
+    unsigned long long z[8] = {0};
+    cudaMemcpyToSymbol(g_wide_dbg, z, sizeof z);
+  }
+#endif
   if (net->p.eps > 0.f) k_bump<<<1, 1, 0, stream>>>(net->p.call_counter);
   return BB_OK;
 }
@@ -716,7 +727,8 @@ static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, siz
   if ((rc = upload(pb, (size_t)A * 4, (const void**)&net->p.pol_b))) return rc;
   net->use_tc = tc;
   if (tc) {
-    // bf16 B operands: layer l, tap t, k-step ks: N = F rows x K = 16, element (n = cout, k) at byte (k / 8) * F * 16 + n * 16 + (k % 8) * 2
+    // bf16 B operands: layer l, k-step ks, tap t (k-step outer: net_wide.cuh streams the activations k-step by k-step): N = F rows x K = 16,
+    // element (n = cout, k) at byte (k / 8) * F * 16 + n * 16 + (k % 8) * 2
     auto bf16_rn = [](float f) -> uint16_t {
       uint32_t u;
       memcpy(&u, &f, 4);
@@ -737,7 +749,7 @@ static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, siz
             for (int o = 0; o < F; ++o) {
               const int ci = ks * 16 + k;
               const float v = ci < ci_n ? lw[((size_t)t * ci_n + ci) * F + o] : 0.f;
-              dst[((size_t)(t * ks_n + ks) * F * 32) / 2 + (size_t)(k / 8) * F * 8 + (size_t)o * 8 + (k % 8)] = bf16_rn(v);
+              dst[((size_t)(ks * 9 + t) * F * 32) / 2 + (size_t)(k / 8) * F * 8 + (size_t)o * 8 + (k % 8)] = bf16_rn(v);   // [k-step][tap][2][F][8]
             }
     }
     if ((rc = upload(wb.data(), wb.size() * 2, (const void**)&wd.wbf))) return rc;

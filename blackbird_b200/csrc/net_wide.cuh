@@ -11,15 +11,16 @@
 //                contiguous block: ONE cp.async.bulk brings it into shared memory, and the nine taps of the convolution
 //                are the same block read through descriptors whose start address is shifted by tap_offset x 16 bytes.
 //                Padding rows are zeroed once at allocation and never written.
-//   weights      w[layer][tap][k-step][2][F][8] bf16 (BN folded): a k-step (16 input channels) is an N = F, K = 16 operand
-//                of F x 32 bytes; k-steps of a tap are consecutive, so a ring stage is one bulk copy of <= 16 KB.
+//   weights      w[layer][k-step][tap][2][F][8] bf16 (BN folded): a (k-step, tap) is an N = F, K = 16 operand of F x 32 bytes;
+//                a ring stage is one bulk copy of three taps (F = 64, 6 KB) or one tap (F = 256, 8 KB).
 //   accumulator  128 rows x F fp32 columns of TMEM per tile; a CTA works on a GROUP of tiles at a time (4 at F = 64, 2 at
 //                F = 256) so that every weight stage is used by all tiles of the group before it is released.
-//   kernel       k_wide_conv<F>: warp 0 = TMA producer (group's tiles, then the layer's weight stages through the ring),
-//                warp 1 = MMA issuer (one elected lane; M128 N F K16, kind::f16), warps 2-5 = epilogue (tcgen05.ld, bias,
-//                skip from HBM, ReLU, bf16, 16-byte stores that are 512 contiguous bytes per warp).  At F = 64 tiles and
-//                accumulators are double-buffered (the epilogue of group g overlaps the MMAs of group g + 1); at F = 256
-//                one group fills both shared memory (160 KB of activations) and TMEM (512 columns).
+//   kernel       k_wide_conv<F>: warp 0 = TMA producer (k-step by k-step: the group's two planes per tile, then the k-step's
+//                weight stages through a 7-8 stage ring), warp 1 = MMA issuer (one elected lane; M128 N F K16, kind::f16, one
+//                asm block per (k-step, tap) covering the group's tiles), warps 2-5 = epilogue (tcgen05.ld, bias, skip rows
+//                prefetched from HBM into registers before the accumulator is waited for, ReLU, bf16, 16-byte stores that are
+//                512 contiguous bytes per warp).  At F = 64 accumulators are double-buffered (the epilogue of group g overlaps
+//                the MMAs of group g + 1); at F = 256 one group fills TMEM (512 columns).
 //   heads        k_wide_heads<G>: 1x1 head convolutions from the last activations, fixed-order sums, then heads_finish.
 //
 // The fp32 twin (precision 0) is plain SIMT over NHWC fp32 activations: it is the 1e-5 parity path, not a fast one.
@@ -39,35 +40,43 @@ inline WideGeo wide_geo() { return WideGeo{G::H, G::W, TcGeom<G>::LW, TcGeom<G>:
 
 template <int F>
 struct WideCfg {
-  static constexpr int TPG = F <= 64 ? 4 : (F <= 128 ? 2 : 2);      // tiles per group
-  static constexpr int NB = F <= 64 ? 2 : 1;                         // activation / accumulator buffers
+  static constexpr int TPG = F <= 64 ? 4 : 2;                        // tiles per group
+  static constexpr int NACC = F <= 64 ? 2 : 1;                       // accumulator sets (2: the epilogue of group g overlaps the MMAs of group g + 1)
   static constexpr int ACC_COLS = TPG * F;                           // TMEM columns of one accumulator set
-  static constexpr int TMEM_COLS = NB * ACC_COLS <= 256 ? 256 : 512;
-  static_assert(NB * ACC_COLS <= 512, "TMEM has 512 columns");
-  static constexpr int NST = F <= 64 ? 4 : 3;                        // weight-ring stages
-  static constexpr int STAGE = F <= 64 ? 8192 : 16384;               // bytes per weight-ring stage
-  static constexpr int KPS_MAX = STAGE / (F * 32);                   // k-steps per stage, at most
+  static constexpr int TMEM_COLS = NACC * ACC_COLS <= 256 ? 256 : 512;
+  static_assert(NACC * ACC_COLS <= 512, "TMEM has 512 columns");
+  static constexpr int KS_MAX = F / 16;                              // k-steps of a full-width layer
+  static constexpr int TPS = F <= 64 ? 3 : 1;                        // taps per weight-ring stage
+  static constexpr int STAGE = TPS * F * 32;                         // bytes per stage: 6 KB / 8 KB
+  static constexpr int NST = F <= 64 ? 8 : 7;                        // ring stages
   static constexpr int TILE_BYTES = (F / 8) * WIDE_PLANE;            // one tile of F-channel activations
   static constexpr int A_BYTES = TPG * TILE_BYTES;
   static constexpr int THREADS = 192;
-  // shared memory: [A buffers][ring][bias F floats][barriers]
-  static constexpr int OFF_RING = NB * A_BYTES;
+  // shared memory: [A tiles][ring][bias F floats][barriers]
+  static constexpr int OFF_RING = A_BYTES;
   static constexpr int OFF_BIAS = OFF_RING + NST * STAGE;
   static constexpr int OFF_BAR = OFF_BIAS + F * 4;
-  static constexpr int N_BAR = 4 * NB + 2 * NST;                     // a_full, a_free, d_full, d_free per buffer; w_full, w_free per stage
+  static constexpr int N_BAR = 2 * KS_MAX + 2 * NACC + 2 * NST;      // a_full / a_free per k-step; d_full / d_free per accumulator set; w_full / w_free per stage
   static constexpr int OFF_TMEM = OFF_BAR + N_BAR * 8;
   static constexpr int SMEM = OFF_TMEM + 16;
   static_assert(SMEM <= 227 * 1024, "shared memory");
 };
 
 struct WideLayer {
-  const uint8_t* in;       // input activations (tiles of `in_planes` planes)
+  const uint8_t* in;       // input activations (tiles of 2 * ksteps planes)
   uint8_t* out;            // output activations (tiles of F / 8 planes)
   const uint8_t* skip;     // block input to add before the ReLU (may alias out), or null
-  const uint8_t* w;        // this layer's weights
+  const uint8_t* w;        // this layer's weights [k-step][tap][2][F][8]
   const float* bias;       // [F]
   int ksteps;              // 16-channel steps of the input (stem: ceil(cin / 16); else F / 16)
 };
+
+#ifdef BB_WIDE_TIMING
+__device__ unsigned long long g_wide_dbg[8];   // MMA warp: cycles waiting for tiles, for the accumulator, for weight stages, total, groups
+#define WT(x) x
+#else
+#define WT(x)
+#endif
 
 // this warp's 32 TMEM lanes x 16 columns, no wait (the caller batches loads and waits once)
 __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
@@ -80,8 +89,58 @@ __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// One (k-step, tap) of a tile group in ONE asm block: the same weight operand against the A operand of up to four tiles
+// (descriptor low words differ by the tile stride, accumulators by F columns).  The issuing thread's instruction count
+// per MMA is what paces the tensor pipe when descriptors are rebuilt in C (~110 cycles per MMA measured; N = 64 needs 32).
+template <int F, int TPG>
+__device__ __forceinline__ void umma_group(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t a_step, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                           uint32_t accumulate, int nt) {
+  if (TPG == 4) {
+    asm volatile(
+        "{\n"
+        ".reg .pred pz, pe, p1, p2, p3;\n"
+        ".reg .b32 al, dd;\n"
+        ".reg .b64 ad, bd;\n"
+        "elect.sync _|pe, 0xFFFFFFFF;\n"
+        "setp.ne.u32 pz, %7, 0;\n"
+        "setp.gt.and.s32 p1, %8, 1, pe;\n"
+        "setp.gt.and.s32 p2, %8, 2, pe;\n"
+        "setp.gt.and.s32 p3, %8, 3, pe;\n"
+        "mov.b64 bd, {%4, %5};\n"
+        "mov.b64 ad, {%1, %2};\n"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %6, pz;\n"
+        "add.u32 al, %1, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, %0, %9;\n"
+        "@p1 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
+        "add.u32 al, al, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, dd, %9;\n"
+        "@p2 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
+        "add.u32 al, al, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, dd, %9;\n"
+        "@p3 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(F)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred pz, pe, p1;\n"
+        ".reg .b32 al, dd;\n"
+        ".reg .b64 ad, bd;\n"
+        "elect.sync _|pe, 0xFFFFFFFF;\n"
+        "setp.ne.u32 pz, %7, 0;\n"
+        "setp.gt.and.s32 p1, %8, 1, pe;\n"
+        "mov.b64 bd, {%4, %5};\n"
+        "mov.b64 ad, {%1, %2};\n"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %6, pz;\n"
+        "add.u32 al, %1, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, %0, %9;\n"
+        "@p1 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(F)
+        : "memory");
+  }
+}
+
 // One 3x3 convolution layer (+ folded BN, + skip, ReLU) over the live tiles of a chunk.  count_dev (may be null): device-
 // side number of positions of the WHOLE call; this chunk holds positions [chunk_base, chunk_base + n_chunk).
+// Loop order is k-step outer, tap inner: the two planes of a k-step are needed for its nine taps and then never again, so the
+// group's tiles STREAM through shared memory k-step by k-step (a_full / a_free per k-step: the next group's planes land as
+// soon as this group's MMAs on them have completed, and the first MMAs of a group start when its first 10 KB have arrived).
 template <int F>
 __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, int n_chunk, int chunk_base, const int* __restrict__ count_dev) {
   using C = WideCfg<F>;
@@ -90,8 +149,8 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
   uint8_t* sRing = wsm + C::OFF_RING;
   float* sBias = reinterpret_cast<float*>(wsm + C::OFF_BIAS);
   uint64_t* bars = reinterpret_cast<uint64_t*>(wsm + C::OFF_BAR);
-  uint64_t *a_full = bars, *a_free = bars + C::NB, *d_full = bars + 2 * C::NB, *d_free = bars + 3 * C::NB;
-  uint64_t *w_full = bars + 4 * C::NB, *w_free = w_full + C::NST;
+  uint64_t *a_full = bars, *a_free = bars + C::KS_MAX, *d_full = bars + 2 * C::KS_MAX, *d_free = d_full + C::NACC;
+  uint64_t *w_full = d_free + C::NACC, *w_free = w_full + C::NST;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wsm + C::OFF_TMEM);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -101,15 +160,14 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
   const int n_tiles = (cnt + geo.PPT - 1) / geo.PPT, n_groups = (n_tiles + C::TPG - 1) / C::TPG;
   if ((int)blockIdx.x >= n_groups) return;
 
-  const int ksteps = L.ksteps, kps = ksteps < C::KPS_MAX ? ksteps : C::KPS_MAX;   // k-steps per ring stage (divides ksteps: 1, 2 or F / 16)
-  const int n_stages = 9 * ksteps / kps;
-  const uint32_t stage_bytes = (uint32_t)kps * F * 32u;
-  const int in_planes = ksteps * 2;
-  const uint32_t in_tile_bytes = (uint32_t)in_planes * WIDE_PLANE;
+  const int ksteps = L.ksteps;
+  constexpr int SPK = 9 / C::TPS;                                    // weight stages per k-step
+  const uint32_t in_tile_bytes = (uint32_t)ksteps * 2u * WIDE_PLANE;
 
   if (warp == 1) {
     if (lane == 0) {
-      for (int b = 0; b < C::NB; ++b) { mbar_init(&a_full[b], 1); mbar_init(&a_free[b], 1); mbar_init(&d_full[b], 1); mbar_init(&d_free[b], 4); }
+      for (int k = 0; k < C::KS_MAX; ++k) { mbar_init(&a_full[k], 1); mbar_init(&a_free[k], 1); }
+      for (int b = 0; b < C::NACC; ++b) { mbar_init(&d_full[b], 1); mbar_init(&d_free[b], 4); }
       for (int s = 0; s < C::NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_free[s], 1); }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -124,23 +182,24 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ---- producer: the group's tiles, then the layer's weights through the ring ------------------------------------
+    // ---- producer: per k-step the group's two planes per tile, then the k-step's weight stages -------------------------
     if (lane == 0) {
       unsigned wseq = 0, it = 0;
       for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
-        const unsigned b = it % C::NB, use = it / C::NB;
-        mbar_wait(&a_free[b], (use & 1u) ^ 1u);                      // the MMAs that read this buffer have completed (passes at first use)
         const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&a_full[b])), "r"((uint32_t)nt * in_tile_bytes) : "memory");
-        for (int i = 0; i < nt; ++i)
-          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                           smem_u32(sA + b * C::A_BYTES + i * in_tile_bytes)),
-                       "l"(L.in + (size_t)(t0 + i) * in_tile_bytes), "r"(in_tile_bytes), "r"(smem_u32(&a_full[b]))
-                       : "memory");
-        for (int c = 0; c < n_stages; ++c, ++wseq) {
-          const unsigned s = wseq % C::NST;
-          mbar_wait(&w_free[s], ((wseq / C::NST) & 1u) ^ 1u);
-          bulk_g2s(sRing + s * C::STAGE, L.w + (size_t)c * stage_bytes, stage_bytes, &w_full[s]);
+        for (int ks = 0; ks < ksteps; ++ks) {
+          mbar_wait(&a_free[ks], (it & 1u) ^ 1u);                    // the previous group's MMAs on these planes have completed (passes at first use)
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&a_full[ks])), "r"((uint32_t)nt * 2u * WIDE_PLANE) : "memory");
+          for (int i = 0; i < nt; ++i)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             smem_u32(sA + i * in_tile_bytes + ks * 2 * WIDE_PLANE)),
+                         "l"(L.in + (size_t)(t0 + i) * in_tile_bytes + (size_t)ks * 2 * WIDE_PLANE), "r"(2u * WIDE_PLANE), "r"(smem_u32(&a_full[ks]))
+                         : "memory");
+          for (int c = 0; c < SPK; ++c, ++wseq) {
+            const unsigned s = wseq % C::NST;
+            mbar_wait(&w_free[s], ((wseq / C::NST) & 1u) ^ 1u);
+            bulk_g2s(sRing + s * C::STAGE, L.w + (size_t)(ks * SPK + c) * C::STAGE, C::STAGE, &w_full[s]);
+          }
         }
       }
     }
@@ -148,79 +207,98 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
     // ---- MMA issuer (warp-uniform control flow, one elected lane issues) -------------------------------------------
     constexpr uint32_t IDESC = umma_idesc_bf16(128, F);
     unsigned wseq = 0, it = 0;
+    WT(long long wa = 0; long long wd = 0; long long ww = 0; long long ngr = 0; const long long t_in = clock64();)
+    const uint64_t adesc0 = umma_desc(smem_u32(sA) + TC_MARGIN * 16, WIDE_PLANE, 128);
+    const uint32_t a_hi = (uint32_t)(adesc0 >> 32), a_lo0 = (uint32_t)adesc0, a_step = in_tile_bytes >> 4;
+    const uint64_t bdesc0 = umma_desc(smem_u32(sRing), F * 16, 128);
+    const uint32_t b_hi = (uint32_t)(bdesc0 >> 32), b_lo0 = (uint32_t)bdesc0;
     for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
-      const unsigned b = it % C::NB, use = it / C::NB;
+      const unsigned b = it % C::NACC, use = it / C::NACC;
       const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
-      mbar_wait(&a_full[b], use & 1u);
+      WT(const long long q1 = clock64();)
       mbar_wait(&d_free[b], (use & 1u) ^ 1u);                        // the epilogue has drained this accumulator set (passes at first use)
-      tc_fence_after();
-      const uint32_t a_addr = smem_u32(sA + b * C::A_BYTES) + TC_MARGIN * 16;
-      for (int c = 0; c < n_stages; ++c, ++wseq) {
-        const unsigned s = wseq % C::NST;
-        mbar_wait(&w_full[s], (wseq / C::NST) & 1u);
+      WT(wd += clock64() - q1; ngr += 1;)
+      const uint32_t dcol = tmem_base + b * C::ACC_COLS;
+      for (int ks = 0; ks < ksteps; ++ks) {
+        WT(const long long q0 = clock64();)
+        mbar_wait(&a_full[ks], it & 1u);
+        WT(wa += clock64() - q0;)
         tc_fence_after();
-        const int k0 = c * kps, tap = k0 / ksteps, ks0 = k0 % ksteps;
-        const int toff = (tap / 3 - 1) * geo.LW + (tap % 3 - 1);
-        const uint32_t b_addr = smem_u32(sRing + s * C::STAGE);
-        for (int kk = 0; kk < kps; ++kk) {
-          const uint64_t bdesc = umma_desc(b_addr + kk * F * 32, F * 16, 128);
-          for (int i = 0; i < nt; ++i) {
-            const uint64_t adesc = umma_desc(a_addr + i * in_tile_bytes + (ks0 + kk) * 2 * WIDE_PLANE + toff * 16, WIDE_PLANE, 128);
-            const uint32_t acc = (c | kk) ? 1u : 0u;
-            asm volatile(
-                "{\n"
-                ".reg .pred p, pe;\n"
-                "setp.ne.b32 p, %4, 0;\n"
-                "elect.sync _|pe, 0xFFFFFFFF;\n"
-                "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-                "}\n" ::"r"(tmem_base + b * C::ACC_COLS + i * F),
-                "l"(adesc), "l"(bdesc), "r"(IDESC), "r"(acc)
-                : "memory");
+        const uint32_t a_ks = a_lo0 + (uint32_t)(ks * 2 * (WIDE_PLANE >> 4));
+        for (int c = 0; c < SPK; ++c, ++wseq) {
+          const unsigned s = wseq % C::NST;
+          WT(const long long q2 = clock64();)
+          mbar_wait(&w_full[s], (wseq / C::NST) & 1u);
+          WT(ww += clock64() - q2;)
+          tc_fence_after();
+#pragma unroll
+          for (int tt = 0; tt < C::TPS; ++tt) {
+            const int tap = c * C::TPS + tt;
+            const int toff = (tap / 3 - 1) * geo.LW + (tap % 3 - 1);
+            umma_group<F, C::TPG>(dcol, a_ks + (uint32_t)toff, a_hi, a_step, b_lo0 + (uint32_t)((s * C::STAGE + tt * F * 32) >> 4), b_hi, IDESC,
+                                  (ks | tap) ? 1u : 0u, nt);
           }
+          umma_commit_elect(&w_free[s]);
         }
-        umma_commit_elect(&w_free[s]);
+        umma_commit_elect(&a_free[ks]);
       }
       umma_commit_elect(&d_full[b]);
-      umma_commit_elect(&a_free[b]);
     }
+    WT(if (lane == 0 && L.ksteps > 2) { atomicAdd(&g_wide_dbg[0], (unsigned long long)wa); atomicAdd(&g_wide_dbg[1], (unsigned long long)wd);
+         atomicAdd(&g_wide_dbg[2], (unsigned long long)ww); atomicAdd(&g_wide_dbg[3], (unsigned long long)(clock64() - t_in)); atomicAdd(&g_wide_dbg[4], (unsigned long long)ngr); })
   } else {
     // ---- epilogue: TMEM lane quarter q = warp % 4 ------------------------------------------------------------------
     const int q = warp & 3, rt = q * 32 + lane;
     const int pl = rt / geo.RPP, l = rt % geo.RPP, line = l / geo.LW, col = l % geo.LW;
     const bool cell = pl < geo.PPT && line >= 1 && col < geo.W;     // this row is a board cell (in every tile)
+    constexpr int NPL = F / 8;                                       // planes of an output tile
+    constexpr int SKR = NPL <= 8 ? NPL : 16;                         // skip planes held in registers ahead of their use
     unsigned it = 0;
     for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
-      const unsigned b = it % C::NB, use = it / C::NB;
+      const unsigned b = it % C::NACC, use = it / C::NACC;
       const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
+      // The skip rows do not depend on this layer's MMAs: the first ones are asked for BEFORE the wait for the accumulator, and
+      // every register that is consumed is refilled with the plane SKR further on (of this tile or the next), so the HBM / L2
+      // latency of the skip reads hides behind the tensor work instead of being paid once per 32 channels.
+      uint4 sk[SKR];
+      const size_t row_off = (size_t)(rt + TC_MARGIN) * 16;
+      const bool has_skip = L.skip != nullptr;
+      auto skip_ptr = [&](int lin) {                                 // lin = tile-in-group * NPL + plane
+        return L.skip + (size_t)(t0 + lin / NPL) * C::TILE_BYTES + (size_t)(lin % NPL) * WIDE_PLANE + row_off;
+      };
+      if (has_skip && cell) {
+#pragma unroll
+        for (int j = 0; j < SKR; ++j) sk[j] = __ldcg(reinterpret_cast<const uint4*>(skip_ptr(j)));
+      }
       mbar_wait(&d_full[b], use & 1u);
       tc_fence_after();
       for (int i = 0; i < nt; ++i) {
         const bool ok = cell && (t0 + i) * geo.PPT + pl < cnt;
-        const size_t tile_off = (size_t)(t0 + i) * C::TILE_BYTES + (size_t)(rt + TC_MARGIN) * 16;
-        uint8_t* orow = L.out + tile_off;
-        const uint8_t* srow = L.skip ? L.skip + tile_off : nullptr;
+        uint8_t* orow = L.out + (size_t)(t0 + i) * C::TILE_BYTES + row_off;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + b * C::ACC_COLS + i * F;
-#pragma unroll 1
+#pragma unroll
         for (int cb = 0; cb < F / 32; ++cb) {                        // 32 channels (four planes) per step: two loads in flight
           uint32_t r[32];
           tmem_ld16_nowait(taddr + cb * 32, r);
           tmem_ld16_nowait(taddr + cb * 32 + 16, r + 16);
           tmem_ld_wait();
-          if (ok) {
 #pragma unroll
-            for (int h = 0; h < 4; ++h) {                            // plane cb * 4 + h: channels cb * 32 + h * 8 ..
-              float v[8];
+          for (int h = 0; h < 4; ++h) {                              // plane cb * 4 + h: channels cb * 32 + h * 8 ..
+            const int plane = cb * 4 + h;
+            float v[8];
 #pragma unroll
-              for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[h * 8 + k]) + sBias[cb * 32 + h * 8 + k];
-              if (srow) {
-                const uint4 sk = *reinterpret_cast<const uint4*>(srow + (size_t)(cb * 4 + h) * WIDE_PLANE);
-                const uint32_t sw[4] = {sk.x, sk.y, sk.z, sk.w};
+            for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[h * 8 + k]) + sBias[cb * 32 + h * 8 + k];
+            if (has_skip && cell) {
+              const uint4 skv = sk[plane % SKR];
+              const uint32_t sw[4] = {skv.x, skv.y, skv.z, skv.w};
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16(sw[k]); v[2 * k] += f.x; v[2 * k + 1] += f.y; }
-              }
-              *reinterpret_cast<uint4*>(orow + (size_t)(cb * 4 + h) * WIDE_PLANE) =
-                  make_uint4(pack_relu_bf16(v[0], v[1]), pack_relu_bf16(v[2], v[3]), pack_relu_bf16(v[4], v[5]), pack_relu_bf16(v[6], v[7]));
+              for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16(sw[k]); v[2 * k] += f.x; v[2 * k + 1] += f.y; }
+              const int nxt = i * NPL + plane + SKR;                 // refill: SKR planes further on, possibly in the next tile of the group
+              if (nxt < nt * NPL) sk[plane % SKR] = __ldcg(reinterpret_cast<const uint4*>(skip_ptr(nxt)));
             }
+            if (ok)
+              *reinterpret_cast<uint4*>(orow + (size_t)plane * WIDE_PLANE) =
+                  make_uint4(pack_relu_bf16(v[0], v[1]), pack_relu_bf16(v[2], v[3]), pack_relu_bf16(v[4], v[5]), pack_relu_bf16(v[6], v[7]));
           }
         }
       }
