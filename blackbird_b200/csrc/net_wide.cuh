@@ -14,7 +14,8 @@
 //   weights      w[layer][k-step][tap][2][F][8] bf16 (BN folded): a (k-step, tap) is an N = F, K = 16 operand of F x 32 bytes;
 //                a ring stage is one bulk copy of three taps (F = 64, 6 KB) or one tap (F = 256, 8 KB).
 //   accumulator  128 rows x F fp32 columns of TMEM per tile; a CTA works on a GROUP of tiles at a time (4 at F = 64, 2 at
-//                F = 256) so that every weight stage is used by all tiles of the group before it is released.
+//                F = 256) so that every weight stage is used by all tiles of the group before it is released.  Only four
+//                k-steps of the group's activations are in shared memory at a time (a 40 / 80 KB ring); the rest is the weight ring.
 //   kernel       k_wide_conv<F>: warp 0 = TMA producer (k-step by k-step: the group's two planes per tile, then the k-step's
 //                weight stages through a 7-8 stage ring), warp 1 = MMA issuer (one elected lane; M128 N F K16, kind::f16, one
 //                asm block per (k-step, tap) covering the group's tiles), warps 2-5 = epilogue (tcgen05.ld, bias, skip rows
@@ -48,15 +49,17 @@ struct WideCfg {
   static constexpr int KS_MAX = F / 16;                              // k-steps of a full-width layer
   static constexpr int TPS = F <= 64 ? 3 : 1;                        // taps per weight-ring stage
   static constexpr int STAGE = TPS * F * 32;                         // bytes per stage: 6 KB / 8 KB
-  static constexpr int NST = F <= 64 ? 8 : 7;                        // ring stages
-  static constexpr int TILE_BYTES = (F / 8) * WIDE_PLANE;            // one tile of F-channel activations
-  static constexpr int A_BYTES = TPG * TILE_BYTES;
+  static constexpr int NST = F <= 64 ? 16 : 22;                      // weight-ring stages (96 KB / 176 KB: ~2.5 k-steps of latency cover at F = 256)
+  static constexpr int TILE_BYTES = (F / 8) * WIDE_PLANE;            // one tile of F-channel activations (in HBM)
+  static constexpr int NKA = 4;                                      // activation-ring slots: one k-step (two planes) of every tile of the group each
+  static constexpr int A_SLOT = TPG * 2 * WIDE_PLANE;                // bytes per slot: 20 KB / 10 KB
+  static constexpr int A_BYTES = NKA * A_SLOT;
   static constexpr int THREADS = 192;
   // shared memory: [A tiles][ring][bias F floats][barriers]
   static constexpr int OFF_RING = A_BYTES;
   static constexpr int OFF_BIAS = OFF_RING + NST * STAGE;
   static constexpr int OFF_BAR = OFF_BIAS + F * 4;
-  static constexpr int N_BAR = 2 * KS_MAX + 2 * NACC + 2 * NST;      // a_full / a_free per k-step; d_full / d_free per accumulator set; w_full / w_free per stage
+  static constexpr int N_BAR = 2 * NKA + 2 * NACC + 2 * NST;         // a_full / a_free per activation slot; d_full / d_free per accumulator set; w_full / w_free per stage
   static constexpr int OFF_TMEM = OFF_BAR + N_BAR * 8;
   static constexpr int SMEM = OFF_TMEM + 16;
   static_assert(SMEM <= 227 * 1024, "shared memory");
@@ -149,7 +152,7 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
   uint8_t* sRing = wsm + C::OFF_RING;
   float* sBias = reinterpret_cast<float*>(wsm + C::OFF_BIAS);
   uint64_t* bars = reinterpret_cast<uint64_t*>(wsm + C::OFF_BAR);
-  uint64_t *a_full = bars, *a_free = bars + C::KS_MAX, *d_full = bars + 2 * C::KS_MAX, *d_free = d_full + C::NACC;
+  uint64_t *a_full = bars, *a_free = bars + C::NKA, *d_full = bars + 2 * C::NKA, *d_free = d_full + C::NACC;
   uint64_t *w_full = d_free + C::NACC, *w_free = w_full + C::NST;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wsm + C::OFF_TMEM);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -166,7 +169,7 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
 
   if (warp == 1) {
     if (lane == 0) {
-      for (int k = 0; k < C::KS_MAX; ++k) { mbar_init(&a_full[k], 1); mbar_init(&a_free[k], 1); }
+      for (int k = 0; k < C::NKA; ++k) { mbar_init(&a_full[k], 1); mbar_init(&a_free[k], 1); }
       for (int b = 0; b < C::NACC; ++b) { mbar_init(&d_full[b], 1); mbar_init(&d_free[b], 4); }
       for (int s = 0; s < C::NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_free[s], 1); }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -184,16 +187,17 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
   if (warp == 0) {
     // ---- producer: per k-step the group's two planes per tile, then the k-step's weight stages -------------------------
     if (lane == 0) {
-      unsigned wseq = 0, it = 0;
-      for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
+      unsigned wseq = 0, aseq = 0;
+      for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
         const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
-        for (int ks = 0; ks < ksteps; ++ks) {
-          mbar_wait(&a_free[ks], (it & 1u) ^ 1u);                    // the previous group's MMAs on these planes have completed (passes at first use)
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&a_full[ks])), "r"((uint32_t)nt * 2u * WIDE_PLANE) : "memory");
+        for (int ks = 0; ks < ksteps; ++ks, ++aseq) {
+          const unsigned sl = aseq % C::NKA;
+          mbar_wait(&a_free[sl], ((aseq / C::NKA) & 1u) ^ 1u);       // the MMAs that read this slot last have completed (passes at first use)
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&a_full[sl])), "r"((uint32_t)nt * 2u * WIDE_PLANE) : "memory");
           for (int i = 0; i < nt; ++i)
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                             smem_u32(sA + i * in_tile_bytes + ks * 2 * WIDE_PLANE)),
-                         "l"(L.in + (size_t)(t0 + i) * in_tile_bytes + (size_t)ks * 2 * WIDE_PLANE), "r"(2u * WIDE_PLANE), "r"(smem_u32(&a_full[ks]))
+                             smem_u32(sA + sl * C::A_SLOT + i * 2 * WIDE_PLANE)),
+                         "l"(L.in + (size_t)(t0 + i) * in_tile_bytes + (size_t)ks * 2 * WIDE_PLANE), "r"(2u * WIDE_PLANE), "r"(smem_u32(&a_full[sl]))
                          : "memory");
           for (int c = 0; c < SPK; ++c, ++wseq) {
             const unsigned s = wseq % C::NST;
@@ -209,7 +213,8 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
     unsigned wseq = 0, it = 0;
     WT(long long wa = 0; long long wd = 0; long long ww = 0; long long ngr = 0; const long long t_in = clock64();)
     const uint64_t adesc0 = umma_desc(smem_u32(sA) + TC_MARGIN * 16, WIDE_PLANE, 128);
-    const uint32_t a_hi = (uint32_t)(adesc0 >> 32), a_lo0 = (uint32_t)adesc0, a_step = in_tile_bytes >> 4;
+    const uint32_t a_hi = (uint32_t)(adesc0 >> 32), a_lo0 = (uint32_t)adesc0, a_step = (2 * WIDE_PLANE) >> 4;
+    unsigned aseq = 0;
     const uint64_t bdesc0 = umma_desc(smem_u32(sRing), F * 16, 128);
     const uint32_t b_hi = (uint32_t)(bdesc0 >> 32), b_lo0 = (uint32_t)bdesc0;
     for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
@@ -219,12 +224,13 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
       mbar_wait(&d_free[b], (use & 1u) ^ 1u);                        // the epilogue has drained this accumulator set (passes at first use)
       WT(wd += clock64() - q1; ngr += 1;)
       const uint32_t dcol = tmem_base + b * C::ACC_COLS;
-      for (int ks = 0; ks < ksteps; ++ks) {
+      for (int ks = 0; ks < ksteps; ++ks, ++aseq) {
+        const unsigned sl = aseq % C::NKA;
         WT(const long long q0 = clock64();)
-        mbar_wait(&a_full[ks], it & 1u);
+        mbar_wait(&a_full[sl], (aseq / C::NKA) & 1u);
         WT(wa += clock64() - q0;)
         tc_fence_after();
-        const uint32_t a_ks = a_lo0 + (uint32_t)(ks * 2 * (WIDE_PLANE >> 4));
+        const uint32_t a_ks = a_lo0 + (uint32_t)((sl * C::A_SLOT) >> 4);
         for (int c = 0; c < SPK; ++c, ++wseq) {
           const unsigned s = wseq % C::NST;
           WT(const long long q2 = clock64();)
@@ -240,7 +246,7 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
           }
           umma_commit_elect(&w_free[s]);
         }
-        umma_commit_elect(&a_free[ks]);
+        umma_commit_elect(&a_free[sl]);
       }
       umma_commit_elect(&d_full[b]);
     }
