@@ -294,7 +294,8 @@ struct EngineT : bb_engine {
     A_(d.slots, n);
     A_(d.nodes, n * 2 * cap);
     A_(d.path, nw * PATH_LEN);
-    if (c.contexts > 0) A_(d.ctx, nw);
+    d.vl_hdr = nullptr;
+    if (c.contexts > 0) { A_(d.ctx, nw); A_(d.vl_hdr, n); }
     A_(ctl_dev, lanes.size());
     A_(d.req_slot, n);
     A_(d.req_state, n);
@@ -562,6 +563,7 @@ struct EngineT : bb_engine {
   }
   // Streaming mode is used whenever the evaluator is the built-in tensor-core network (BB_STREAM=0 falls back
   // to ticks).  Results are identical in both modes (tests/test_gpu_network.py).
+  bool stack_sized = false;         // run_stream has reserved the search kernel's local-memory frame
   int stream_fits = -1;             // the two persistent kernels must share an SM, or the search would spin on a network that never starts
   bool use_stream() {
     if (cfg.evaluator != BB_EVAL_NET || !net || !net_is_tc(net)) return false;
@@ -602,6 +604,17 @@ struct EngineT : bb_engine {
     if (const char* g = getenv("BB_STREAM_CTAS")) grid = atoi(g) > 0 ? atoi(g) : grid;     // tuning knob
     int div = sms;                                                                          // a claim takes open / div tickets (1 .. NP); div = pipelines serving
     if (const char* dv = getenv("BB_STREAM_DIV")) div = atoi(dv) > 0 ? atoi(dv) : div;
+    if (!stack_sized) {
+      // A launch whose per-thread local memory exceeds what the context has reserved makes the driver grow the reservation,
+      // which waits for every running kernel -- here the persistent network kernel, which in turn waits for the search kernel:
+      // the pair would sit until the watchdog.  Reserve the search kernel's frame while nothing runs.
+      cudaFuncAttributes fa{};
+      BB_CUDA(d.vl > 0 ? cudaFuncGetAttributes(&fa, k_search_stream<G, true>) : cudaFuncGetAttributes(&fa, k_search_stream<G>));
+      size_t cur = 0;
+      BB_CUDA(cudaDeviceGetLimit(&cur, cudaLimitStackSize));
+      if (fa.localSizeBytes > cur) BB_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, (fa.localSizeBytes + 255) & ~(size_t)255));
+      stack_sized = true;
+    }
     k_stream_arm<<<1, 1, 0, stream>>>(q_dev, (unsigned)grid, (unsigned)div, goal_moves);
     BB_CUDA(cudaGetLastError());
     BB_CUDA(cudaStreamSynchronize(stream));

@@ -421,6 +421,8 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
   const int W = E.vl;
   Slot<G> s = E.slots[g];
   if (!phase_busy(s.phase)) return s.phase;
+  uint32_t ctx_cur, ctx_busy;                                  // kept beside the slot (the exact mode's Slot record stays as it was)
+  { const uint2 h = E.vl_hdr[g]; ctx_cur = h.x; ctx_busy = h.y; }
   unsigned long long n_sims = 0, n_nodes = 0, n_exp = 0, n_sel = 0, n_moves = 0, n_done = 0, n_evals = 0, n_look = 0, n_hit = 0;
   constexpr bool EC = G::A <= ECACHE_MAX_ACTIONS;
   Path path;
@@ -440,7 +442,7 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
     }
     if (s.phase != BB_PH_RUN) break;
     // ---- the turn of context c ---------------------------------------------------------------------------------------
-    const uint32_t c = s.ctx_cur, mb = (uint32_t)g * (uint32_t)W + c;
+    const uint32_t c = ctx_cur, mb = (uint32_t)g * (uint32_t)W + c;
     Ctx<G>* cx = E.ctx + mb;
     uint32_t* prow = E.path + (size_t)mb * PATH_LEN;
     const int cst = cx->st;
@@ -470,9 +472,9 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
       BB_ASSERT(!(ch.meta & META_PENDING));
     } else {                                                      // idle: start the next simulation, if the move has any left
       if (s.root_plays >= s.end_plays) {
-        if (s.ctx_busy != 0) { s.ctx_cur = (c + 1u) % (uint32_t)W; continue; }
+        if (ctx_busy != 0) { ctx_cur = (c + 1u) % (uint32_t)W; continue; }
         // ---- every simulation of the move has come back: MCTS.py:298-299, then the self-play step as in the exact mode ----
-        s.ctx_cur = 0;
+        ctx_cur = 0;
         s.phase = BB_PH_MOVE_READY;
         if (!E.autoplay) break;
         BB_ASSERT(s.root < s.n_nodes);
@@ -522,7 +524,7 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
       start_descent(s, path);
       if (lane == 0) nodes[s.root].s.plays += 1;               // the visit, on the way down
       s.root_plays += 1;
-      s.ctx_busy += 1;
+      ctx_busy += 1;
       ch = nodes[s.root].h;
     }
     // ---- run the context until its simulation ends or it must wait -----------------------------------------------------
@@ -580,7 +582,7 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
         }
         backup<G, true>(s, nodes, path, ch.eval);
         n_sims += 1;
-        s.ctx_busy -= 1;
+        ctx_busy -= 1;
         park = CTX_IDLE;
       }
     }
@@ -618,14 +620,15 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
     }
     if (lane == 0) cx->st = park;
     __syncwarp();
-    s.ctx_cur = (c + 1u) % (uint32_t)W;
+    ctx_cur = (c + 1u) % (uint32_t)W;
     if (budget <= 0 && park == CTX_IDLE) break;                 // yield between simulations (keeps a pass over the warp's slots short)
   }
   if (ticket) *ticket = s.req_idx;
-  if (mailbox) *mailbox = (uint32_t)g * (uint32_t)W + s.ctx_cur;
+  if (mailbox) *mailbox = (uint32_t)g * (uint32_t)W + ctx_cur;
   (void)waiting;
   if (lane == 0) {
     E.slots[g] = s;
+    E.vl_hdr[g] = make_uint2(ctx_cur, ctx_busy);
     Counters* c = E.counters;
     if (n_sims) atomicAdd(&c->sims, n_sims);
     if (n_evals) atomicAdd(&c->evals, n_evals);
@@ -666,7 +669,7 @@ __global__ void __maxnreg__(BB_STREAM_MAXREG) k_search_stream(EngineDev<G> E) { 
       // a slot left waiting by an earlier launch keeps its ticket (the answer is in flight or already there)
       s_state[wl][n_own] = (ph == BB_PH_WAIT_EXPAND || ph == BB_PH_WAIT_LEAF) ? 1 : (phase_busy(ph) ? 0 : 2);
       s_ticket[wl][n_own] = E.slots[g].req_idx;
-      if (VL) s_mbox[wl][n_own] = (uint32_t)g * (uint32_t)E.vl + E.slots[g].ctx_cur;
+      if (VL) s_mbox[wl][n_own] = (uint32_t)g * (uint32_t)E.vl + E.vl_hdr[g].x;
     }
     ++n_own;
   }
@@ -786,7 +789,7 @@ __global__ void k_reset(EngineDev<G> E, const typename G::State* init) {
   s.cp_head = s.cp_n = s.cp_src = 0;
   s.row = (uint32_t)g;
   s.rng_pos = 0;
-  s.ctx_cur = s.ctx_busy = 0;
+  if (E.vl) E.vl_hdr[g] = make_uint2(0u, 0u);
   for (int c = 0; c < E.vl; ++c) E.ctx[(size_t)g * E.vl + c].st = CTX_IDLE;
   E.slots[g] = s;
   if (E.n_moves) E.n_moves[g] = 0;

@@ -70,7 +70,6 @@ struct Slot {
   uint32_t cp_src;                // old id of the new root
   uint32_t row;                   // record / uniform row of the game this slot is playing (= slot id unless n_rows > n_games)
   uint32_t rng_pos;               // rollout evaluator: next unread word of the slot's MT19937 word stream
-  uint32_t ctx_cur, ctx_busy;     // virtual-loss mode: the context whose turn it is (strict cyclic order), contexts with a simulation in progress
 };
 
 // Virtual-loss mode (bb_config.contexts = W >= 1; DESIGN.md "x1"): W simulations of one game are in flight at a time.  A
@@ -136,6 +135,7 @@ struct EngineDev {                // passed to kernels by value
   typename G::State* q_state;     // [n_games] the state a slot asks about (a slot has one open request at a time)
   unsigned* resp_seq;             // [n_games]
   unsigned q_mask;
+  uint2* vl_hdr;                  // [n_games] virtual-loss mode: x = the context whose turn it is (strict cyclic order), y = contexts with a simulation in progress
   Ctx<G>* ctx;                    // [n_games][vl] parked contexts (virtual-loss mode); mailboxes (q_state, resp_*, path rows) are indexed g * vl + context
   int vl;                         // contexts per slot; 0 = exact mode (one simulation in flight per game, the reference's order)
   uint32_t* ecache;               // evaluation cache (common.cuh); nullptr = off
