@@ -235,12 +235,10 @@ struct DragonChess {
 
   // legal targets (bit = row*8+col) of the piece on square `from`
   BB_HD static uint64_t legal_row(const State& s, int from) {
-    int r1 = from >> 3, c1 = from & 7;
-    int pc = at(s, r1, c1);
+    int pc = at(s, from >> 3, from & 7);
     if (pc == 0) return 0;
     bool white = is_white(pc);
     if (white != (player(s) == 1)) return 0;     // _sanity_check: wrong side to move
-    int kind = pc & 7;
     uint64_t own = 0, foe = 0;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -253,6 +251,37 @@ struct DragonChess {
         }
       }
     }
+    return legal_row_occ(s, from, own, foe);
+  }
+#ifdef __CUDACC__
+  // The same with the occupancy of the side to move (own) and of the other side (foe) worked out ONCE per position by the
+  // whole warp (lane l looks at squares l and l + 32, two ballots per colour) instead of by a 64-step loop in every call:
+  // an expansion asks for 64 rows, and the loop was most of its instructions.
+  static constexpr bool HAS_OCC = true;
+  __device__ static void occ_warp(const State& s, uint64_t* own, uint64_t* foe) {
+    const int l = threadIdx.x & 31;
+    const int v0 = at(s, l >> 3, l & 7), v1 = at(s, 4 + (l >> 3), l & 7);
+    const uint64_t wh = (uint64_t)__ballot_sync(0xFFFFFFFFu, is_white(v0)) | ((uint64_t)__ballot_sync(0xFFFFFFFFu, is_white(v1)) << 32);
+    const uint64_t bl = (uint64_t)__ballot_sync(0xFFFFFFFFu, is_black(v0)) | ((uint64_t)__ballot_sync(0xFFFFFFFFu, is_black(v1)) << 32);
+    const bool w = player(s) == 1;
+    *own = w ? wh : bl;
+    *foe = w ? bl : wh;
+  }
+  __device__ static int winner_warp(const State& s, int) {    // winner(): both kings looked for by the warp
+    const int l = threadIdx.x & 31;
+    const int v0 = at(s, l >> 3, l & 7), v1 = at(s, 4 + (l >> 3), l & 7);
+    const bool wk = __any_sync(0xFFFFFFFFu, v0 == K || v1 == K), bk = __any_sync(0xFFFFFFFFu, v0 == (BLACK | K) || v1 == (BLACK | K));
+    return !bk ? 1 : (!wk ? 2 : -1);
+  }
+#endif
+  // own / foe: occupancy of the colour of the piece on `from` / of the other colour; 0 when the piece is not the mover's
+  BB_HD static uint64_t legal_row_occ(const State& s, int from, uint64_t own, uint64_t foe) {
+    int r1 = from >> 3, c1 = from & 7;
+    int pc = at(s, r1, c1);
+    if (pc == 0) return 0;
+    bool white = is_white(pc);
+    if (white != (player(s) == 1)) return 0;     // _sanity_check: wrong side to move
+    int kind = pc & 7;
     uint64_t occ = own | foe, out = 0;
     if (kind == K || kind == N) {
       const int kd[8][2] = {{1, 0}, {1, 1}, {0, 1}, {-1, 1}, {-1, 0}, {-1, -1}, {0, -1}, {1, -1}};
@@ -306,6 +335,12 @@ struct DragonChess {
     if (a < 0 || a >= A) return false;            // ids >= 4032 (promotion/castle) are never legal
     int from = row_of(a), to = bit_of(a);
     if (!((legal_row(s, from) >> to) & 1ull)) return false;
+    apply_trusted(s, a);
+    return true;
+  }
+  // the move itself, for an action that is known to be legal (a child of the tree: it was generated from legal_row)
+  BB_HD static void apply_trusted(State& s, int a) {
+    int from = row_of(a), to = bit_of(a);
     int pc = at(s, from >> 3, from & 7);
     put(s, to >> 3, to & 7, pc);
     put(s, from >> 3, from & 7, 0);
@@ -317,7 +352,6 @@ struct DragonChess {
     if (at(s, 7, 4) != (BLACK | K)) f &= ~12u; else if (at(s, 7, 7) != (BLACK | R)) f &= ~4u;
     if (at(s, 7, 0) != (BLACK | R)) f &= ~8u;
     s.meta = f | ((uint32_t)(pl - 1) << 4) | ((uint32_t)pv << 5);
-    return true;
   }
 
   BB_HD static int winner(const State& s, int) {

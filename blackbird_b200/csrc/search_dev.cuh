@@ -126,6 +126,24 @@ __device__ __forceinline__ int puct_select(const Node* kids, int k, double c, do
   return bj;
 }
 
+// Rules calls of the descent, in their warp-cooperative / unchecked forms where a game has them (games.cuh: DragonChess).
+template <class G>
+__device__ __forceinline__ int winner_w(const typename G::State& s, int last) {
+  if constexpr (G::NROWS > 1) return G::winner_warp(s, last); else return G::winner(s, last);
+}
+template <class G>
+__device__ __forceinline__ void apply_child(typename G::State& s, int a) {      // a is the action of a tree child: legal by construction
+  if constexpr (G::NROWS > 1) G::apply_trusted(s, a); else G::apply(s, a);
+}
+template <class G>
+__device__ __forceinline__ void occ_w(const typename G::State& s, uint64_t* own, uint64_t* foe) {
+  if constexpr (G::NROWS > 1) G::occ_warp(s, own, foe); else { *own = 0; *foe = 0; }
+}
+template <class G>
+__device__ __forceinline__ uint64_t legal_row_w(const typename G::State& s, int row, uint64_t own, uint64_t foe) {
+  if constexpr (G::NROWS > 1) return G::legal_row_occ(s, row, own, foe); else return G::legal_row(s, row);
+}
+
 template <class G>
 struct SelectChunks { static constexpr int N = G::A <= 32 ? 1 : 4; };
 
@@ -251,10 +269,12 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     constexpr int RPL = (G::NROWS + 31) / 32;             // action rows per lane
     uint64_t m[RPL];
     int cnt = 0;
+    uint64_t own, foe;
+    occ_w<G>(s.cur_state, &own, &foe);                    // occupancy once per position, by the warp
 #pragma unroll
     for (int r = 0; r < RPL; ++r) {
       int row = lane * RPL + r;
-      m[r] = row < G::NROWS ? G::legal_row(s.cur_state, row) : 0ull;
+      m[r] = row < G::NROWS ? legal_row_w<G>(s.cur_state, row, own, foe) : 0ull;
       cnt += popc64(m[r]);
     }
     int incl = cnt;

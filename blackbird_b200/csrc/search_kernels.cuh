@@ -104,9 +104,9 @@ __device__ void play_move(const EngineDev<G>& E, Slot<G>& s, int g, Node* nodes,
   const int action = meta_action(nodes[child].h.meta);
   if (E.chosen && lane == 0) E.chosen[row * E.max_plies + s.ply] = (uint16_t)action;
   s.root_parent_player = G::player(s.root_state);
-  G::apply(s.root_state, action);
+  apply_child<G>(s.root_state, action);
   s.ply += 1;
-  const int w = G::winner(s.root_state, -1);                 // lastAction is always None (Blackbird.py:242,253)
+  const int w = winner_w<G>(s.root_state, -1);               // lastAction is always None (Blackbird.py:242,253)
   if (w != WIN_NONE || s.ply >= E.max_plies) {
     if (lane == 0) {
       if (E.rec_states) {
@@ -224,7 +224,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
     if (step == ST_TOP) {
       if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }     // FixedMCTS.py:23
       if (ch.child_base == NONE) {                              // Children is None
-        if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
+        if (winner_w<G>(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; } // :24-26
         if (RO) { step = ST_EXPAND; continue; }                 // AddChildren with GetPriors == ones: nothing to ask
         if constexpr (EC) if (E.ecache) {                       // the memo of GetPriors / SampleValue (Blackbird.py:350,372)
           float v;
@@ -271,7 +271,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
       // MCTS.py:341: the dense argmax lands on an illegal index when no legal U is positive
       if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
-      G::apply(s.cur_state, a);
+      apply_child<G>(s.cur_state, a);
       s.cur = ch.child_base + (uint32_t)j;
       ch = chosen;
       s.last_action = a;
@@ -533,7 +533,7 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
       if (step == ST_TOP) {
         if (E.search == BB_FIXED && s.depth == E.max_depth) { step = ST_LEAF; continue; }
         if (ch.child_base == NONE) {
-          if (G::winner(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; }
+          if (winner_w<G>(s.cur_state, s.last_action) != WIN_NONE) { step = ST_LEAF; continue; }
           if (ch.meta & META_PENDING) { park = CTX_RETRY; break; }
           // A memoised answer is taken exactly like a computed one -- the context parks, the node is pending, the answer sits in
           // the mailbox when the turn comes back -- so that WHEN another game's answer reached the cache cannot change the order
@@ -559,7 +559,7 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
         const int j = puct_select<SelectChunks<G>::N, false>(nodes + ch.child_base, meta_nchild(ch.meta), E.c, &u, &chosen);
         const int a = j == 0x7FFFFFFF ? 0 : meta_action(chosen.meta);
         if (j == 0x7FFFFFFF || (!(u > 0.0) && j < a)) { s.phase = BB_PH_ERROR; s.status = BB_EASSERT; break; }
-        G::apply(s.cur_state, a);
+        apply_child<G>(s.cur_state, a);
         s.cur = ch.child_base + (uint32_t)j;
         ch = chosen;
         if (lane == 0) nodes[s.cur].s.plays += 1;              // the visit, on the way down
