@@ -256,60 +256,82 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
       for (int d = 0; d < D; ++d) o = fmaf(fmaxf(fmaf(sv, d1w[d], (float)HW * d1b[d]), 0.f), d2w[d], o);
       value[out_idx ? out_idx[tid] : base + tid] = tanhf(o);
     }
-    for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
-      const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
-      float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
-      if (FAST && G::NROWS > 1 && co.legal_only && zbuf) {
+    if constexpr (FAST && G::NROWS > 1) {
+      if (co.legal_only && zbuf) {
         // The search only ever reads the policy at the LEGAL actions of the position it asked about (GetPriors:
         // getPolicy(state) * LegalActions() / sum, Blackbird.py:386-387), and the engine holds that position: generate
         // its legal moves here, evaluate the <= ~100 logits that matter instead of all 4032, soft-max over those, and
         // store them at their action index (the other entries of the row are left alone).  The normaliser cancels in
         // GetPriors' division, so the priors are the reference's up to fp32 rounding of two different partial sums --
-        // well inside the bf16 kernel's tolerance; the fp32 kernel keeps the dense head.  4032 x 3 passes and a 16 KB
-        // row write per position become one pass over the legal list (DragonChess: 96 k -> ~10 k cycles of heads per batch).
-        typename G::State st;
-        memcpy(&st, co.states + p * co.stride, sizeof(st));
-        int* list = reinterpret_cast<int*>(zbuf);                       // [0, CAP) action ids, then CAP logits, then scan scratch
-        constexpr int CAP = 512;
-        float* zl = zbuf + CAP;
-        int* scan = reinterpret_cast<int*>(zbuf + 2 * CAP);             // [NROWS + 1]
-        uint64_t m = 0;
-        if (tid < G::NROWS) { m = G::legal_row(st, tid); scan[tid + 1] = popc64(m); }
-        if (tid == 0) scan[0] = 0;
-        tm.sync();
-        if (tid == 0) for (int r = 0; r < G::NROWS; ++r) scan[r + 1] += scan[r];
-        tm.sync();
-        const int k = min(scan[G::NROWS], CAP);
-        if (tid < G::NROWS) {
-          int j = scan[tid];
-          while (m && j < CAP) { const int bit = ctz64(m); m &= m - 1; list[j++] = G::action_of(tid, bit); }
-        }
-        tm.sync();
-        float mx = -INFINITY;
-        for (int i = tid; i < k; i += nthreads) {
-          const int a = list[i];
-          const float z = fmaf(s0, __ldg(pol_w + a), fmaf(s1, __ldg(pol_w + G::A + a), (float)HW * __ldg(pol_b + a)));
-          zl[i] = z;
-          mx = fmaxf(mx, z);
-        }
-        mx = block_reduce(mx, red, true, tm);
-        float sum = 0.f;
-        for (int i = tid; i < k; i += nthreads) { const float e = __expf(zl[i] - mx); zl[i] = e; sum += e; }
-        sum = block_reduce(sum, red, false, tm);
-        if (np.eps > 0.f) {                                             // (1 - eps) softmax + eps noise, renormalised -- over the legal actions
-          float tot = 0.f;
-          for (int i = tid; i < k; i += nthreads) {
-            const float pa = (1.f - np.eps) * (zl[i] / sum) + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (nb + p) * G::A + list[i]);
-            zl[i] = pa;
-            tot += pa;
+        // well inside the bf16 kernel's tolerance; the fp32 kernel keeps the dense head.
+        // A WARP per position (the positions of a batch side by side): the occupancy by two ballots per
+        // colour, lane l lists the moves of squares 2l and 2l + 1 at its scan offset, then the <= 256 logits, their soft-max
+        // and the noise mix with xor-tree reductions -- no block barrier anywhere.  The block-wide form below took the
+        // positions one after the other with six named barriers each: 24 k cycles of a 49 k-cycle DragonChess batch.
+        const int wq = tid >> 5, lane = tid & 31, nw = nthreads >> 5;
+        constexpr int CAP = 256, QPL = CAP / 32;
+        int* list = reinterpret_cast<int*>(zbuf) + wq * CAP;           // (A floats of scratch: room for 15 warps)
+        for (int p = wq; p < P && base + p < n; p += nw) {
+          typename G::State st;
+          memcpy(&st, co.states + p * co.stride, sizeof(st));
+          uint64_t own, foe;
+          G::occ_warp(st, &own, &foe);
+          const uint64_t m0 = G::legal_row_occ(st, 2 * lane, own, foe), m1 = G::legal_row_occ(st, 2 * lane + 1, own, foe);
+          const int cnt = popc64(m0) + popc64(m1);
+          int incl = cnt;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
           }
-          sum = block_reduce(tot, red, false, tm);
+          const int k = min(__shfl_sync(0xFFFFFFFFu, incl, 31), CAP);
+          int j = incl - cnt;
+          for (uint64_t mm = m0; mm && j < CAP; mm &= mm - 1) list[j++] = G::action_of(2 * lane, ctz64(mm));
+          for (uint64_t mm = m1; mm && j < CAP; mm &= mm - 1) list[j++] = G::action_of(2 * lane + 1, ctz64(mm));
+          __syncwarp();
+          const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
+          float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
+          float z[QPL];
+          int act[QPL];
+          float mx = -INFINITY;
+#pragma unroll
+          for (int q = 0; q < QPL; ++q) {
+            const int i = q * 32 + lane;
+            act[q] = i < k ? list[i] : 0;
+            z[q] = i < k ? fmaf(s0, __ldg(pol_w + act[q]), fmaf(s1, __ldg(pol_w + G::A + act[q]), (float)HW * __ldg(pol_b + act[q]))) : -INFINITY;
+            mx = fmaxf(mx, z[q]);
+          }
+#pragma unroll
+          for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+          float sum = 0.f;
+#pragma unroll
+          for (int q = 0; q < QPL; ++q) { z[q] = q * 32 + lane < k ? __expf(z[q] - mx) : 0.f; sum += z[q]; }
+#pragma unroll
+          for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+          if (np.eps > 0.f) {                                           // (1 - eps) softmax + eps noise, renormalised -- over the legal actions
+            float tot = 0.f;
+#pragma unroll
+            for (int q = 0; q < QPL; ++q)
+              if (q * 32 + lane < k) {
+                z[q] = (1.f - np.eps) * (z[q] / sum) + np.eps * beta_noise(np.alpha, np.seed ^ (call * 0x632BE59BD9B4E019ull), (nb + p) * G::A + act[q]);
+                tot += z[q];
+              }
+#pragma unroll
+            for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+            sum = tot;
+          }
+          const float inv = 1.f / sum;
+#pragma unroll
+          for (int q = 0; q < QPL; ++q)
+            if (q * 32 + lane < k) out[act[q]] = z[q] * inv;
+          __syncwarp();                                                 // the list is rewritten by this warp's next position
         }
-        const float inv = 1.f / sum;
-        for (int i = tid; i < k; i += nthreads) out[list[i]] = zl[i] * inv;
-        tm.sync();                                                      // list / zl are rewritten by the next position
-        continue;
+        return;
       }
+    }
+    for (int p = 0; p < P && base + p < n; ++p) {      // block-wide over the 4032 actions
+      const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
+      float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
       // intermediate values live in shared memory when the caller has room for A floats (every thread touches
       // only its own actions, so no barrier beyond the reductions'); otherwise in the output row itself.
       // Same operations in the same order either way: the results are bit-identical.

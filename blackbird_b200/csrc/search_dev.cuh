@@ -163,6 +163,7 @@ __device__ double pairwise_sum_sparse(int k, Get get) {
   for (int L = 0; L < P.n_leaves; ++L) {
     const int lo = P.leaf_lo[L], n = P.leaf_n[L];
     const int nfull = n < 8 ? 0 : n - (n & 7);
+    if (!(j < k && a < lo + n)) { leaf_sum[L] = 0.0; continue; }   // no legal action in this leaf: a sum of zeros (most leaves of a 4032-wide row)
     double r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double res = 0.0;
     bool combined = false;
@@ -287,6 +288,52 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     if (base + (uint32_t)k > E.node_cap) return -1;
     const bool staged = !RO && k <= STAGE_MAX;
     int j = incl - cnt;
+    if (k <= STAGE_MAX) {
+      // Every lane lists the actions of its rows (ascending, at its scan offset), then the WARP creates the children: child i
+      // by lane i % 32, so the policy reads of an expansion are in flight together (the row-by-row loop below pays one L2
+      // round trip per move of the busiest lane -- a queen's 20-odd moves one after the other) and a node is written once,
+      // with its normalised prior.
+#pragma unroll
+      for (int r = 0; r < RPL; ++r) {
+        uint64_t mm = m[r];
+        const int row = lane * RPL + r;
+        while (mm) {
+          const int bit = ctz64(mm);
+          mm &= mm - 1;
+          ws.action[j++] = (uint16_t)G::action_of(row, bit);
+        }
+      }
+      __syncwarp();
+      constexpr int CPL = STAGE_MAX / 32;                   // children per lane
+      double pr[CPL];
+#pragma unroll
+      for (int q = 0; q < CPL; ++q) {
+        const int i = q * 32 + lane;
+        pr[q] = 0.0;
+        if (!RO && i < k) { pr[q] = (double)__ldcg(policy + ws.action[i]); ws.prior[i] = pr[q]; }
+      }
+      __syncwarp();
+      double sum = 1.0;
+      if (!RO) {
+        if (lane == 0) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
+        sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+      }
+#pragma unroll
+      for (int q = 0; q < CPL; ++q) {
+        const int i = q * 32 + lane;
+        if (i < k) {
+          Node n;
+          n.s.plays = 0u;
+          n.s.value = 0.f;
+          n.s.prior = RO ? 0.0 : __ddiv_rn(pr[q], sum);
+          n.h.parent = node;
+          n.h.child_base = NONE;
+          n.h.meta = meta_pack((int)ws.action[i], 0, child_player, false);
+          n.h.eval = 0.f;
+          nodes[base + i] = n;
+        }
+      }
+    } else {
 #pragma unroll
     for (int r = 0; r < RPL; ++r) {
       uint64_t mm = m[r];
@@ -304,21 +351,19 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
         n.h.meta = meta_pack(a, 0, child_player, false);
         n.h.eval = 0.f;
         nodes[base + j] = n;
-        if (staged) { ws.prior[j] = n.s.prior; ws.action[j] = (uint16_t)a; }
         ++j;
       }
     }
     __syncwarp();
     if (!RO) {
       double sum = 0.0;
-      if (lane == 0) {
-        if (staged) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
-        else sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = meta_action(nodes[base + q].h.meta); return nodes[base + q].s.prior; });
-      }
+      if (lane == 0)
+        sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = meta_action(nodes[base + q].h.meta); return nodes[base + q].s.prior; });
       sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
-      for (int i = lane; i < k; i += 32)
-        nodes[base + i].s.prior = __ddiv_rn(staged ? ws.prior[i] : nodes[base + i].s.prior, sum);
+      for (int i = lane; i < k; i += 32) nodes[base + i].s.prior = __ddiv_rn(nodes[base + i].s.prior, sum);
     }
+    }
+    (void)staged;
   }
   node_hdr->child_base = base;
   node_hdr->meta = (node_hdr->meta & ~(0x3FFu << 12)) | ((uint32_t)k << 12);
