@@ -26,6 +26,29 @@ static void plan_rec(PairwisePlan& P, int lo, int n) {        // numpy pairwise_
   P.ops[P.n_ops++] = -1;
 }
 
+static void plan_levels(PairwisePlan& P) {                   // the additions of P.ops grouped by height
+  int stack[32], sp = 0, n_int = 0;
+  int l[PW_MAX_LEAVES], r[PW_MAX_LEAVES], h[2 * PW_MAX_LEAVES] = {0};
+  for (int i = 0; i < P.n_ops; ++i) {
+    if (P.ops[i] >= 0) { stack[sp++] = P.ops[i]; continue; }
+    const int b = stack[--sp], a = stack[--sp], t = n_int++;
+    l[t] = a; r[t] = b;
+    h[P.n_leaves + t] = 1 + (h[a] > h[b] ? h[a] : h[b]);
+    stack[sp++] = P.n_leaves + t;
+  }
+  P.root = stack[0];
+  int hmax = 0;
+  for (int t = 0; t < n_int; ++t) hmax = h[P.n_leaves + t] > hmax ? h[P.n_leaves + t] : hmax;
+  P.n_levels = hmax;
+  int q = 0;
+  for (int lv = 1; lv <= hmax; ++lv) {
+    P.lvl_off[lv - 1] = (uint8_t)q;
+    for (int t = 0; t < n_int; ++t)
+      if (h[P.n_leaves + t] == lv) { P.add_dst[q] = (uint8_t)(P.n_leaves + t); P.add_l[q] = (uint8_t)l[t]; P.add_r[q] = (uint8_t)r[t]; ++q; }
+  }
+  P.lvl_off[hmax] = (uint8_t)q;
+}
+
 template <class G>
 __global__ void k_root_stats(EngineDev<G> E, int kmax, int32_t* n_children, int32_t* actions, uint32_t* plays,
                              float* child_value, double* child_prior, uint32_t* root_plays, double* root_value,
@@ -263,6 +286,7 @@ struct EngineT : bb_engine {
     stream = lanes[0].stream;
     PairwisePlan P{};
     plan_rec(P, 0, G::A);
+    plan_levels(P);
     BB_CUDA(cudaMemcpyToSymbol(c_plan, &P, sizeof P, sizeof(PairwisePlan) * G::ID));
     const size_t n = c.n_games, cap = c.node_cap;
     const size_t nw = n * (size_t)(c.contexts > 0 ? c.contexts : 1);   // evaluator mailboxes: one per slot, or per (slot, context) in virtual-loss mode
@@ -658,6 +682,9 @@ struct EngineT : bb_engine {
               (double)h.ndbg[1] / h.batches, (double)h.ndbg[2] / h.batches, (double)h.ndbg[3] / h.batches, (double)h.ndbg[7] / h.batches);
 #endif
 #ifdef BB_SEARCH_TIMING
+    if (getenv("BB_DEBUG_STREAM") && h.xdbg[4])
+      fprintf(stderr, "[bbengine] expand_node (wide games) per call: legal rows + scan %.0f, list + policy reads %.0f, prior sum %.0f, node writes %.0f cycles\n",
+              (double)h.xdbg[0] / h.xdbg[4], (double)h.xdbg[1] / h.xdbg[4], (double)h.xdbg[2] / h.xdbg[4], (double)h.xdbg[3] / h.xdbg[4]);
     if (getenv("BB_DEBUG_STREAM") && h.search_calls) {
       const char* nm[6] = {"load", "post_request", "expand", "select level", "backup", "other"};
       for (int i = 0; i < 6; ++i)

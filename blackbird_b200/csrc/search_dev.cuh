@@ -198,6 +198,65 @@ __device__ double pairwise_sum_sparse(int k, Get get) {
   return stack[0];
 }
 
+// The same sum by the whole warp, for the staged children of a wide game (ws.action / ws.prior, k <= STAGE_MAX): leaf L of
+// the plan belongs to lane L % 32, which walks the k pairs and adds the ones in its range in numpy's order (eight
+// interleaved accumulators over the leaf's multiple-of-eight head, their fixed tree, then the tail one by one); the leaf
+// sums are then combined level by level of the plan's tree (PairwisePlan::add_*), one addition per lane.  Same additions on the
+// same operands as pairwise_sum_sparse -- which, on one lane with its accumulators, leaf sums and stack in local memory, took 46 k
+// cycles of a 61 k-cycle DragonChess expansion.  Overwrites ws.prior (the caller keeps the numerators in registers).
+template <class G>
+__device__ double pairwise_sum_warp(int k, WarpScratch& ws) {
+  const PairwisePlan& P = c_plan[G::ID];
+  const int lane = lane_id();
+  double mine[2] = {0.0, 0.0};
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int L = lane + 32 * t;
+    if (L < P.n_leaves) {
+      const int lo = P.leaf_lo[L], n = P.leaf_n[L];
+      const int nfull = n < 8 ? 0 : n - (n & 7);
+      double r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0, tail = 0.0;
+      bool any = false, has_tail = false;
+      // pass 1: the head goes to accumulator i & 7; the tail elements are summed in order on top of the combined head below
+      for (int j = 0; j < k; ++j) {
+        const int i = (int)ws.action[j] - lo;
+        if (i < 0 || i >= n) continue;
+        any = true;
+        if (i < nfull) {
+          const double v = ws.prior[j];
+          const int c = i & 7;
+          r0 = c == 0 ? __dadd_rn(r0, v) : r0; r1 = c == 1 ? __dadd_rn(r1, v) : r1; r2 = c == 2 ? __dadd_rn(r2, v) : r2; r3 = c == 3 ? __dadd_rn(r3, v) : r3;
+          r4 = c == 4 ? __dadd_rn(r4, v) : r4; r5 = c == 5 ? __dadd_rn(r5, v) : r5; r6 = c == 6 ? __dadd_rn(r6, v) : r6; r7 = c == 7 ? __dadd_rn(r7, v) : r7;
+        } else {
+          has_tail = true;
+        }
+      }
+      if (any) {
+        double res = nfull ? __dadd_rn(__dadd_rn(__dadd_rn(r0, r1), __dadd_rn(r2, r3)), __dadd_rn(__dadd_rn(r4, r5), __dadd_rn(r6, r7))) : 0.0;
+        if (has_tail)
+          for (int j = 0; j < k; ++j) {
+            const int i = (int)ws.action[j] - lo;
+            if (i >= nfull && i < n) res = __dadd_rn(res, ws.prior[j]);
+          }
+        mine[t] = res;
+      }
+      (void)tail;
+    }
+  }
+  __syncwarp();                                               // every lane has read the numerators
+#pragma unroll
+  for (int t = 0; t < 2; ++t)
+    if (lane + 32 * t < P.n_leaves) ws.prior[lane + 32 * t] = mine[t];
+  __syncwarp();
+  for (int lv = 0; lv < P.n_levels; ++lv) {                   // the plan's additions, one tree level at a time (a + b is commutative: operand order is free)
+    for (int q = P.lvl_off[lv] + lane; q < P.lvl_off[lv + 1]; q += 32) ws.prior[P.add_dst[q]] = __dadd_rn(ws.prior[P.add_l[q]], ws.prior[P.add_r[q]]);
+    __syncwarp();
+  }
+  const double total = ws.prior[P.root];
+  __syncwarp();
+  return total;
+}
+
 // ---- evaluation cache lookup (common.cuh): true = hit, policy in ws.cpol[0..A), raw value in *value -----------------------
 template <class G>
 __device__ __forceinline__ bool ecache_lookup(const EngineDev<G>& E, const typename G::State& st, WarpScratch& ws, float* value) {
@@ -271,6 +330,9 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     uint64_t m[RPL];
     int cnt = 0;
     uint64_t own, foe;
+#ifdef BB_SEARCH_TIMING
+    long long xt0 = clock64(), xt1 = 0, xt2 = 0, xt3 = 0;
+#endif
     occ_w<G>(s.cur_state, &own, &foe);                    // occupancy once per position, by the warp
 #pragma unroll
     for (int r = 0; r < RPL; ++r) {
@@ -288,6 +350,9 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     if (base + (uint32_t)k > E.node_cap) return -1;
     const bool staged = !RO && k <= STAGE_MAX;
     int j = incl - cnt;
+#ifdef BB_SEARCH_TIMING
+    xt1 = clock64();
+#endif
     if (k <= STAGE_MAX) {
       // Every lane lists the actions of its rows (ascending, at its scan offset), then the WARP creates the children: child i
       // by lane i % 32, so the policy reads of an expansion are in flight together (the row-by-row loop below pays one L2
@@ -313,11 +378,16 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
         if (!RO && i < k) { pr[q] = (double)__ldcg(policy + ws.action[i]); ws.prior[i] = pr[q]; }
       }
       __syncwarp();
+#ifdef BB_SEARCH_TIMING
+      xt2 = clock64();
+#endif
       double sum = 1.0;
       if (!RO) {
-        if (lane == 0) sum = pairwise_sum_sparse<G>(k, [&](int q, int* act) { *act = ws.action[q]; return ws.prior[q]; });
-        sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+        sum = pairwise_sum_warp<G>(k, ws);
       }
+#ifdef BB_SEARCH_TIMING
+      xt3 = clock64();
+#endif
 #pragma unroll
       for (int q = 0; q < CPL; ++q) {
         const int i = q * 32 + lane;
@@ -364,6 +434,14 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     }
     }
     (void)staged;
+#ifdef BB_SEARCH_TIMING
+    if (lane == 0 && E.q && xt3) {
+      const long long xt4 = clock64();
+      atomicAdd(&E.q->xdbg[0], (unsigned long long)(xt1 - xt0)); atomicAdd(&E.q->xdbg[1], (unsigned long long)(xt2 - xt1));
+      atomicAdd(&E.q->xdbg[2], (unsigned long long)(xt3 - xt2)); atomicAdd(&E.q->xdbg[3], (unsigned long long)(xt4 - xt3));
+      atomicAdd(&E.q->xdbg[4], 1ull);
+    }
+#endif
   }
   node_hdr->child_base = base;
   node_hdr->meta = (node_hdr->meta & ~(0x3FFu << 12)) | ((uint32_t)k << 12);

@@ -92,6 +92,11 @@ struct PairwisePlan {
   int n_leaves, n_ops;
   int16_t leaf_lo[PW_MAX_LEAVES], leaf_n[PW_MAX_LEAVES];
   int8_t ops[PW_MAX_OPS];         // >=0: push leaf sum; -1: add the two top entries
+  // the same tree by levels (pairwise_sum_warp): value slots 0 .. n_leaves-1 are the leaf sums, slot n_leaves + t the t-th
+  // addition; additions sorted by height, lvl_off[h] .. lvl_off[h + 1] are the ones whose operands are ready after level h - 1
+  int n_levels, root;
+  uint8_t lvl_off[16];
+  uint8_t add_dst[PW_MAX_LEAVES], add_l[PW_MAX_LEAVES], add_r[PW_MAX_LEAVES];
 };
 
 struct Counters {                 // mirrors bb_counters
