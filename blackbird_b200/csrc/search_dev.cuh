@@ -310,9 +310,16 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     __syncwarp();
     double sum = 1.0;
     if (!RO) {
-      if (lane == 0)
-        sum = pairwise_sum_sparse<G>(k, [&](int j, int* act) { *act = ws.action[j]; return ws.prior[j]; });
-      sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+      if constexpr (G::A < 8) {
+        // fewer than eight actions: numpy's pairwise sum is its plain loop (res = 0.; res += a[i]), zeros at illegal
+        // indices are identities -- the k numerators in ascending action order, straight from their lanes' registers
+        sum = 0.0;
+        for (int j = 0; j < k; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, p, j));
+      } else {
+        if (lane == 0)
+          sum = pairwise_sum_sparse<G>(k, [&](int j, int* act) { *act = ws.action[j]; return ws.prior[j]; });
+        sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+      }
     }
     if (lane < k) {
       Node n;

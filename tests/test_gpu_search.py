@@ -232,3 +232,29 @@ def test_lanes_do_not_change_results(mods):
         outs.append((records.build_records(eng), c['sims'], c['evals'], c['nodes'], c['moves']))
         eng.close()
     assert outs[0] == outs[1]
+
+
+def test_stalemated_dragonchess_root_trips_the_reference_assert(mods):
+    """A root with no legal move and no winner (the reference never detects stalemate: DragonChess.py:161-167 only looks for
+    the kings): _selectAction's `assert root.LegalActions[choice] == 1` (MCTS.py:341) fails in the reference; here the slot
+    reports BB_EASSERT -> AssertionError.  White: king in the corner behind three pawns that cannot move (pawns on the last
+    two ranks have no move shapes); Black: a lone king far away."""
+    engine, _ = mods
+    from oracle import rules_np
+    s = GAMES['DragonChess']()
+    s.board[:] = 0
+    s.board[7, 7] = rules_np.K
+    s.board[6, 6] = s.board[6, 7] = s.board[7, 6] = rules_np.P
+    s.board[0, 0] = -rules_np.K
+    s.castle = [False, False, False, False]
+    assert s.Winner() is None and int(s.LegalActions().sum()) == 0
+    cells = s.board.astype(np.int8).ravel()[None, :]
+    dev = engine.pack('DragonChess', cells, [1], [0], [0])
+    assert int(engine.legal('DragonChess', dev).sum()) == 0
+    for kind in ('fixed', 'dynamic'):
+        eng = engine.Engine('DragonChess', kind, n_games=1, evaluator='kat', max_plies=8, node_cap=4096)
+        eng.reset(dev)
+        with pytest.raises(AssertionError):
+            eng.step(1, 8, 1.0, np.full((1, eng.max_plies), 0.5))
+            eng.check_status()
+        eng.close()
