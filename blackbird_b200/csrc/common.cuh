@@ -61,6 +61,9 @@ struct StreamCtl {
   unsigned long long sdbg[12];
   unsigned long long xdbg[8];     // expand_node: legal rows + scan, list + policy reads, prior sum, node writes; calls
 #endif
+#ifdef BB_NET_TIMING_HEADS
+  unsigned long long hdbg[8];     // legal-only policy head (heads_finish): phase cycles, positions
+#endif
 #if defined(BB_NET_TIMING_TOWER) || defined(BB_NET_TIMING_HEADS)
   unsigned long long ndbg[8];     // MMA warp: cycles waiting for `ready`, issuing; epilogue warp 0: waiting for `full`, working; staging; tile-layers
 #endif

@@ -283,15 +283,17 @@ struct DragonChess {
     if (white != (player(s) == 1)) return 0;     // _sanity_check: wrong side to move
     int kind = pc & 7;
     uint64_t occ = own | foe, out = 0;
-    if (kind == K || kind == N) {
-      const int kd[8][2] = {{1, 0}, {1, 1}, {0, 1}, {-1, 1}, {-1, 0}, {-1, -1}, {0, -1}, {1, -1}};
-      const int nd[8][2] = {{1, 2}, {2, 1}, {2, -1}, {1, -2}, {-1, -2}, {-2, -1}, {-2, 1}, {-1, 2}};
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        int r = r1 + (kind == K ? kd[i][0] : nd[i][0]), c = c1 + (kind == K ? kd[i][1] : nd[i][1]);
-        if (r >= 0 && r < 8 && c >= 0 && c < 8) out |= 1ull << (r * 8 + c);
-      }
+    const uint64_t bit = 1ull << from;
+    constexpr uint64_t FA = 0x0101010101010101ull, FH = 0x8080808080808080ull;    // columns 0 and 7
+    if (kind == K) {
+      // one step in the eight directions: shifts of the piece's bit, wraps across the board edge masked at the destination
+      out = (bit << 8) | (bit >> 8) | (((bit << 1) | (bit << 9) | (bit >> 7)) & ~FA) | (((bit >> 1) | (bit << 7) | (bit >> 9)) & ~FH);
       return out & ~own;                          // castling shapes are never legal (A.19)
+    }
+    if (kind == N) {
+      out = (((bit << 17) | (bit >> 15)) & ~FA) | (((bit << 15) | (bit >> 17)) & ~FH) | (((bit << 10) | (bit >> 6)) & ~(FA | (FA << 1))) |
+            (((bit << 6) | (bit >> 10)) & ~(FH | (FH >> 1)));
+      return out & ~own;
     }
     if (kind == P) {
       int fwd = white ? 1 : -1, home = white ? 1 : 6, last = white ? 6 : 1;
@@ -311,21 +313,35 @@ struct DragonChess {
       if (c1 < 7 && ((foe >> (r2 * 8 + c1 + 1)) & 1)) out |= 1ull << (r2 * 8 + c1 + 1);
       return out;
     }
-    // sliders: walk each ray to the first blocker; capture it if it is a foe
-    const int rd[8][2] = {{1, 0}, {-1, 0}, {0, 1}, {0, -1}, {1, 1}, {1, -1}, {-1, 1}, {-1, -1}};
-    int lo = (kind == B) ? 4 : 0, hi = (kind == R) ? 4 : 8;
-    for (int i = lo; i < hi; ++i) {
-      int r = r1 + rd[i][0], c = c1 + rd[i][1];
-      while (r >= 0 && r < 8 && c >= 0 && c < 8) {
-        uint64_t bit = 1ull << (r * 8 + c);
-        if (own & bit) break;
-        out |= bit;
-        if (foe & bit) break;
-        r += rd[i][0];
-        c += rd[i][1];
-      }
-    }
-    return out;
+    // sliders: along each ray up to and including the first blocker, then without the own pieces -- as occluded fills
+    // (Kogge-Stone, three doubling steps per direction: no loop over squares, no branch per step)
+    const uint64_t empty = ~occ;
+    const uint64_t gr = kind != B ? bit : 0ull, gb = kind != R ? bit : 0ull;      // rook-wise / bishop-wise movers
+    out = ray_up<8>(gr, empty, ~0ull) | ray_down<8>(gr, empty, ~0ull) | ray_up<1>(gr, empty, ~FA) | ray_down<1>(gr, empty, ~FH) |
+          ray_up<9>(gb, empty, ~FA) | ray_up<7>(gb, empty, ~FH) | ray_down<7>(gb, empty, ~FA) | ray_down<9>(gb, empty, ~FH);
+    return out & ~own;
+  }
+  // squares attacked from `gen` along one direction (shift by S towards higher / lower bits), stopping at the first non-empty
+  // square (included); m = squares a step may land on (the column a wrap would land on is excluded)
+  template <int S>
+  BB_HD static uint64_t ray_up(uint64_t gen, uint64_t pro, uint64_t m) {
+    pro &= m;
+    gen |= pro & (gen << S);
+    pro &= pro << S;
+    gen |= pro & (gen << (2 * S));
+    pro &= pro << (2 * S);
+    gen |= pro & (gen << (4 * S));
+    return (gen << S) & m;
+  }
+  template <int S>
+  BB_HD static uint64_t ray_down(uint64_t gen, uint64_t pro, uint64_t m) {
+    pro &= m;
+    gen |= pro & (gen >> S);
+    pro &= pro >> S;
+    gen |= pro & (gen >> (2 * S));
+    pro &= pro >> (2 * S);
+    gen |= pro & (gen >> (4 * S));
+    return (gen >> S) & m;
   }
   BB_HD static int action_of(int from, int to) { return from * 63 + to - (to > from ? 1 : 0); }
   BB_HD static int row_of(int a) { return a / 63; }

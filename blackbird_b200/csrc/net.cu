@@ -177,6 +177,9 @@ struct CacheOut {
   const uint8_t* states = nullptr;        // the batch's staged packed states
   int stride = 0, state_bytes = 0;
   int legal_only = 0;                     // wide heads: softmax over the LEGAL actions of the staged state only (see heads_finish)
+#ifdef BB_NET_TIMING_HEADS
+  unsigned long long* dbg = nullptr;      // legal-only head: cycles in moves + list, logits, soft-max + noise, stores; positions
+#endif
 };
 
 template <class G, bool FAST = false>
@@ -272,6 +275,9 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
         constexpr int CAP = 256, QPL = CAP / 32;
         int* list = reinterpret_cast<int*>(zbuf) + wq * CAP;           // (A floats of scratch: room for 15 warps)
         for (int p = wq; p < P && base + p < n; p += nw) {
+#ifdef BB_NET_TIMING_HEADS
+          const long long h0 = clock64();
+#endif
           typename G::State st;
           memcpy(&st, co.states + p * co.stride, sizeof(st));
           uint64_t own, foe;
@@ -289,6 +295,9 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
           for (uint64_t mm = m0; mm && j < CAP; mm &= mm - 1) list[j++] = G::action_of(2 * lane, ctz64(mm));
           for (uint64_t mm = m1; mm && j < CAP; mm &= mm - 1) list[j++] = G::action_of(2 * lane + 1, ctz64(mm));
           __syncwarp();
+#ifdef BB_NET_TIMING_HEADS
+          const long long h1 = clock64();
+#endif
           const float s0 = hsum[p * 4 + 1], s1 = hsum[p * 4 + 2];
           float* out = policy + (out_idx ? (size_t)out_idx[p] : (size_t)(base + p)) * G::A;
           float z[QPL];
@@ -303,6 +312,9 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
           }
 #pragma unroll
           for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+#ifdef BB_NET_TIMING_HEADS
+          const long long h2 = clock64();
+#endif
           float sum = 0.f;
 #pragma unroll
           for (int q = 0; q < QPL; ++q) { z[q] = q * 32 + lane < k ? __expf(z[q] - mx) : 0.f; sum += z[q]; }
@@ -321,10 +333,20 @@ __device__ void heads_finish(const NetParams& np, const float* hd, const float* 
             sum = tot;
           }
           const float inv = 1.f / sum;
+#ifdef BB_NET_TIMING_HEADS
+          const long long h3 = clock64();
+#endif
 #pragma unroll
           for (int q = 0; q < QPL; ++q)
             if (q * 32 + lane < k) out[act[q]] = z[q] * inv;
           __syncwarp();                                                 // the list is rewritten by this warp's next position
+#ifdef BB_NET_TIMING_HEADS
+          if (co.dbg && lane == 0) {
+            const long long h4 = clock64();
+            atomicAdd(co.dbg + 0, (unsigned long long)(h1 - h0)); atomicAdd(co.dbg + 1, (unsigned long long)(h2 - h1));
+            atomicAdd(co.dbg + 2, (unsigned long long)(h3 - h2)); atomicAdd(co.dbg + 3, (unsigned long long)(h4 - h3)); atomicAdd(co.dbg + 4, 1ull);
+          }
+#endif
         }
         return;
       }

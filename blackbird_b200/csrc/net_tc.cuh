@@ -828,6 +828,9 @@ k_net_forward_tc(NetParams np, TcParams tp, const typename G::State* __restrict_
       co.states = sState; co.stride = ST_STRIDE; co.state_bytes = (int)sizeof(State);
       co.legal_only = sv.legal_only;
       if (G::A <= ECACHE_MAX_ACTIONS && serve && sv.ecache) { co.base = sv.ecache; co.ent = sEnt; }
+#ifdef BB_NET_TIMING_HEADS
+      if (serve) co.dbg = sv.q->hdbg;
+#endif
       heads_finish<G, true>(np, sHead, pw, pb, hsum, red, serve ? (int)(ticket0 & 0x3FFFFFFFu) : base, n, cnt, call, policy, value, team, serve ? sIdx : nullptr,
                       reinterpret_cast<float*>(pb_ + L.zb), serve ? (long long)ticket0 : -1ll, co);
     }

@@ -677,6 +677,9 @@ struct EngineT : bb_engine {
               (double)h.ndbg[6] / h.ndbg[5], ((double)h.ndbg[3] - h.ndbg[4] - h.ndbg[6]) / h.ndbg[5]);
 #endif
 #ifdef BB_NET_TIMING_HEADS
+    if (getenv("BB_DEBUG_STREAM") && h.hdbg[4])
+      fprintf(stderr, "[bbengine] legal-only policy head per position: moves + list %.0f, logits %.0f, soft-max + noise %.0f, stores %.0f cycles\n",
+              (double)h.hdbg[0] / h.hdbg[4], (double)h.hdbg[1] / h.hdbg[4], (double)h.hdbg[2] / h.hdbg[4], (double)h.hdbg[3] / h.hdbg[4]);
     if (getenv("BB_DEBUG_STREAM") && h.batches)
       fprintf(stderr, "[bbengine] heads phase per batch: sums + sync %.0f, heads_finish %.0f, fence %.0f, sync %.0f, publish + last sync %.0f\n", (double)h.ndbg[0] / h.batches,
               (double)h.ndbg[1] / h.batches, (double)h.ndbg[2] / h.batches, (double)h.ndbg[3] / h.batches, (double)h.ndbg[7] / h.batches);
