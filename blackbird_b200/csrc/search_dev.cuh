@@ -215,7 +215,7 @@ __device__ double pairwise_sum_warp(int k, WarpScratch& ws) {
     if (L < P.n_leaves) {
       const int lo = P.leaf_lo[L], n = P.leaf_n[L];
       const int nfull = n < 8 ? 0 : n - (n & 7);
-      double r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0, tail = 0.0;
+      double r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
       bool any = false, has_tail = false;
       // pass 1: the head goes to accumulator i & 7; the tail elements are summed in order on top of the combined head below
       for (int j = 0; j < k; ++j) {
@@ -240,7 +240,6 @@ __device__ double pairwise_sum_warp(int k, WarpScratch& ws) {
           }
         mine[t] = res;
       }
-      (void)tail;
     }
   }
   __syncwarp();                                               // every lane has read the numerators
@@ -355,7 +354,6 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
     }
     k = __shfl_sync(0xFFFFFFFFu, incl, 31);
     if (base + (uint32_t)k > E.node_cap) return -1;
-    const bool staged = !RO && k <= STAGE_MAX;
     int j = incl - cnt;
 #ifdef BB_SEARCH_TIMING
     xt1 = clock64();
@@ -440,7 +438,6 @@ __device__ int expand_node(const EngineDev<G>& E, Slot<G>& s, Node* nodes, uint3
       for (int i = lane; i < k; i += 32) nodes[base + i].s.prior = __ddiv_rn(nodes[base + i].s.prior, sum);
     }
     }
-    (void)staged;
 #ifdef BB_SEARCH_TIMING
     if (lane == 0 && E.q && xt3) {
       const long long xt4 = clock64();

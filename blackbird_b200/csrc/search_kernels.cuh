@@ -431,7 +431,6 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
   ch.parent = NONE; ch.child_base = NONE; ch.meta = 0; ch.eval = 0.f;
   if (s.phase == BB_PH_WAIT_EXPAND || s.phase == BB_PH_WAIT_LEAF) s.phase = BB_PH_RUN;   // "the context whose turn it is waits": the caller has seen its answer
   int budget = E.step_budget * (W > 4 ? 4 : W);
-  bool waiting = false;
   for (;;) {
     if (s.phase == BB_PH_COMPACT) {
       budget -= 2 * E.compact_rounds;
@@ -454,7 +453,6 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
       if (*reinterpret_cast<volatile unsigned*>(&E.resp_seq[mb]) != tk + 1u) {       // not answered yet: the slot waits for THIS context
         s.req_idx = tk;
         s.phase = BB_PH_WAIT_LEAF;
-        waiting = true;
         break;
       }
       fence_acq_rel();
@@ -625,7 +623,6 @@ __device__ int advance_slot_vl(const EngineDev<G>& E, int g, WarpScratch& ws, ui
   }
   if (ticket) *ticket = s.req_idx;
   if (mailbox) *mailbox = (uint32_t)g * (uint32_t)W + ctx_cur;
-  (void)waiting;
   if (lane == 0) {
     E.slots[g] = s;
     E.vl_hdr[g] = make_uint2(ctx_cur, ctx_busy);
