@@ -57,6 +57,8 @@ def parse():
     ap.add_argument('--ref-seconds', type=float, default=150.0, help='--impl reference: total length of warm-up + timed windows')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'], help='network kernel: bf16 tcgen05 or fp32 SIMT')
     ap.add_argument('--lanes', type=int, default=0, help='engine lanes (0 = engine default)')
+    ap.add_argument('--filters', type=int, default=16, choices=[16, 64, 256], help='tower width (default: the template\'s 16; 64 / 256 run the layer-by-layer '
+                    'tensor-core kernels of net_wide.cuh behind a tick-mode search: SURVEY.md 8d row 5a)')
     ap.add_argument('--contexts', type=int, default=0, help='0 (default): exact mode, the reference\'s search. W >= 1: virtual-loss mode with W simulations of a '
                     'game in flight -- NOT the reference\'s search for W > 1; the line says so in config.search_mode and is never the headline')
     ap.add_argument('--prelude', type=int, default=None, help='untimed move rounds at <= 32 sims/move that desynchronise the game slots')
@@ -66,6 +68,7 @@ def parse():
     ap.add_argument('--no-e2e-records', action='store_true')
     args = ap.parse_args()
     global GAME, SEARCH, METRIC, MAX_PLIES, LABEL
+    NET['filters'] = args.filters
     c = CONFIGS[args.config]
     GAME, SEARCH, MAX_PLIES, LABEL = c['game'], c['search'], c['max_plies'], c['label']
     METRIC = '%s_mcts_simulations_per_sec' % GAME.lower()
@@ -81,7 +84,7 @@ def parse():
 def config_dict(args, n_gpus):
     search = 'FixedMCTS(maxDepth 10, c 0.85)' if SEARCH == 'fixed' else 'DynamicMCTS(c 0.85)'
     return {'workload': '%s %s self-play, %d sims/move, %d concurrent games/GPU, '
-                        'network blocks4/filters16/dense16 (%s)' % (GAME, search, args.sims, args.games, LABEL),
+                        'network blocks%d/filters%d/dense%d (%s)' % (GAME, search, args.sims, args.games, NET['blocks'], NET['filters'], NET['dense'], LABEL),
             'games_per_gpu': args.games, 'sims_per_move': args.sims, 'search': 'FixedMCTS' if SEARCH == 'fixed' else 'DynamicMCTS', 'max_depth': MAX_DEPTH,
             'step': 'one move round: the %d slots together play %d moves (FindMove+MoveRoot each), no barrier between moves, finished games restart in place' % (args.games, args.games),
             'prelude': '%d untimed move rounds at %d sims/move to desynchronise the slots, then the warm-up steps' % (args.prelude, min(32, args.sims)),
@@ -415,6 +418,8 @@ def run_ours(args):
     if streaming:
         kname = 'k_net_forward_tc<%s> serve mode' % GAME + ' (bf16 tcgen05 tower, persistent: %d evals/launch/GPU, batches of %.2f)' % (
             cp['evals'] / n_launch / per_world, cp['evals'] / per_world / prof_ticks)
+    elif args.precision == 'bf16' and NET['filters'] != 16:
+        kname = 'k_wide_conv<%d> x %d layers + stage + heads (bf16 tcgen05, layer by layer; %d evals per tick avg)' % (NET['filters'], 1 + 2 * NET['blocks'], cp['evals'] / prof_ticks)
     elif args.precision == 'bf16':
         kname = 'k_net_forward_tc<%s> (bf16 tcgen05 tower, %d evals/launch avg)' % (GAME, cp['evals'] / prof_ticks)
     else:
