@@ -793,7 +793,8 @@ static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, siz
             for (int o = 0; o < F; ++o) {
               const int ci = ks * 16 + k;
               const float v = ci < ci_n ? lw[((size_t)t * ci_n + ci) * F + o] : 0.f;
-              dst[((size_t)(ks * 9 + t) * F * 32) / 2 + (size_t)(k / 8) * F * 8 + (size_t)o * 8 + (k % 8)] = bf16_rn(v);   // [k-step][tap][2][F][8]
+              const int nm = F <= 64 ? F : F / 2, hp = o / nm, on = o % nm;       // passes of net_wide.cuh (WideCfg::NS): [pass][k-step][tap][2][nm][8]
+              dst[((size_t)((hp * ks_n + ks) * 9 + t) * nm * 32) / 2 + (size_t)(k / 8) * nm * 8 + (size_t)on * 8 + (k % 8)] = bf16_rn(v);
             }
     }
     if ((rc = upload(wb.data(), wb.size() * 2, (const void**)&wd.wbf))) return rc;

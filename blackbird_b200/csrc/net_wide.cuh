@@ -42,14 +42,16 @@ inline WideGeo wide_geo() { return WideGeo{G::H, G::W, TcGeom<G>::LW, TcGeom<G>:
 template <int F>
 struct WideCfg {
   static constexpr int TPG = F <= 64 ? 4 : 2;                        // tiles per group
-  static constexpr int NACC = F <= 64 ? 2 : 1;                       // accumulator sets (2: the epilogue of group g overlaps the MMAs of group g + 1)
-  static constexpr int ACC_COLS = TPG * F;                           // TMEM columns of one accumulator set
+  static constexpr int NS = F <= 64 ? 1 : 2;                         // passes over a group, each producing F / NS output channels (N of the MMA)
+  static constexpr int NM = F / NS;                                  // output channels per pass: 64 / 128
+  static constexpr int NACC = 2;                                     // accumulator sets: the epilogue of one pass overlaps the MMAs of the next
+  static constexpr int ACC_COLS = TPG * NM;                          // TMEM columns of one accumulator set
   static constexpr int TMEM_COLS = NACC * ACC_COLS <= 256 ? 256 : 512;
   static_assert(NACC * ACC_COLS <= 512, "TMEM has 512 columns");
   static constexpr int KS_MAX = F / 16;                              // k-steps of a full-width layer
-  static constexpr int TPS = F <= 64 ? 3 : 1;                        // taps per weight-ring stage
-  static constexpr int STAGE = TPS * F * 32;                         // bytes per stage: 6 KB / 8 KB
-  static constexpr int NST = F <= 64 ? 16 : 22;                      // weight-ring stages (96 KB / 176 KB: ~2.5 k-steps of latency cover at F = 256)
+  static constexpr int TPS = 3;                                      // taps per weight-ring stage
+  static constexpr int STAGE = TPS * NM * 32;                        // bytes per stage: 6 KB / 12 KB
+  static constexpr int NST = F <= 64 ? 16 : 14;                      // weight-ring stages (96 KB / 168 KB: ~4.7 k-steps of a pass ahead at F = 256)
   static constexpr int TILE_BYTES = (F / 8) * WIDE_PLANE;            // one tile of F-channel activations (in HBM)
   static constexpr int NKA = 4;                                      // activation-ring slots: one k-step (two planes) of every tile of the group each
   static constexpr int A_SLOT = TPG * 2 * WIDE_PLANE;                // bytes per slot: 20 KB / 10 KB
@@ -69,7 +71,7 @@ struct WideLayer {
   const uint8_t* in;       // input activations (tiles of 2 * ksteps planes)
   uint8_t* out;            // output activations (tiles of F / 8 planes)
   const uint8_t* skip;     // block input to add before the ReLU (may alias out), or null
-  const uint8_t* w;        // this layer's weights [k-step][tap][2][F][8]
+  const uint8_t* w;        // this layer's weights [pass][k-step][tap][2][F / passes][8]
   const float* bias;       // [F]
   int ksteps;              // 16-channel steps of the input (stem: ceil(cin / 16); else F / 16)
 };
@@ -95,7 +97,7 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // One (k-step, tap) of a tile group in ONE asm block: the same weight operand against the A operand of up to four tiles
 // (descriptor low words differ by the tile stride, accumulators by F columns).  The issuing thread's instruction count
 // per MMA is what paces the tensor pipe when descriptors are rebuilt in C (~110 cycles per MMA measured; N = 64 needs 32).
-template <int F, int TPG>
+template <int NM, int TPG>
 __device__ __forceinline__ void umma_group(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t a_step, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
                                            uint32_t accumulate, int nt) {
   if (TPG == 4) {
@@ -118,7 +120,7 @@ __device__ __forceinline__ void umma_group(uint32_t tmem_d, uint32_t a_lo, uint3
         "@p2 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
         "add.u32 al, al, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, dd, %9;\n"
         "@p3 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
-        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(F)
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(NM)
         : "memory");
   } else {
     asm volatile(
@@ -134,7 +136,7 @@ __device__ __forceinline__ void umma_group(uint32_t tmem_d, uint32_t a_lo, uint3
         "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], ad, bd, %6, pz;\n"
         "add.u32 al, %1, %3;\n  mov.b64 ad, {al, %2};\n  add.u32 dd, %0, %9;\n"
         "@p1 tcgen05.mma.cta_group::1.kind::f16 [dd], ad, bd, %6, pz;\n"
-        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(F)
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(a_step), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(nt), "n"(NM)
         : "memory");
   }
 }
@@ -188,7 +190,8 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
     // ---- producer: per k-step the group's two planes per tile, then the k-step's weight stages -------------------------
     if (lane == 0) {
       unsigned wseq = 0, aseq = 0;
-      for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+      for (int g = blockIdx.x; g < n_groups; g += gridDim.x)
+      for (int h = 0; h < C::NS; ++h) {                              // a pass streams the group's activations again and its own half of the weights
         const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
         for (int ks = 0; ks < ksteps; ++ks, ++aseq) {
           const unsigned sl = aseq % C::NKA;
@@ -202,22 +205,23 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
           for (int c = 0; c < SPK; ++c, ++wseq) {
             const unsigned s = wseq % C::NST;
             mbar_wait(&w_free[s], ((wseq / C::NST) & 1u) ^ 1u);
-            bulk_g2s(sRing + s * C::STAGE, L.w + (size_t)(ks * SPK + c) * C::STAGE, C::STAGE, &w_full[s]);
+            bulk_g2s(sRing + s * C::STAGE, L.w + (size_t)((h * ksteps + ks) * SPK + c) * C::STAGE, C::STAGE, &w_full[s]);
           }
         }
       }
     }
   } else if (warp == 1) {
     // ---- MMA issuer (warp-uniform control flow, one elected lane issues) -------------------------------------------
-    constexpr uint32_t IDESC = umma_idesc_bf16(128, F);
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, C::NM);
     unsigned wseq = 0, it = 0;
     WT(long long wa = 0; long long wd = 0; long long ww = 0; long long ngr = 0; const long long t_in = clock64();)
     const uint64_t adesc0 = umma_desc(smem_u32(sA) + TC_MARGIN * 16, WIDE_PLANE, 128);
     const uint32_t a_hi = (uint32_t)(adesc0 >> 32), a_lo0 = (uint32_t)adesc0, a_step = (2 * WIDE_PLANE) >> 4;
     unsigned aseq = 0;
-    const uint64_t bdesc0 = umma_desc(smem_u32(sRing), F * 16, 128);
+    const uint64_t bdesc0 = umma_desc(smem_u32(sRing), C::NM * 16, 128);
     const uint32_t b_hi = (uint32_t)(bdesc0 >> 32), b_lo0 = (uint32_t)bdesc0;
-    for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
+    for (int g = blockIdx.x; g < n_groups; g += gridDim.x)
+    for (int h = 0; h < C::NS; ++h, ++it) {
       const unsigned b = it % C::NACC, use = it / C::NACC;
       const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
       WT(const long long q1 = clock64();)
@@ -241,7 +245,7 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
           for (int tt = 0; tt < C::TPS; ++tt) {
             const int tap = c * C::TPS + tt;
             const int toff = (tap / 3 - 1) * geo.LW + (tap % 3 - 1);
-            umma_group<F, C::TPG>(dcol, a_ks + (uint32_t)toff, a_hi, a_step, b_lo0 + (uint32_t)((s * C::STAGE + tt * F * 32) >> 4), b_hi, IDESC,
+            umma_group<C::NM, C::TPG>(dcol, a_ks + (uint32_t)toff, a_hi, a_step, b_lo0 + (uint32_t)((s * C::STAGE + tt * C::NM * 32) >> 4), b_hi, IDESC,
                                   (ks | tap) ? 1u : 0u, nt);
           }
           umma_commit_elect(&w_free[s]);
@@ -257,10 +261,11 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
     const int q = warp & 3, rt = q * 32 + lane;
     const int pl = rt / geo.RPP, l = rt % geo.RPP, line = l / geo.LW, col = l % geo.LW;
     const bool cell = pl < geo.PPT && line >= 1 && col < geo.W;     // this row is a board cell (in every tile)
-    constexpr int NPL = F / 8;                                       // planes of an output tile
+    constexpr int NPL = C::NM / 8;                                   // planes one pass writes per tile
     constexpr int SKR = NPL <= 8 ? NPL : 16;                         // skip planes held in registers ahead of their use
     unsigned it = 0;
-    for (int g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
+    for (int g = blockIdx.x; g < n_groups; g += gridDim.x)
+    for (int h = 0; h < C::NS; ++h, ++it) {
       const unsigned b = it % C::NACC, use = it / C::NACC;
       const int t0 = g * C::TPG, nt = min(C::TPG, n_tiles - t0);
       // The skip rows do not depend on this layer's MMAs: the first ones are asked for BEFORE the wait for the accumulator, and
@@ -270,7 +275,7 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
       const size_t row_off = (size_t)(rt + TC_MARGIN) * 16;
       const bool has_skip = L.skip != nullptr;
       auto skip_ptr = [&](int lin) {                                 // lin = tile-in-group * NPL + plane
-        return L.skip + (size_t)(t0 + lin / NPL) * C::TILE_BYTES + (size_t)(lin % NPL) * WIDE_PLANE + row_off;
+        return L.skip + (size_t)(t0 + lin / NPL) * C::TILE_BYTES + (size_t)(h * NPL + lin % NPL) * WIDE_PLANE + row_off;
       };
       if (has_skip && cell) {
 #pragma unroll
@@ -280,20 +285,21 @@ __global__ void __launch_bounds__(192, 1) k_wide_conv(WideLayer L, WideGeo geo, 
       tc_fence_after();
       for (int i = 0; i < nt; ++i) {
         const bool ok = cell && (t0 + i) * geo.PPT + pl < cnt;
-        uint8_t* orow = L.out + (size_t)(t0 + i) * C::TILE_BYTES + row_off;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + b * C::ACC_COLS + i * F;
+        uint8_t* orow = L.out + (size_t)(t0 + i) * C::TILE_BYTES + (size_t)(h * NPL) * WIDE_PLANE + row_off;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + b * C::ACC_COLS + i * C::NM;
+        const float* bias_h = sBias + h * C::NM;
 #pragma unroll
-        for (int cb = 0; cb < F / 32; ++cb) {                        // 32 channels (four planes) per step: two loads in flight
+        for (int cb = 0; cb < C::NM / 32; ++cb) {                        // 32 channels (four planes) per step: two loads in flight
           uint32_t r[32];
           tmem_ld16_nowait(taddr + cb * 32, r);
           tmem_ld16_nowait(taddr + cb * 32 + 16, r + 16);
           tmem_ld_wait();
 #pragma unroll
-          for (int h = 0; h < 4; ++h) {                              // plane cb * 4 + h: channels cb * 32 + h * 8 ..
-            const int plane = cb * 4 + h;
+          for (int hh = 0; hh < 4; ++hh) {                           // plane cb * 4 + hh of this pass: channels cb * 32 + hh * 8 ..
+            const int plane = cb * 4 + hh;
             float v[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[h * 8 + k]) + sBias[cb * 32 + h * 8 + k];
+            for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[hh * 8 + k]) + bias_h[cb * 32 + hh * 8 + k];
             if (has_skip && cell) {
               const uint4 skv = sk[plane % SKR];
               const uint32_t sw[4] = {skv.x, skv.y, skv.z, skv.w};
