@@ -11,8 +11,9 @@
 //                contiguous block: ONE cp.async.bulk brings it into shared memory, and the nine taps of the convolution
 //                are the same block read through descriptors whose start address is shifted by tap_offset x 16 bytes.
 //                Padding rows are zeroed once at allocation and never written.
-//   weights      w[layer][k-step][tap][2][F][8] bf16 (BN folded): a (k-step, tap) is an N = F, K = 16 operand of F x 32 bytes;
-//                a ring stage is one bulk copy of three taps (F = 64, 6 KB) or one tap (F = 256, 8 KB).
+//   weights      w[layer][pass][k-step][tap][2][N][8] bf16 (BN folded), N = 64 (F = 64, one pass) or 128 (F = 256, two passes
+//                over a tile group, each producing half of the output channels): a (k-step, tap) is an N x K16 operand of
+//                N x 32 bytes; a ring stage is one bulk copy of three taps (6 / 12 KB).
 //   accumulator  128 rows x F fp32 columns of TMEM per tile; a CTA works on a GROUP of tiles at a time (4 at F = 64, 2 at
 //                F = 256) so that every weight stage is used by all tiles of the group before it is released.  Only four
 //                k-steps of the group's activations are in shared memory at a time (a 40 / 80 KB ring); the rest is the weight ring.
@@ -20,8 +21,8 @@
 //                weight stages through a 7-8 stage ring), warp 1 = MMA issuer (one elected lane; M128 N F K16, kind::f16, one
 //                asm block per (k-step, tap) covering the group's tiles), warps 2-5 = epilogue (tcgen05.ld, bias, skip rows
 //                prefetched from HBM into registers before the accumulator is waited for, ReLU, bf16, 16-byte stores that are
-//                512 contiguous bytes per warp).  At F = 64 accumulators are double-buffered (the epilogue of group g overlaps
-//                the MMAs of group g + 1); at F = 256 one group fills TMEM (512 columns).
+//                512 contiguous bytes per warp).  Accumulators are double-buffered at both widths (2 x 256 TMEM columns): the
+//                epilogue of one pass runs under the MMAs of the next.
 //   heads        k_wide_heads<G>: 1x1 head convolutions from the last activations, fixed-order sums, then heads_finish.
 //
 // The fp32 twin (precision 0) is plain SIMT over NHWC fp32 activations: it is the 1e-5 parity path, not a fast one.
