@@ -327,18 +327,21 @@ class Replay(object):
         return self._eval(planes)[1]
 
 
-@pytest.mark.parametrize('kind,P,precision', [('dynamic', 64, 'fp32'), ('fixed', 24, 'fp32'),
-                                              ('dynamic', 64, 'bf16'), ('fixed', 24, 'bf16')])
-def test_selfplay_with_network_replay(mods, kind, P, precision):
+@pytest.mark.parametrize('kind,P,precision,filters', [('dynamic', 64, 'fp32', 16), ('fixed', 24, 'fp32', 16),
+                                                      ('dynamic', 64, 'bf16', 16), ('fixed', 24, 'bf16', 16),
+                                                      ('fixed', 24, 'bf16', 64), ('dynamic', 40, 'bf16', 256), ('fixed', 16, 'fp32', 40)])
+def test_selfplay_with_network_replay(mods, kind, P, precision, filters):
     """Self-play driven by the built-in network vs the oracle search fed with the SAME kernel's outputs
     (replayed per position): visit counts, moves and record bytes must agree exactly.  fp32 runs in tick
-    mode, bf16 in streaming mode (persistent search + network kernels, request ring)."""
+    mode, bf16 in streaming mode (persistent search + network kernels, request ring) at the template width and in
+    tick mode behind the layer-by-layer kernels at 64 / 256 filters."""
     engine, records = mods
     game, G = 'Connect4', 6
-    w = network_np.init_weights(3, 7, seed=2, jitter=0.1)
+    blocks = 4 if filters == 16 else 1
+    w = network_np.init_weights(3, 7, blocks=blocks, filters=filters, dense=16, seed=2, jitter=0.1)
     eng = engine.Engine(game, kind, n_games=G, evaluator='net', play_limit_hint=P)
-    eng.load_network(network_np.flatten_weights(w), 4, 16, 16, precision=precision)
-    assert eng.streaming == (precision == 'bf16')
+    eng.load_network(network_np.flatten_weights(w), blocks, filters, 16, precision=precision)
+    assert eng.streaming == (precision == 'bf16' and filters == 16)
     u = np.stack([np.random.RandomState(1000 + g).random_sample(eng.max_plies) for g in range(G)])
     eng.selfplay(P, 1.0, u)
     got = records.build_records(eng)
