@@ -537,3 +537,33 @@ def test_noise_statistics(mods):
     pol2, _ = eng.net_forward(dev)
     assert not torch.equal(pol, pol2)          # fresh draw on every evaluation
     eng.close()
+
+
+def test_dragonchess_selfplay_behind_a_wide_network(mods):
+    """DragonChess self-play with a 64-filter network (tick mode; k_wide_heads answers at the legal actions only, a warp per
+    position): two runs give the same records, every recorded root has exactly the legal moves as children (in order), and the
+    chosen move was visited."""
+    engine, records = mods
+    game, G, P = 'DragonChess', 8, 10
+    C, A = engine.plane_shape(game)[2], engine.n_actions(game)
+    w = network_np.init_weights(C, A, blocks=1, filters=64, dense=16, seed=13, jitter=0.2)
+    runs = []
+    for _ in range(2):
+        eng = engine.Engine(game, 'dynamic', n_games=G, evaluator='net', play_limit_hint=P, max_plies=24, node_cap=16384)
+        eng.load_network(network_np.flatten_weights(w), 1, 64, 16, precision='bf16')
+        assert not eng.streaming
+        u = np.stack([np.random.RandomState(2000 + g).random_sample(eng.max_plies) for g in range(G)])
+        eng.selfplay(P, 1.0, u)
+        runs.append((records.build_records(eng), eng.records_raw()))
+        eng.close()
+    assert runs[0][0] == runs[1][0]
+    raw = runs[0][1]
+    for g in range(G):
+        s = GAMES[game]()
+        for ply in range(int(raw['n_moves'][g])):
+            lo, hi = int(raw['rec_off'][g, ply]), int(raw['rec_off'][g, ply + 1])
+            legal = np.flatnonzero(s.LegalActions() == 1)
+            assert np.array_equal(raw['pool_actions'][g, lo:hi], legal)
+            a = int(raw['chosen'][g, ply])
+            assert raw['pool_plays'][g, lo:hi][list(legal).index(a)] > 0
+            s.ApplyAction(a)
