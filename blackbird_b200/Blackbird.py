@@ -103,8 +103,11 @@ def GenerateTrainingSamples(model, nGames, temp, uniforms=None, precision='bf16'
     if max_slots:
         slots = max(1, min(slots, int(max_slots)))         # concurrent games on the GPU (default: what the memory budget allows)
     evaluator = getattr(model, '_SELFPLAY_EVALUATOR', 'net')   # 'kat'  only in parity tests
+    # networks wider than the template's 16 filters run tick by tick (no persistent kernel pair): eight lanes keep the tensor
+    # cores busy with one lane's network launch while the others search (measured: 1.8 -> 2.6 M sims/s at 256 filters)
+    wide = evaluator == 'net' and int(getattr(getattr(model, '_net_shape', None), 'filters', 16) or 16) != 16
     eng = _engine.Engine(game, search, n_games=slots, max_depth=max_depth, exploration_rate=model.ExplorationRate,
-                         evaluator=evaluator, play_limit_hint=play_limit, device=model.DEVICE)
+                         evaluator=evaluator, play_limit_hint=play_limit, device=model.DEVICE, lanes=8 if wide and slots >= 64 else 0)
     written = 0
     try:
         if evaluator == 'net':

@@ -232,6 +232,33 @@ def test_train_with_examples_mirror(bb, tmp_path, monkeypatch):
     model.Conn.Close()
 
 
+def test_main_sequence_with_a_64_filter_network(bb, tmp_path, monkeypatch):
+    """`filters` comes from the YAML (NetworkFactory.py:46-103): main.py's sequence with a 64-filter network on Connect4 --
+    self-play behind the layer-by-layer tensor-core kernels (tick mode), records in the database, one TrainWithExamples
+    pass with the width-generic trainer kernels, and a search with the trained weights."""
+    monkeypatch.chdir(tmp_path)
+    B = bb['Blackbird']
+    cfg = {'maxDepth': 6, 'explorationRate': 0.85, 'timeLimit': None, 'playLimit': 16,
+           'temperature': {'exploration': 1, 'exploitation': 0.1}}
+    net = {'hasTeacher': False, 'blocks': 1, 'filters': 64, 'eval': {'dense': 16},
+           'policy': {'dirichlet': {'epsilon': 0.3, 'alpha': 0.2}}, 'loss': {'L2_norm': 0.001},
+           'training': {'optimizer': 'adam', 'learning_rate': 1e-3, 'momentum': 0.9, 'batch_size': 50}}
+    model = B.FixedModel(bb['games']['Connect4'], 'Wide', cfg, net, {})
+    n = B.GenerateTrainingSamples(model, 96, 1)
+    recs = model.Conn.GetGames(model.Name, model.Version)
+    assert n == len(recs) and n >= 96 * 8
+    ex = B.ExampleState.FromSerialized(recs[0])
+    assert ex.Board.shape == (1, 6, 7, 3) and abs(ex.MctsPolicy.sum() - 1) < 1e-12
+    w0 = model.getWeights().copy()
+    B.TrainWithExamples(model, batchSize=50, learningRate=1e-3)
+    assert model.Version == 2 and not np.array_equal(w0, model.getWeights())
+    assert all(np.isfinite(x) for x in model.lastLosses)
+    s = model.Game()
+    nxt, v, probs = model.FindMove(s, 1, playLimit=16)
+    assert abs(probs.sum() - 1) < 1e-9
+    model.Conn.Close()
+
+
 @pytest.mark.parametrize('index', [0, 1, 2, 3])
 def test_random_arena_vs_reference(bb, golden, index):
     """Blackbird.TestRandom (Blackbird.py:84-112) against the RandomMCTS mirror: with random.seed / np.random.seed
