@@ -85,8 +85,8 @@ class Network(object):
         seed = _entropy(48) if seed is None else seed     # TF's noise is unseeded too; never drawn from `random` / `np.random` (the arena goldens replay those streams)
         s = self._net_shape
         precision = precision or self.PRECISION
-        if precision == 'bf16' and s.filters not in (16, 64, 256):
-            precision = 'fp32'                            # tensor-core kernels exist for 16 / 64 / 256 filters; the fp32 CUDA kernels take any width
+        if precision == 'bf16' and s.filters not in (16, 32, 64, 128, 256):
+            precision = 'fp32'                            # tensor-core kernels exist for 16 / 32 / 64 / 128 / 256 filters; the fp32 CUDA kernels take any width
         eng.load_network(self._net_loaded_weights, s.blocks, s.filters, s.dense,
                          epsilon=s.epsilon if epsilon is None else epsilon, alpha=s.alpha, seed=seed,
                          precision=precision)

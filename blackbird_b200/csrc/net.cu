@@ -634,8 +634,10 @@ static int net_launch_wide(NetDev* net, const void* states, int n, const int* co
         L.w = wd.wbf + wd.wbf_off[l];
         L.bias = wd.bias + (size_t)l * F;
         L.ksteps = l == 0 ? wd.ksteps0 : F / 16;
-        int rc = F == 64 ? wide_conv_launch<64>(L, geo, nc, base, count_dev, net->sm_count, stream)
-                         : wide_conv_launch<256>(L, geo, nc, base, count_dev, net->sm_count, stream);
+        int rc = F == 32 ? wide_conv_launch<32>(L, geo, nc, base, count_dev, net->sm_count, stream)
+               : F == 64 ? wide_conv_launch<64>(L, geo, nc, base, count_dev, net->sm_count, stream)
+               : F == 128 ? wide_conv_launch<128>(L, geo, nc, base, count_dev, net->sm_count, stream)
+                          : wide_conv_launch<256>(L, geo, nc, base, count_dev, net->sm_count, stream);
         if (rc != BB_OK) return rc;
         last = L.out;
       }
@@ -717,7 +719,7 @@ static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, siz
   const int F = d->filters, D = d->dense, blocks = d->blocks, cin = d->cin, A = G::A, HW = G::H * G::W;
   const bool tc = d->precision == 1;
   if (F < 1 || F > 1024) { set_error("filters must be in [1, 1024] (got %d)", F); return BB_EINVAL; }
-  if (tc && F != 64 && F != 256) { set_error("the tensor-core network kernels are built for filters = 16, 64 and 256 (got %d); precision fp32 takes any width", F); return BB_EINVAL; }
+  if (tc && F != 32 && F != 64 && F != 128 && F != 256) { set_error("the tensor-core network kernels are built for filters = 16, 32, 64, 128 and 256 (got %d); precision fp32 takes any width", F); return BB_EINVAL; }
   if (cin != G::C) { set_error("cin %d does not match the game's %d input planes", cin, G::C); return BB_EINVAL; }
   if (D < 1 || D > NET_MAX_DENSE || blocks < 0) { set_error("dense must be in [1,%d], blocks >= 0", NET_MAX_DENSE); return BB_EINVAL; }
   auto conv_sz = [](int k, int ci, int co) { return (size_t)k * k * ci * co + 5 * (size_t)co; };
@@ -793,7 +795,7 @@ static int net_build_wide(NetDev* net, const bb_net_desc* d, const float* w, siz
             for (int o = 0; o < F; ++o) {
               const int ci = ks * 16 + k;
               const float v = ci < ci_n ? lw[((size_t)t * ci_n + ci) * F + o] : 0.f;
-              const int nm = F <= 64 ? F : F / 2, hp = o / nm, on = o % nm;       // passes of net_wide.cuh (WideCfg::NS): [pass][k-step][tap][2][nm][8]
+              const int nm = F <= 128 ? F : F / 2, hp = o / nm, on = o % nm;       // passes of net_wide.cuh (WideCfg::NS): [pass][k-step][tap][2][nm][8]
               dst[((size_t)((hp * ks_n + ks) * 9 + t) * nm * 32) / 2 + (size_t)(k / 8) * nm * 8 + (size_t)on * 8 + (k % 8)] = bf16_rn(v);
             }
     }

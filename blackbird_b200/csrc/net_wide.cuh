@@ -1,7 +1,7 @@
 // Policy-value network forward for tower widths other than the template's 16 filters (NetworkFactory.py:46-103 takes
 // `filters` from the YAML; SURVEY.md 8d row 5a lists 64 and 256).  Included by net.cu after net_tc.cuh.
 //
-// At 16 filters the whole tower lives in one CTA's shared memory (net_tc.cuh).  At 64 / 256 filters one 3x3 layer is
+// At 16 filters the whole tower lives in one CTA's shared memory (net_tc.cuh).  At 64 / 256 filters (32 and 128 are built too) one 3x3 layer is
 // 74 KB / 1.18 MB of bf16 weights, so the tower runs LAYER BY LAYER: activations stay in HBM / L2 between layers in exactly
 // the layout the tensor cores read them in, weights stream through a shared-memory ring.
 //
@@ -42,9 +42,10 @@ inline WideGeo wide_geo() { return WideGeo{G::H, G::W, TcGeom<G>::LW, TcGeom<G>:
 
 template <int F>
 struct WideCfg {
+  static_assert(F == 32 || F == 64 || F == 128 || F == 256, "tower widths of the layer-by-layer kernel");
   static constexpr int TPG = F <= 64 ? 4 : 2;                        // tiles per group
-  static constexpr int NS = F <= 64 ? 1 : 2;                         // passes over a group, each producing F / NS output channels (N of the MMA)
-  static constexpr int NM = F / NS;                                  // output channels per pass: 64 / 128
+  static constexpr int NS = F <= 128 ? 1 : 2;                        // passes over a group, each producing F / NS output channels (N of the MMA)
+  static constexpr int NM = F / NS;                                  // output channels per pass: 32 / 64 / 128 / 128
   static constexpr int NACC = 2;                                     // accumulator sets: the epilogue of one pass overlaps the MMAs of the next
   static constexpr int ACC_COLS = TPG * NM;                          // TMEM columns of one accumulator set
   static constexpr int TMEM_COLS = NACC * ACC_COLS <= 256 ? 256 : 512;

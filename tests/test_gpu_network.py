@@ -136,7 +136,8 @@ def test_bf16_launch_mode_vs_fp64(mods, game, n_states, jitter, seed):
 
 
 WIDE_CASES = [('TicTacToe', 64, 2, 300), ('Connect4', 64, 2, 400), ('DragonChess', 64, 1, 60),
-              ('TicTacToe', 256, 1, 200), ('Connect4', 256, 1, 150), ('DragonChess', 256, 1, 24)]
+              ('TicTacToe', 256, 1, 200), ('Connect4', 256, 1, 150), ('DragonChess', 256, 1, 24),
+              ('Connect4', 32, 2, 300), ('Connect4', 128, 1, 200), ('DragonChess', 32, 1, 40), ('TicTacToe', 128, 1, 150)]
 
 
 @pytest.mark.parametrize('game,filters,blocks,n', WIDE_CASES + [('Connect4', 40, 1, 100)])
@@ -177,7 +178,7 @@ def test_other_tower_widths_bf16_vs_fp64(mods, game, filters, blocks, n):
     dev_all = pack(engine, game, states)
     planes_all = np.concatenate([s.AsInputArray() for s in states])
     ppt = {'TicTacToe': 8, 'Connect4': 2, 'DragonChess': 1}[game]
-    tpg = 4 if filters == 64 else 2
+    tpg = 4 if filters <= 64 else 2
     for m in (1, ppt * tpg - 1, ppt * tpg + 1, n, ppt * tpg * 148 * 2 + 5, 4096 + 3 * ppt + 1):
         idx = np.arange(m) % n
         dev = dev_all[torch.as_tensor(idx, device=dev_all.device)]

@@ -148,7 +148,7 @@ def net_sweep_widths():
     peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'MEASURED_PEAKS.json'))) \
         if os.path.exists(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'MEASURED_PEAKS.json')) else {}
     for game in ('Connect4', 'TicTacToe', 'DragonChess'):
-        for filters in (64, 256):
+        for filters in (32, 64, 128, 256):
             eng = Engine(game, 'fixed', n_games=4, evaluator='net', lanes=1)
             w = netinit.random_weights(engine.plane_shape(game)[2], engine.n_actions(game), seed=0, blocks=4, filters=filters, dense=16)
             eng.load_network(w, 4, filters, 16, precision='bf16')
