@@ -58,7 +58,7 @@ struct StreamCtl {
   unsigned long long cyc_search_busy, cyc_search_total; // search warps: cycles inside advance_slot / resident (measurement)
   unsigned long long search_calls;                      // advance_slot calls (measurement)
 #ifdef BB_SEARCH_TIMING
-  unsigned long long sdbg[12];
+  unsigned long long sdbg[24];
   unsigned long long xdbg[8];     // expand_node: legal rows + scan, list + policy reads, prior sum, node writes; calls
 #endif
 #ifdef BB_NET_TIMING_HEADS

@@ -689,10 +689,12 @@ struct EngineT : bb_engine {
       fprintf(stderr, "[bbengine] expand_node (wide games) per call: legal rows + scan %.0f, list + policy reads %.0f, prior sum %.0f, node writes %.0f cycles\n",
               (double)h.xdbg[0] / h.xdbg[4], (double)h.xdbg[1] / h.xdbg[4], (double)h.xdbg[2] / h.xdbg[4], (double)h.xdbg[3] / h.xdbg[4]);
     if (getenv("BB_DEBUG_STREAM") && h.search_calls) {
-      const char* nm[6] = {"load", "post_request", "expand", "select level", "backup", "other"};
-      for (int i = 0; i < 6; ++i)
-        fprintf(stderr, "[bbengine] advance_slot %-13s %8.0f cycles per call (%.2f per call, %.0f cycles each)\n", nm[i], (double)h.sdbg[i] / h.search_calls,
-                (double)h.sdbg[6 + i] / h.search_calls, h.sdbg[6 + i] ? (double)h.sdbg[i] / h.sdbg[6 + i] : 0.0);
+      const char* nm[12] = {"load", "post_request", "expand", "select level", "backup", "(unused)", "top -> post (winner test, cache miss)", "-> expand (cache hit / answer)",
+                            "-> select", "leaf -> post (cache miss)", "leaf -> backup", "exit"};
+      for (int i = 0; i < 12; ++i)
+        if (h.sdbg[12 + i])
+          fprintf(stderr, "[bbengine] advance_slot %-38s %8.0f cycles per call (%.2f per call, %.0f cycles each)\n", nm[i], (double)h.sdbg[i] / h.search_calls,
+                  (double)h.sdbg[12 + i] / h.search_calls, (double)h.sdbg[i] / h.sdbg[12 + i]);
     }
 #endif
     if (h.stop == 2u) { set_error("streaming watchdog fired: a search warp or the network kernel waited for seconds (see stderr)"); return BB_ESTATE; }

@@ -169,8 +169,8 @@ template <class G, bool RO = false>
 __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScratch& ws, uint32_t* ticket = nullptr) {
   const int lane = lane_id();
 #ifdef BB_SEARCH_TIMING
-  long long st_acc[6] = {0, 0, 0, 0, 0, 0};
-  int st_cnt[6] = {0, 0, 0, 0, 0, 0};
+  long long st_acc[12] = {0};
+  int st_cnt[12] = {0};
 #endif
   ST_T0();
   Slot<G> s = E.slots[g];
@@ -239,7 +239,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
             continue;
           }
         }
-        ST_ADD(5);
+        ST_ADD(6);
         post_request(E, s, g, par);                             // GetPriors(state) of this node
         ST_ADD(1);
         n_evals += 1;
@@ -248,7 +248,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
       }
       step = meta_nchild(ch.meta) == 0 ? ST_LEAF : ST_SELECT;   // np.sum(LegalActions) == 0
     } else if (step == ST_EXPAND) {
-      ST_ADD(5);
+      ST_ADD(7);
       const int k = expand_node<G, RO>(E, s, nodes, s.cur, &ch, RO ? nullptr : pol_cached ? ws.cpol : E.resp_policy + (size_t)(E.q ? (uint32_t)g : s.req_idx) * G::A, ws,
                                        pol_cached);
       pol_cached = false;
@@ -260,7 +260,7 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
     } else if (step == ST_SELECT) {
       double u;
       NodeHdr chosen = ch;
-      ST_ADD(5);
+      ST_ADD(8);
 #ifdef BB_DEBUG
       if (ch.child_base + (uint32_t)meta_nchild(ch.meta) > s.n_nodes && lane == 0)
         printf("DBG g=%d cur=%u depth=%d cb=%u nch=%d meta=%x n_nodes=%u ply=%d half=%u root=%u rp=%u cp_n=%u cp_head=%u\n", g, s.cur, s.depth,
@@ -298,14 +298,14 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
         }
       }
       if (!(ch.meta & META_HAS_VALUE)) {
-        ST_ADD(5);
+        ST_ADD(9);
         post_request(E, s, g, par);                             // getEvaluation(state) of the leaf
         ST_ADD(1);
         n_evals += 1;
         s.phase = BB_PH_WAIT_LEAF;
         break;
       }
-      ST_ADD(5);
+      ST_ADD(10);
       backup(s, nodes, path, ch.eval);
       ST_ADD(4);
       }
@@ -382,8 +382,8 @@ __device__ int advance_slot(const EngineDev<G>& E, int g, unsigned par, WarpScra
 #endif
   if (ticket) *ticket = s.req_idx;
 #ifdef BB_SEARCH_TIMING
-  ST_ADD(5);
-  if (lane == 0 && E.q) for (int i = 0; i < 6; ++i) { atomicAdd(&E.q->sdbg[i], (unsigned long long)st_acc[i]); atomicAdd(&E.q->sdbg[6 + i], (unsigned long long)st_cnt[i]); }
+  ST_ADD(11);
+  if (lane == 0 && E.q) for (int i = 0; i < 12; ++i) { atomicAdd(&E.q->sdbg[i], (unsigned long long)st_acc[i]); atomicAdd(&E.q->sdbg[12 + i], (unsigned long long)st_cnt[i]); }
 #endif
   if (lane == 0) {
     E.slots[g] = s;
