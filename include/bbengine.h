@@ -97,7 +97,9 @@ int bb_engine_destroy(bb_engine* e);
 
 /* ---- built-in network (NetworkFactory.py:22-183 forward, Network.py:48-64) ---------------- */
 typedef struct bb_net_desc {
-  int32_t blocks, filters, dense;   /* parameters_template.yaml:12-16 */
+  int32_t blocks, filters, dense;   /* parameters_template.yaml:12-16.  filters: 16 (the template: shared-memory-resident kernels, streaming
+                                       self-play); 32 / 64 / 128 / 256 with precision 1 (layer-by-layer tensor-core kernels, tick-mode
+                                       searches); any width up to 1024 with precision 0 */
   int32_t cin;                      /* input planes (3 / 3 / 17)      */
   float epsilon;                    /* policy noise weight (A.17); 0 = deterministic */
   float alpha;
